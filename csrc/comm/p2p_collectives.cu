@@ -1,0 +1,483 @@
+// NVLink-5 / NVSwitch peer-memory collectives for the gradient path (sm_100a).
+//
+// Every rank owns a "symmetric" arena (same layout on every GPU) that all peers have mapped
+// through CUDA IPC.  The kernels below read and write peers' arenas directly with 16-byte
+// loads/stores; cross-GPU ordering uses monotonically increasing 32-bit epochs in a per-rank
+// signal pad (st.release.sys / ld.acquire.sys), one slot per (CTA, peer), so no flag is ever
+// reset and a captured CUDA graph can be replayed (the epoch counters live on the device).
+//
+//   two-shot all-reduce : rank r reduces slice r from all peers, applies the fused epilogue,
+//                         and stores the result into every peer (reduce-scatter + all-gather
+//                         in one kernel, 2(N-1)/N * S bytes per GPU per direction)
+//   one-shot all-reduce : every rank reads all peers and reduces locally (small messages)
+//   broadcast           : the source rank stores into every peer (initial parameter sync and
+//                         the per-step BatchNorm buffer sync)
+//
+// Fused epilogues on the reduced value while it is still in registers:
+//   F1: x (1/world) x inv_scale, non-finite check -> found_inf word on every rank
+//   F2: F1 + SGD-momentum update of the fp32 master slice, new fp32 weights and bf16 shadow
+//       pushed to every peer (momentum stays sharded on the owner, ZeRO-1 style)
+//
+// Replaces torch DDP's Reducer -> ProcessGroupNCCL allreduce (reference train_ddp.py:305-310,
+// 207/213), GradScaler's unscale_ + found_inf.item() (:208) and, in F2, optimizer.step() (:214).
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+
+#include "../../include/dptb200.h"
+#include "../common/ptx.cuh"
+
+namespace dpt {
+
+constexpr int kMaxWorld = 8;
+constexpr int kMaxCommCtas = 64;
+constexpr int kCommThreads = 512;
+
+struct CommCtx {
+    int rank, world;
+    uint32_t* flags[kMaxWorld];  // signal pad of every rank: [kMaxCommCtas][kMaxWorld] u32
+    uint32_t* epoch;             // local: [kMaxCommCtas] barrier counters
+    uint32_t* err;               // local (host-mapped) error word, 0 = ok
+    unsigned long long timeout_ns;
+};
+
+struct Peers {
+    void* p[kMaxWorld];
+};
+
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+// All-ranks barrier for CTA index blockIdx.x.  Establishes: everything this CTA wrote (to any
+// GPU) before the call is visible to the matching CTA of every peer after its call returns.
+__device__ __forceinline__ void xgpu_barrier(const CommCtx& c, uint32_t e) {
+    __syncthreads();
+    if (threadIdx.x < c.world) {
+        const int peer = threadIdx.x;
+        uint32_t* remote = c.flags[peer] + blockIdx.x * kMaxWorld + c.rank;
+        __threadfence_system();
+        st_release_sys_u32(remote, e);
+        const uint32_t* mine = c.flags[c.rank] + blockIdx.x * kMaxWorld + peer;
+        const unsigned long long t0 = globaltimer_ns();
+        while (static_cast<int32_t>(ld_acquire_sys_u32(mine) - e) < 0) {
+            if (c.timeout_ns != 0 && globaltimer_ns() - t0 > c.timeout_ns) {
+                // peer never arrived: report (rank, peer, epoch) and stop waiting
+                atomicCAS(c.err, 0u, 0x80000000u | (uint32_t(peer) << 24) | (e & 0xffffffu));
+                break;
+            }
+        }
+    }
+    __syncthreads();
+}
+
+__device__ __forceinline__ float4 ld_stream(const float4* p) {
+    float4 r;
+    asm volatile("ld.global.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+                 : "l"(p)
+                 : "memory");
+    return r;
+}
+__device__ __forceinline__ void st_stream(float4* p, float4 v) {
+    asm volatile("st.global.L1::no_allocate.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x),
+                 "f"(v.y), "f"(v.z), "f"(v.w)
+                 : "memory");
+}
+
+struct Epilogue {
+    float scale;              // 1/world (times a static factor)
+    const float* inv_scale;   // optional device scalar (AMP 1/loss_scale)
+    float* found_inf[kMaxWorld];  // found_inf word of every rank (may be null)
+    // F2 (fused SGD) -- all null/0 for F1
+    float* param[kMaxWorld];          // fp32 master weights of every rank
+    __nv_bfloat16* shadow[kMaxWorld]; // bf16 shadow of every rank
+    float* momentum;                  // local momentum (only the owner's slice is touched)
+    float lr, mu, wd;
+    int nesterov;
+    int fused_sgd;
+};
+
+
+// grads: symmetric buffers (float), n4 = number of float4.  In place.
+template <int WORLD>
+__global__ void __launch_bounds__(kCommThreads, 1)
+allreduce_twoshot_kernel(CommCtx c, Peers grads, long long n4, Epilogue ep) {
+    __shared__ uint32_t s_epoch;
+    if (threadIdx.x == 0) s_epoch = c.epoch[blockIdx.x];
+    __syncthreads();
+    const uint32_t e0 = s_epoch;
+    xgpu_barrier(c, e0 + 1);  // every peer's bucket is complete and its consumers are done
+    constexpr int kUnroll = WORLD > 4 ? 2 : 4;  // keep WORLD * kUnroll float4 in registers
+
+    const long long per = (n4 + WORLD - 1) / WORLD;
+    const long long lo = per * c.rank;
+    const long long hi = min(n4, lo + per);
+    const float gs = ep.scale * (ep.inv_scale ? *ep.inv_scale : 1.f);
+    bool bad = false;
+    const long long step = static_cast<long long>(gridDim.x) * kCommThreads;
+    for (long long i0 = lo + static_cast<long long>(blockIdx.x) * kCommThreads + threadIdx.x;
+         i0 < hi; i0 += step * kUnroll) {
+        float4 v[kUnroll][WORLD];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            const long long i = i0 + u * step;
+            if (i < hi) {
+#pragma unroll
+                for (int p = 0; p < WORLD; ++p)
+                    v[u][p] = ld_stream(reinterpret_cast<const float4*>(grads.p[p]) + i);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            const long long i = i0 + u * step;
+            if (i >= hi) continue;
+            // fixed summation order => bitwise identical on every rank
+            float4 s = v[u][0];
+#pragma unroll
+            for (int p = 1; p < WORLD; ++p) {
+                s.x += v[u][p].x;
+                s.y += v[u][p].y;
+                s.z += v[u][p].z;
+                s.w += v[u][p].w;
+            }
+            bad |= !(isfinite(s.x) && isfinite(s.y) && isfinite(s.z) && isfinite(s.w));
+            s.x *= gs;
+            s.y *= gs;
+            s.z *= gs;
+            s.w *= gs;
+            if (!ep.fused_sgd) {
+#pragma unroll
+                for (int p = 0; p < WORLD; ++p)
+                    st_stream(reinterpret_cast<float4*>(grads.p[p]) + i, s);
+            } else {
+                float4 pv = reinterpret_cast<float4*>(ep.param[c.rank])[i];
+                float4 mv = reinterpret_cast<float4*>(ep.momentum)[i];
+                float pa[4] = {pv.x, pv.y, pv.z, pv.w};
+                float ma[4] = {mv.x, mv.y, mv.z, mv.w};
+                const float ga[4] = {s.x, s.y, s.z, s.w};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    float d = fmaf(ep.wd, pa[k], ga[k]);
+                    ma[k] = fmaf(ep.mu, ma[k], d);
+                    d = ep.nesterov ? fmaf(ep.mu, ma[k], d) : ma[k];
+                    pa[k] = fmaf(-ep.lr, d, pa[k]);
+                }
+                reinterpret_cast<float4*>(ep.momentum)[i] = make_float4(ma[0], ma[1], ma[2], ma[3]);
+                const float4 np = make_float4(pa[0], pa[1], pa[2], pa[3]);
+                __nv_bfloat162 b0 = __floats2bfloat162_rn(pa[0], pa[1]);
+                __nv_bfloat162 b1 = __floats2bfloat162_rn(pa[2], pa[3]);
+                uint2 pk;
+                pk.x = *reinterpret_cast<uint32_t*>(&b0);
+                pk.y = *reinterpret_cast<uint32_t*>(&b1);
+#pragma unroll
+                for (int p = 0; p < WORLD; ++p) {
+                    st_stream(reinterpret_cast<float4*>(ep.param[p]) + i, np);
+                    reinterpret_cast<uint2*>(ep.shadow[p])[i] = pk;
+                }
+            }
+        }
+    }
+    if (ep.found_inf[0] != nullptr && __any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) {
+#pragma unroll
+        for (int p = 0; p < WORLD; ++p) *ep.found_inf[p] = 1.f;
+    }
+    xgpu_barrier(c, e0 + 2);  // all slices have landed everywhere
+    if (threadIdx.x == 0) c.epoch[blockIdx.x] = e0 + 2;
+}
+
+// One-shot: out (local, may alias nothing symmetric that peers read) = epilogue(sum_p in_p).
+template <int WORLD>
+__global__ void __launch_bounds__(kCommThreads, 1)
+allreduce_oneshot_kernel(CommCtx c, Peers in, float* __restrict__ out, long long n4, Epilogue ep) {
+    __shared__ uint32_t s_epoch;
+    if (threadIdx.x == 0) s_epoch = c.epoch[blockIdx.x];
+    __syncthreads();
+    const uint32_t e0 = s_epoch;
+    xgpu_barrier(c, e0 + 1);
+    const float gs = ep.scale * (ep.inv_scale ? *ep.inv_scale : 1.f);
+    bool bad = false;
+    const long long step = static_cast<long long>(gridDim.x) * kCommThreads;
+    for (long long i = static_cast<long long>(blockIdx.x) * kCommThreads + threadIdx.x; i < n4;
+         i += step) {
+        float4 v[WORLD];
+#pragma unroll
+        for (int p = 0; p < WORLD; ++p) v[p] = ld_stream(reinterpret_cast<const float4*>(in.p[p]) + i);
+        float4 s = v[0];
+#pragma unroll
+        for (int p = 1; p < WORLD; ++p) {
+            s.x += v[p].x;
+            s.y += v[p].y;
+            s.z += v[p].z;
+            s.w += v[p].w;
+        }
+        bad |= !(isfinite(s.x) && isfinite(s.y) && isfinite(s.z) && isfinite(s.w));
+        s.x *= gs;
+        s.y *= gs;
+        s.z *= gs;
+        s.w *= gs;
+        reinterpret_cast<float4*>(out)[i] = s;
+    }
+    if (ep.found_inf[0] != nullptr && __any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0)
+        *ep.found_inf[c.rank] = 1.f;
+    xgpu_barrier(c, e0 + 2);  // peers are done reading my input: it may be overwritten
+    if (threadIdx.x == 0) c.epoch[blockIdx.x] = e0 + 2;
+}
+
+// Broadcast n16 16-byte words from rank `src` into every peer's buffer (in place).
+__global__ void __launch_bounds__(kCommThreads, 1)
+broadcast_kernel(CommCtx c, Peers bufs, long long n16, int src) {
+    __shared__ uint32_t s_epoch;
+    if (threadIdx.x == 0) s_epoch = c.epoch[blockIdx.x];
+    __syncthreads();
+    const uint32_t e0 = s_epoch;
+    xgpu_barrier(c, e0 + 1);  // receivers are ready to be overwritten
+    if (c.rank == src) {
+        const long long step = static_cast<long long>(gridDim.x) * kCommThreads;
+        for (long long i = static_cast<long long>(blockIdx.x) * kCommThreads + threadIdx.x; i < n16;
+             i += step) {
+            const float4 v = reinterpret_cast<const float4*>(bufs.p[src])[i];
+            for (int p = 0; p < c.world; ++p)
+                if (p != src) st_stream(reinterpret_cast<float4*>(bufs.p[p]) + i, v);
+        }
+    }
+    xgpu_barrier(c, e0 + 2);
+    if (threadIdx.x == 0) c.epoch[blockIdx.x] = e0 + 2;
+}
+
+__global__ void barrier_kernel(CommCtx c) {
+    __shared__ uint32_t s_epoch;
+    if (threadIdx.x == 0) s_epoch = c.epoch[blockIdx.x];
+    __syncthreads();
+    const uint32_t e0 = s_epoch;
+    xgpu_barrier(c, e0 + 1);
+    if (threadIdx.x == 0) c.epoch[blockIdx.x] = e0 + 1;
+}
+
+// Local (world == 1) version of the F1/F2 epilogue so single-GPU runs share the code path.
+__global__ void __launch_bounds__(256)
+local_epilogue_kernel(float* __restrict__ g, long long n4, Epilogue ep) {
+    const float gs = ep.scale * (ep.inv_scale ? *ep.inv_scale : 1.f);
+    bool bad = false;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n4;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+        float4 s = reinterpret_cast<float4*>(g)[i];
+        bad |= !(isfinite(s.x) && isfinite(s.y) && isfinite(s.z) && isfinite(s.w));
+        s.x *= gs;
+        s.y *= gs;
+        s.z *= gs;
+        s.w *= gs;
+        reinterpret_cast<float4*>(g)[i] = s;
+    }
+    if (ep.found_inf[0] != nullptr && __any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0)
+        *ep.found_inf[0] = 1.f;
+}
+
+}  // namespace dpt
+
+using namespace dpt;
+
+// ---------------------------------------------------------------------------- host objects
+struct dpt_comm {
+    CommCtx ctx;
+    int device;
+    uint32_t* flags_local;
+    uint32_t* err_host;  // pinned, mapped
+    void* opened[kMaxWorld];
+};
+
+extern "C" int dpt_symm_alloc(size_t bytes, void** ptr, void* ipc_handle_64) {
+    cudaError_t e = cudaMalloc(ptr, bytes);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    e = cudaMemset(*ptr, 0, bytes);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    cudaIpcMemHandle_t h;
+    e = cudaIpcGetMemHandle(&h, *ptr);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    static_assert(sizeof(h) == 64, "ipc handle size");
+    memcpy(ipc_handle_64, &h, 64);
+    return 0;
+}
+
+extern "C" int dpt_symm_open(const void* ipc_handle_64, void** ptr) {
+    cudaIpcMemHandle_t h;
+    memcpy(&h, ipc_handle_64, 64);
+    return static_cast<int>(cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+}
+
+extern "C" int dpt_symm_close(void* ptr) { return static_cast<int>(cudaIpcCloseMemHandle(ptr)); }
+extern "C" int dpt_symm_free(void* ptr) { return static_cast<int>(cudaFree(ptr)); }
+
+extern "C" size_t dpt_comm_flag_bytes() { return sizeof(uint32_t) * kMaxCommCtas * kMaxWorld; }
+
+// flags[r] = this process's mapping of rank r's signal pad (flags[rank] is the local one).
+extern "C" int dpt_comm_create(int rank, int world, void* const* flags, double timeout_s,
+                               dpt_comm** out) {
+    if (world < 1 || world > kMaxWorld || rank < 0 || rank >= world) return DPT_ERR_ARG;
+    dpt_comm* c = new dpt_comm();
+    memset(c, 0, sizeof(*c));
+    c->ctx.rank = rank;
+    c->ctx.world = world;
+    for (int r = 0; r < world; ++r) c->ctx.flags[r] = static_cast<uint32_t*>(flags[r]);
+    cudaError_t e = cudaMalloc(&c->ctx.epoch, sizeof(uint32_t) * kMaxCommCtas);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    cudaMemset(c->ctx.epoch, 0, sizeof(uint32_t) * kMaxCommCtas);
+    e = cudaHostAlloc(reinterpret_cast<void**>(&c->err_host), sizeof(uint32_t), cudaHostAllocMapped);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    *c->err_host = 0;
+    void* dptr = nullptr;
+    e = cudaHostGetDevicePointer(&dptr, c->err_host, 0);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    c->ctx.err = static_cast<uint32_t*>(dptr);
+    c->ctx.timeout_ns = static_cast<unsigned long long>(timeout_s * 1e9);
+    cudaGetDevice(&c->device);
+    *out = c;
+    return 0;
+}
+
+extern "C" int dpt_comm_destroy(dpt_comm* c) {
+    if (c == nullptr) return 0;
+    cudaFree(c->ctx.epoch);
+    cudaFreeHost(c->err_host);
+    delete c;
+    return 0;
+}
+
+// 0 = healthy; otherwise bit31 set, bits 24..30 = peer that never arrived, low 24 bits = epoch.
+extern "C" unsigned dpt_comm_error(const dpt_comm* c) { return c ? *c->err_host : 0u; }
+
+static int clamp_ctas(int ctas, long long n4, int world) {
+    if (ctas <= 0) ctas = 32;
+    if (ctas > kMaxCommCtas) ctas = kMaxCommCtas;
+    long long need = (n4 / (world > 0 ? world : 1) + kCommThreads - 1) / kCommThreads;
+    if (need < 1) need = 1;
+    if (ctas > need) ctas = static_cast<int>(need);
+    return ctas;
+}
+
+static void fill_epilogue(Epilogue* ep, int world, float scale, const float* inv_scale,
+                          void* const* found_inf) {
+    memset(ep, 0, sizeof(*ep));
+    ep->scale = scale;
+    ep->inv_scale = inv_scale;
+    if (found_inf != nullptr)
+        for (int r = 0; r < world; ++r) ep->found_inf[r] = static_cast<float*>(found_inf[r]);
+}
+
+template <int W>
+static void launch_twoshot(const dpt_comm* c, const Peers& g, long long n4, const Epilogue& ep,
+                           int ctas, cudaStream_t st) {
+    allreduce_twoshot_kernel<W><<<ctas, kCommThreads, 0, st>>>(c->ctx, g, n4, ep);
+}
+template <int W>
+static void launch_oneshot(const dpt_comm* c, const Peers& g, float* out, long long n4,
+                           const Epilogue& ep, int ctas, cudaStream_t st) {
+    allreduce_oneshot_kernel<W><<<ctas, kCommThreads, 0, st>>>(c->ctx, g, out, n4, ep);
+}
+
+// In-place fused all-reduce of n floats (n % 4 == 0, 16-byte aligned) living at bufs[r] on rank r.
+//   algo: 0 auto, 1 one-shot (needs `scratch_out`... see dpt_allreduce_oneshot), 2 two-shot
+//   scale: static multiplier (1/world); inv_scale: optional device scalar; found_inf[r]: optional
+//   sgd: optional fused update (param[r], shadow[r] for every rank; local momentum).
+extern "C" int dpt_allreduce_fused(dpt_comm* c, void* const* bufs, long long n, float scale,
+                                   const float* inv_scale, void* const* found_inf,
+                                   void* const* param, void* const* shadow, float* momentum,
+                                   float lr, float mu, float wd, int nesterov, int ctas,
+                                   void* stream) {
+    if (n % 4 != 0) return DPT_ERR_SHAPE;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int world = c->ctx.world;
+    const long long n4 = n / 4;
+    Epilogue ep;
+    fill_epilogue(&ep, world, scale, inv_scale, found_inf);
+    if (param != nullptr) {
+        ep.fused_sgd = 1;
+        for (int r = 0; r < world; ++r) {
+            ep.param[r] = static_cast<float*>(param[r]);
+            ep.shadow[r] = static_cast<__nv_bfloat16*>(shadow[r]);
+        }
+        ep.momentum = momentum;
+        ep.lr = lr;
+        ep.mu = mu;
+        ep.wd = wd;
+        ep.nesterov = nesterov;
+    }
+    if (world == 1) {
+        if (ep.fused_sgd) return DPT_ERR_ARG;  // single GPU: use dpt_sgd_flat (same math)
+        long long b = (n4 + 255) / 256;
+        if (b > 148 * 4) b = 148 * 4;
+        if (b < 1) b = 1;
+        local_epilogue_kernel<<<static_cast<int>(b), 256, 0, st>>>(static_cast<float*>(bufs[0]), n4,
+                                                                   ep);
+        return static_cast<int>(cudaGetLastError());
+    }
+    Peers g;
+    memset(&g, 0, sizeof(g));
+    for (int r = 0; r < world; ++r) g.p[r] = bufs[r];
+    ctas = clamp_ctas(ctas, n4, world);
+    switch (world) {
+        case 2: launch_twoshot<2>(c, g, n4, ep, ctas, st); break;
+        case 3: launch_twoshot<3>(c, g, n4, ep, ctas, st); break;
+        case 4: launch_twoshot<4>(c, g, n4, ep, ctas, st); break;
+        case 5: launch_twoshot<5>(c, g, n4, ep, ctas, st); break;
+        case 6: launch_twoshot<6>(c, g, n4, ep, ctas, st); break;
+        case 7: launch_twoshot<7>(c, g, n4, ep, ctas, st); break;
+        case 8: launch_twoshot<8>(c, g, n4, ep, ctas, st); break;
+        default: return DPT_ERR_ARG;
+    }
+    return static_cast<int>(cudaGetLastError());
+}
+
+// One-shot variant: out (local, n floats) = scale * sum_r in[r].  `in` buffers may be reused by
+// their owners as soon as the call completes on every rank.
+extern "C" int dpt_allreduce_oneshot(dpt_comm* c, void* const* in, float* out, long long n,
+                                     float scale, const float* inv_scale, void* const* found_inf,
+                                     int ctas, void* stream) {
+    if (n % 4 != 0) return DPT_ERR_SHAPE;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int world = c->ctx.world;
+    const long long n4 = n / 4;
+    Epilogue ep;
+    fill_epilogue(&ep, world, scale, inv_scale, found_inf);
+    Peers g;
+    memset(&g, 0, sizeof(g));
+    for (int r = 0; r < world; ++r) g.p[r] = in[r];
+    ctas = clamp_ctas(ctas, n4 * world, world);
+    switch (world) {
+        case 1: launch_oneshot<1>(c, g, out, n4, ep, ctas, st); break;
+        case 2: launch_oneshot<2>(c, g, out, n4, ep, ctas, st); break;
+        case 3: launch_oneshot<3>(c, g, out, n4, ep, ctas, st); break;
+        case 4: launch_oneshot<4>(c, g, out, n4, ep, ctas, st); break;
+        case 5: launch_oneshot<5>(c, g, out, n4, ep, ctas, st); break;
+        case 6: launch_oneshot<6>(c, g, out, n4, ep, ctas, st); break;
+        case 7: launch_oneshot<7>(c, g, out, n4, ep, ctas, st); break;
+        case 8: launch_oneshot<8>(c, g, out, n4, ep, ctas, st); break;
+        default: return DPT_ERR_ARG;
+    }
+    return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int dpt_broadcast(dpt_comm* c, void* const* bufs, long long bytes, int src, int ctas,
+                             void* stream) {
+    if (bytes % 16 != 0) return DPT_ERR_SHAPE;
+    const int world = c->ctx.world;
+    if (world == 1) return 0;
+    Peers g;
+    memset(&g, 0, sizeof(g));
+    for (int r = 0; r < world; ++r) g.p[r] = bufs[r];
+    ctas = clamp_ctas(ctas, bytes / 16, 1);
+    broadcast_kernel<<<ctas, kCommThreads, 0, static_cast<cudaStream_t>(stream)>>>(c->ctx, g,
+                                                                                   bytes / 16, src);
+    return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int dpt_barrier(dpt_comm* c, void* stream) {
+    if (c->ctx.world == 1) return 0;
+    barrier_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(c->ctx);
+    return static_cast<int>(cudaGetLastError());
+}

@@ -1,0 +1,854 @@
+// Implicit-GEMM convolution + plain GEMM on the 5th-gen tensor cores (sm_100a).
+//
+// One warp-specialised kernel template covers the three GEMM-shaped passes of a
+// convolution (and the equivalent plain GEMMs of a linear layer):
+//
+//   MODE_FPROP  Y[m, co]  = sum_{tap, ci} X[m @ tap, ci] * W[co, tap, ci]
+//               A = activations, K-major, fetched by 4-D TMA boxes straight out of the NHWC
+//               tensor (one box per filter tap; TMA zero-fills the padding halo);
+//               B = weights [Cout][R*S*Cin], K-major, 2-D TMA.
+//   MODE_DGRAD  dX[m, ci] = sum_{tap, co} dY[m @ tap, co] * W[co, tap, ci]
+//               A = dY, K-major 4-D TMA; B = the *same* weight tensor read as an N-major
+//               operand (no transposed weight copy exists anywhere).
+//               Stride-2 convs are decomposed into 4 output-parity classes (blockIdx.z) so
+//               no multiply-by-zero work is done; a second conv (the 1x1 downsample that
+//               shares the block input) can be accumulated in the same TMEM tile.
+//   MODE_WGRAD  dW[co, tap, ci] = sum_m dY[m, co] * X[m @ tap, ci]
+//               both operands MN-major (the reduction runs over pixels), split over pixel
+//               tiles across CTAs, reduced with vector fp32 RED straight into the gradient
+//               arena slot (no partial buffers, no copy-in for the reducer).
+//
+// Pipeline: warp 0 = TMA producer, warp 1 = tcgen05.mma issuer (one elected lane) and TMEM
+// owner, warps 2..5 = epilogue (tcgen05.ld -> registers -> global), ring of NSTAGES smem
+// stages guarded by full/empty mbarriers; accumulator tile 128 x BLOCK_N fp32 in TMEM.
+//
+// Replaces, on the reference's path, cuDNN convolution fwd/bwd and the cuBLAS fc GEMMs that
+// torchvision's resnet18 dispatches to (reference train_ddp.py:153-156, 205-213).
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+
+#include "../common/ptx.cuh"
+#include "../../include/dptb200.h"
+
+namespace dpt {
+
+constexpr int MODE_FPROP = 0;
+constexpr int MODE_DGRAD = 1;
+constexpr int MODE_WGRAD = 2;
+
+constexpr int OUT_BF16 = 0;
+constexpr int OUT_F32 = 1;
+constexpr int OUT_F32_ATOMIC = 2;
+
+constexpr int kTileM = 128;
+constexpr int kKBlk = 64;
+constexpr int kMaxTaps = 52;
+constexpr int kNumThreads = 192;
+constexpr int kAStageBytes = kTileM * kKBlk * 2;  // 16 KiB in either major-ness
+
+struct IgemmTap {
+    int8_t a_map, b_map;
+    int16_t dw, dh;
+    int16_t pad_;
+    int32_t koff;  // column offset of this tap inside the weight matrix
+};
+
+struct IgemmMaps {
+    CUtensorMap a[4];
+    CUtensorMap b[4];
+};
+
+struct IgemmParams {
+    int bq, bp, bn;                 // rows of a tile enumerate (n, p, q) inside this box
+    int tiles_q, tiles_p, tiles_n;  // tile grid over the row space
+    int Q, P, NB;                   // row-space extents (for masking)
+    int chunks;                     // 64-wide k chunks per tap (fprop/dgrad)
+    int splits;                     // k splits (fprop/dgrad) or pixel-tile splits (wgrad)
+    int nclasses;                   // 1, or 4 for the stride-2 dgrad parity decomposition
+    int cls_begin[5];               // tap range per class
+    int n_total;                    // valid output columns
+    int m_total;                    // wgrad: valid output rows (Cout)
+    int ntile_per_tap;              // wgrad: N tiles per tap
+    // output addressing
+    void* out;
+    int out_mode;
+    long long ldo;
+    int OH, OW, osh, osw;
+    float* stat_sum;
+    float* stat_sq;
+    const float* bias;
+    IgemmTap taps[kMaxTaps];
+};
+
+template <int W>
+__device__ __forceinline__ void xpose_reduce_step(float (&v)[16], uint32_t lane, uint32_t bit) {
+    const bool upper = (lane & bit) != 0;
+#pragma unroll
+    for (int i = 0; i < W / 2; ++i) {
+        float send = upper ? v[i] : v[i + W / 2];
+        float keep = upper ? v[i + W / 2] : v[i];
+        v[i] = keep + __shfl_xor_sync(0xffffffffu, send, bit);
+    }
+}
+// Sum 16 per-lane values over the 32 lanes; afterwards v[0] on lane l holds the total of
+// column ((l>>4)&1)*8 + ((l>>3)&1)*4 + ((l>>2)&1)*2 + ((l>>1)&1) (duplicated on l and l^1).
+__device__ __forceinline__ float warp_colsum16(float (&v)[16], uint32_t lane) {
+    xpose_reduce_step<16>(v, lane, 16);
+    xpose_reduce_step<8>(v, lane, 8);
+    xpose_reduce_step<4>(v, lane, 4);
+    xpose_reduce_step<2>(v, lane, 2);
+    return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 1);
+}
+
+template <int MODE, int BLOCK_N, int NSTAGES>
+__global__ void __launch_bounds__(kNumThreads, 1)
+igemm_kernel(const __grid_constant__ IgemmMaps maps, const __grid_constant__ IgemmParams prm) {
+    constexpr bool A_MN = (MODE == MODE_WGRAD);
+    constexpr bool B_MN = (MODE != MODE_FPROP);
+    constexpr int kBStageBytes = BLOCK_N * kKBlk * 2;
+    constexpr int kStageBytes = kAStageBytes + kBStageBytes;
+    constexpr uint32_t kTmemCols = BLOCK_N < 32 ? 32 : BLOCK_N;
+    constexpr uint32_t kIdesc = make_idesc_bf16(kTileM, BLOCK_N, A_MN ? 1 : 0, B_MN ? 1 : 0);
+
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    // SWIZZLE_128B needs 1024-byte aligned stage bases.
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                               ~uintptr_t(1023));
+    __shared__ __align__(8) uint64_t full_bar[NSTAGES];
+    __shared__ __align__(8) uint64_t empty_bar[NSTAGES];
+    __shared__ __align__(8) uint64_t tmem_full_bar;
+    __shared__ uint32_t tmem_base_smem;
+
+    const uint32_t warp = threadIdx.x >> 5;
+    const uint32_t lane = threadIdx.x & 31;
+
+    // ---------------------------------------------------------------- tile coordinates
+    int cls = 0, split = blockIdx.z;
+    if (MODE != MODE_WGRAD && prm.nclasses > 1) {
+        cls = blockIdx.z / prm.splits;
+        split = blockIdx.z % prm.splits;
+    }
+    int n0 = 0, p0 = 0, q0 = 0;  // row-space origin of this tile (fprop/dgrad)
+    int col0;                    // first output column of this tile
+    int tap_w = 0;               // wgrad: the tap this CTA owns
+    int row0_w = 0;              // wgrad: first output row (cout)
+    int k_begin, k_end;
+    if (MODE != MODE_WGRAD) {
+        int t = blockIdx.x;
+        q0 = (t % prm.tiles_q) * prm.bq;
+        t /= prm.tiles_q;
+        p0 = (t % prm.tiles_p) * prm.bp;
+        t /= prm.tiles_p;
+        n0 = t * prm.bn;
+        col0 = blockIdx.y * BLOCK_N;
+        const int ntap = prm.cls_begin[cls + 1] - prm.cls_begin[cls];
+        const int total = ntap * prm.chunks;
+        const int per = (total + prm.splits - 1) / prm.splits;
+        k_begin = split * per;
+        k_end = min(total, k_begin + per);
+    } else {
+        tap_w = blockIdx.x / prm.ntile_per_tap;
+        col0 = (blockIdx.x % prm.ntile_per_tap) * BLOCK_N;
+        row0_w = blockIdx.y * kTileM;
+        const int total = prm.tiles_q * prm.tiles_p * prm.tiles_n;
+        const int per = (total + prm.splits - 1) / prm.splits;
+        k_begin = split * per;
+        k_end = min(total, k_begin + per);
+    }
+    const int nk = max(0, k_end - k_begin);
+
+    // ---------------------------------------------------------------- one-time setup
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&maps.a[0]);
+        tma_prefetch_desc(&maps.b[0]);
+        for (int s = 0; s < NSTAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        mbar_init(&tmem_full_bar, 1);
+        fence_mbar_init();
+    }
+    if (warp == 1) {
+        tmem_alloc(&tmem_base_smem, kTmemCols);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_base_smem;
+
+    if (warp == 0) {
+        // ============================================================ TMA producer
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int k = k_begin; k < k_end; ++k) {
+                mbar_wait(&empty_bar[stage], phase ^ 1);
+                uint8_t* sa = smem + stage * kStageBytes;
+                uint8_t* sb = sa + kAStageBytes;
+                mbar_expect_tx(&full_bar[stage], kStageBytes);
+                if (MODE == MODE_FPROP) {
+                    const int ti = prm.cls_begin[cls] + k / prm.chunks;
+                    const int j = k % prm.chunks;
+                    const IgemmTap tp = prm.taps[ti];
+                    tma_load_4d(sa, &maps.a[tp.a_map], &full_bar[stage], j * kKBlk, q0 + tp.dw,
+                                p0 + tp.dh, n0);
+                    tma_load_2d(sb, &maps.b[tp.b_map], &full_bar[stage], tp.koff + j * kKBlk, col0);
+                } else if (MODE == MODE_DGRAD) {
+                    const int ti = prm.cls_begin[cls] + k / prm.chunks;
+                    const int j = k % prm.chunks;
+                    const IgemmTap tp = prm.taps[ti];
+                    tma_load_4d(sa, &maps.a[tp.a_map], &full_bar[stage], j * kKBlk, q0 + tp.dw,
+                                p0 + tp.dh, n0);
+#pragma unroll
+                    for (int nb = 0; nb < BLOCK_N / 64; ++nb)
+                        tma_load_2d(sb + nb * 8192, &maps.b[tp.b_map], &full_bar[stage],
+                                    tp.koff + col0 + nb * 64, j * kKBlk);
+                } else {
+                    int t = k;
+                    const int wq = (t % prm.tiles_q) * prm.bq;
+                    t /= prm.tiles_q;
+                    const int wp = (t % prm.tiles_p) * prm.bp;
+                    t /= prm.tiles_p;
+                    const int wn = t * prm.bn;
+                    const IgemmTap tp = prm.taps[tap_w];
+#pragma unroll
+                    for (int mb = 0; mb < kTileM / 64; ++mb)
+                        tma_load_4d(sa + mb * 8192, &maps.a[0], &full_bar[stage], row0_w + mb * 64,
+                                    wq, wp, wn);
+#pragma unroll
+                    for (int nb = 0; nb < BLOCK_N / 64; ++nb)
+                        tma_load_4d(sb + nb * 8192, &maps.b[tp.b_map], &full_bar[stage],
+                                    col0 + nb * 64, wq + tp.dw, wp + tp.dh, wn);
+                }
+                if (++stage == NSTAGES) {
+                    stage = 0;
+                    phase ^= 1;
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ============================================================ MMA issuer
+        if (lane == 0 && nk > 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int k = 0; k < nk; ++k) {
+                mbar_wait(&full_bar[stage], phase);
+                tc_fence_after();
+                const uint32_t sa = smem_u32(smem + stage * kStageBytes);
+                const uint32_t sb = sa + kAStageBytes;
+#pragma unroll
+                for (int kk = 0; kk < kKBlk / 16; ++kk) {
+                    // K-major: 16 bf16 = 32 B further inside the 128 B swizzle row.
+                    // MN-major: 16 k-rows = 2048 B further; LBO = next 64-wide MN block.
+                    const uint64_t da = A_MN ? make_smem_desc_sw128(sa + kk * 2048, 8192, 1024)
+                                             : make_smem_desc_sw128(sa + kk * 32, 16, 1024);
+                    const uint64_t db = B_MN ? make_smem_desc_sw128(sb + kk * 2048, 8192, 1024)
+                                             : make_smem_desc_sw128(sb + kk * 32, 16, 1024);
+                    umma_f16(tmem_base, da, db, kIdesc, (k | kk) != 0 ? 1u : 0u);
+                }
+                umma_commit(&empty_bar[stage]);  // frees the smem slot when the MMAs retire
+                if (++stage == NSTAGES) {
+                    stage = 0;
+                    phase ^= 1;
+                }
+            }
+            umma_commit(&tmem_full_bar);
+        }
+    } else {
+        // ============================================================ epilogue (4 warps)
+        const uint32_t sub = warp & 3;  // TMEM sub-partition this warp may read
+        const int r = sub * 32 + lane;  // accumulator row
+        if (nk > 0) {
+            mbar_wait(&tmem_full_bar, 0);
+            tc_fence_after();
+        }
+        bool row_ok;
+        long long row_off;
+        int koff_out = 0;
+        if (MODE != MODE_WGRAD) {
+            const int q = q0 + r % prm.bq;
+            const int p = p0 + (r / prm.bq) % prm.bp;
+            const int n = n0 + r / (prm.bq * prm.bp);
+            row_ok = (q < prm.Q) && (p < prm.P) && (n < prm.NB);
+            const int oh0 = (prm.nclasses > 1) ? (cls >> 1) : 0;
+            const int ow0 = (prm.nclasses > 1) ? (cls & 1) : 0;
+            row_off = ((static_cast<long long>(n) * prm.OH + (p * prm.osh + oh0)) * prm.OW +
+                       (q * prm.osw + ow0)) *
+                      prm.ldo;
+        } else {
+            const int row = row0_w + r;
+            row_ok = row < prm.m_total;
+            row_off = static_cast<long long>(row) * prm.ldo;
+            koff_out = prm.taps[tap_w].koff;
+        }
+        const bool vec_ok = (prm.ldo % 8) == 0 && (koff_out % 8) == 0;
+#pragma unroll 1
+        for (int c = 0; c < BLOCK_N / 16; ++c) {
+            float f[16];
+            if (nk > 0) {
+                uint32_t v[16];
+                tmem_ld16(tmem_base + ((sub * 32u) << 16) + c * 16, v);
+                tmem_ld_wait();
+#pragma unroll
+                for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
+            } else {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) f[i] = 0.f;
+            }
+            const int cbase = col0 + c * 16;
+            if (cbase >= prm.n_total) break;  // warp-uniform
+            if (prm.bias != nullptr) {
+#pragma unroll
+                for (int i = 0; i < 16; ++i)
+                    if (cbase + i < prm.n_total) f[i] += __ldg(prm.bias + cbase + i);
+            }
+            const bool full = (cbase + 16 <= prm.n_total);
+            if (row_ok) {
+                const long long off = row_off + koff_out + cbase;
+                if (prm.out_mode == OUT_BF16) {
+                    __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(prm.out) + off;
+                    if (full && vec_ok) {
+                        uint32_t pk[8];
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            __nv_bfloat162 h = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+                            pk[i] = *reinterpret_cast<uint32_t*>(&h);
+                        }
+                        uint4* o4 = reinterpret_cast<uint4*>(o);
+                        o4[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                        o4[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i)
+                            if (cbase + i < prm.n_total) o[i] = __float2bfloat16_rn(f[i]);
+                    }
+                } else if (prm.out_mode == OUT_F32) {
+                    float* o = reinterpret_cast<float*>(prm.out) + off;
+                    if (full && vec_ok) {
+                        float4* o4 = reinterpret_cast<float4*>(o);
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            o4[i] = make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i)
+                            if (cbase + i < prm.n_total) o[i] = f[i];
+                    }
+                } else {
+                    float* o = reinterpret_cast<float*>(prm.out) + off;
+                    if (full && vec_ok) {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            red_add_f32x4(o + 4 * i, f[4 * i], f[4 * i + 1], f[4 * i + 2],
+                                          f[4 * i + 3]);
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i)
+                            if (cbase + i < prm.n_total) atomicAdd(o + i, f[i]);
+                    }
+                }
+            }
+            if (MODE == MODE_FPROP && prm.stat_sum != nullptr) {
+                // Per-channel sum / sum-of-squares of this tile for the following BatchNorm
+                // (statistics come from the fp32 accumulators, before bf16 rounding).
+                float s1[16], s2[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    const float x = row_ok ? f[i] : 0.f;
+                    s1[i] = x;
+                    s2[i] = x * x;
+                }
+                const float t1 = warp_colsum16(s1, lane);
+                const float t2 = warp_colsum16(s2, lane);
+                const int colsel = ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 +
+                                   ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
+                if ((lane & 1) == 0 && cbase + colsel < prm.n_total) {
+                    atomicAdd(prm.stat_sum + cbase + colsel, t1);
+                    atomicAdd(prm.stat_sq + cbase + colsel, t2);
+                }
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem_base, kTmemCols);
+}
+
+// ================================================================================ host side
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                    const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                    const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled get_encode() {
+    static PFN_encodeTiled fn = nullptr;
+    if (fn == nullptr) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) ==
+                cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<PFN_encodeTiled>(p);
+    }
+    return fn;
+}
+
+// bf16 tensor map, up to 4-D, inner box = 64 elements (128 B) with SWIZZLE_128B.
+// dims/strides are in elements; strides[i] is the stride of dimension i+1.
+static int make_tmap(CUtensorMap* m, const void* base, int rank, const long long* dims,
+                     const long long* strides, const int* box) {
+    PFN_encodeTiled enc = get_encode();
+    if (enc == nullptr) return DPT_ERR_DRIVER;
+    cuuint64_t gdim[4];
+    cuuint64_t gstr[3];
+    cuuint32_t bdim[4];
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    for (int i = 0; i < rank; ++i) {
+        gdim[i] = static_cast<cuuint64_t>(dims[i] > 0 ? dims[i] : 1);
+        bdim[i] = static_cast<cuuint32_t>(box[i]);
+    }
+    for (int i = 0; i + 1 < rank; ++i) gstr[i] = static_cast<cuuint64_t>(strides[i]) * 2;
+    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(base), gdim, gstr,
+                     bdim, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        fprintf(stderr,
+                "[dptb200] cuTensorMapEncodeTiled failed (%d): rank %d base %p dims %lld %lld %lld "
+                "%lld strides %lld %lld %lld box %d %d %d %d\n",
+                int(r), rank, base, dims[0], rank > 1 ? dims[1] : 0, rank > 2 ? dims[2] : 0,
+                rank > 3 ? dims[3] : 0, strides[0], rank > 2 ? strides[1] : 0,
+                rank > 3 ? strides[2] : 0, box[0], rank > 1 ? box[1] : 0, rank > 2 ? box[2] : 0,
+                rank > 3 ? box[3] : 0);
+        return DPT_ERR_TMAP;
+    }
+    return 0;
+}
+
+static int pow2_ceil(int v) {
+    int p = 1;
+    while (p < v) p <<= 1;
+    return p;
+}
+
+// Choose (bq, bp, bn) with bq*bp*bn == rows covering a (Q, P, N) row space.
+static void pick_box(int rows, int Q, int P, int N, int* bq, int* bp, int* bn) {
+    int q = pow2_ceil(Q);
+    if (q > rows) q = rows;
+    int p = pow2_ceil(P);
+    if (p > rows / q) p = rows / q;
+    int n = rows / (q * p);
+    (void)N;
+    *bq = q;
+    *bp = p;
+    *bn = n;
+}
+
+template <int MODE, int BLOCK_N>
+static int launch_cfg(const IgemmMaps& maps, const IgemmParams& prm, dim3 grid, cudaStream_t st) {
+    constexpr int kBStageBytes = BLOCK_N * kKBlk * 2;
+    constexpr int NST = (BLOCK_N == 128) ? 6 : 8;
+    const int smem = NST * (kAStageBytes + kBStageBytes) + 1024;
+    auto kern = igemm_kernel<MODE, BLOCK_N, NST>;
+    static bool attr_done = false;
+    if (!attr_done) {
+        cudaError_t e =
+            cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e != cudaSuccess) return int(e);
+        attr_done = true;
+    }
+    kern<<<grid, kNumThreads, smem, st>>>(maps, prm);
+    return int(cudaGetLastError());
+}
+
+template <int MODE>
+static int launch(const IgemmMaps& maps, const IgemmParams& prm, dim3 grid, int block_n,
+                  cudaStream_t st) {
+    if (block_n == 128) return launch_cfg<MODE, 128>(maps, prm, grid, st);
+    return launch_cfg<MODE, 64>(maps, prm, grid, st);
+}
+
+// A-side activation maps for a conv whose taps read X[n, p*stride + r - pad, q*stride + s - pad].
+// For stride 2 one strided "parity view" map per (h parity, w parity) is built so that every
+// tap is a unit-stride box in its view.  Returns taps (map index + box offsets) for all (r, s)
+// whose receptive row/column range intersects the tensor at all.
+struct TapBuilder {
+    IgemmTap taps[kMaxTaps];
+    int ntaps = 0;
+};
+
+static int build_act_maps(CUtensorMap* maps4, const void* x, int N, int H, int W, int C, int stride,
+                          int rows, int bq, int bp, int bn) {
+    (void)rows;
+    const int box[4] = {64, bq, bp, bn};
+    if (stride == 1) {
+        const long long dims[4] = {C, W, H, N};
+        const long long str[3] = {C, (long long)W * C, (long long)H * W * C};
+        int e = make_tmap(&maps4[0], x, 4, dims, str, box);
+        if (e) return e;
+        for (int i = 1; i < 4; ++i) maps4[i] = maps4[0];
+        return 0;
+    }
+    for (int ph = 0; ph < 2; ++ph)
+        for (int pw = 0; pw < 2; ++pw) {
+            const __nv_bfloat16* base =
+                reinterpret_cast<const __nv_bfloat16*>(x) + ((long long)ph * W + pw) * C;
+            const long long dims[4] = {C, (W - pw + 1) / 2, (H - ph + 1) / 2, N};
+            const long long str[3] = {2LL * C, 2LL * W * C, (long long)H * W * C};
+            if (dims[1] <= 0 || dims[2] <= 0) {
+                maps4[ph * 2 + pw] = maps4[0];
+                continue;
+            }
+            int e = make_tmap(&maps4[ph * 2 + pw], base, 4, dims, str, box);
+            if (e) return e;
+        }
+    return 0;
+}
+
+// floor division / modulo for possibly negative numerators
+static inline int fdiv(int a, int b) { return (a >= 0) ? a / b : -((-a + b - 1) / b); }
+static inline int fmod_pos(int a, int b) { return a - fdiv(a, b) * b; }
+
+static void fprop_taps(TapBuilder* tb, int H, int W, int P, int Q, int Cin, int R, int S, int stride,
+                       int pad, int b_map) {
+    for (int r = 0; r < R; ++r)
+        for (int s = 0; s < S; ++s) {
+            // skip taps that only ever see padding
+            const int hmin = r - pad, hmax = (P - 1) * stride + r - pad;
+            const int wmin = s - pad, wmax = (Q - 1) * stride + s - pad;
+            if (hmax < 0 || hmin >= H || wmax < 0 || wmin >= W) continue;
+            IgemmTap t{};
+            const int dh = r - pad, dw = s - pad;
+            if (stride == 1) {
+                t.a_map = 0;
+                t.dh = dh;
+                t.dw = dw;
+            } else {
+                const int ph = fmod_pos(dh, stride), pw = fmod_pos(dw, stride);
+                t.a_map = ph * 2 + pw;
+                t.dh = fdiv(dh, stride);
+                t.dw = fdiv(dw, stride);
+            }
+            t.b_map = b_map;
+            t.koff = (r * S + s) * Cin;
+            tb->taps[tb->ntaps++] = t;
+        }
+}
+
+}  // namespace dpt
+
+using namespace dpt;
+
+extern "C" int dpt_conv_fprop(const void* x, const void* w, void* y, int N, int H, int W, int Cin,
+                              int Cout, int R, int S, int stride, int pad, float* stat_sum,
+                              float* stat_sq, int out_f32_atomic, int splits, void* stream) {
+    if (Cin % 8 != 0 || (stride != 1 && stride != 2) || R * S > kMaxTaps) return DPT_ERR_SHAPE;
+    const int P = (H + 2 * pad - R) / stride + 1, Q = (W + 2 * pad - S) / stride + 1;
+    IgemmMaps maps;
+    IgemmParams prm;
+    memset(&prm, 0, sizeof(prm));
+    pick_box(kTileM, Q, P, N, &prm.bq, &prm.bp, &prm.bn);
+    int e = build_act_maps(maps.a, x, N, H, W, Cin, stride, kTileM, prm.bq, prm.bp, prm.bn);
+    if (e) return e;
+    const int block_n = (Cout >= 128) ? 128 : 64;
+    {
+        const long long dims[2] = {(long long)R * S * Cin, Cout};
+        const long long str[1] = {(long long)R * S * Cin};
+        const int box[2] = {64, block_n};
+        e = make_tmap(&maps.b[0], w, 2, dims, str, box);
+        if (e) return e;
+        for (int i = 1; i < 4; ++i) maps.b[i] = maps.b[0];
+    }
+    TapBuilder tb;
+    fprop_taps(&tb, H, W, P, Q, Cin, R, S, stride, pad, 0);
+    if (tb.ntaps == 0) return DPT_ERR_SHAPE;
+    memcpy(prm.taps, tb.taps, sizeof(IgemmTap) * tb.ntaps);
+    prm.tiles_q = (Q + prm.bq - 1) / prm.bq;
+    prm.tiles_p = (P + prm.bp - 1) / prm.bp;
+    prm.tiles_n = (N + prm.bn - 1) / prm.bn;
+    prm.Q = Q;
+    prm.P = P;
+    prm.NB = N;
+    prm.chunks = (Cin + 63) / 64;
+    const int ksteps = tb.ntaps * prm.chunks;
+    if (splits < 1) splits = 1;
+    if (splits > ksteps) splits = ksteps;
+    if (!out_f32_atomic) splits = 1;
+    // make sure no split is empty
+    {
+        int per = (ksteps + splits - 1) / splits;
+        splits = (ksteps + per - 1) / per;
+    }
+    prm.splits = splits;
+    prm.nclasses = 1;
+    prm.cls_begin[0] = 0;
+    prm.cls_begin[1] = tb.ntaps;
+    prm.n_total = Cout;
+    prm.out = y;
+    prm.out_mode = out_f32_atomic ? OUT_F32_ATOMIC : OUT_BF16;
+    prm.ldo = Cout;
+    prm.OH = P;
+    prm.OW = Q;
+    prm.osh = 1;
+    prm.osw = 1;
+    prm.stat_sum = out_f32_atomic ? nullptr : stat_sum;
+    prm.stat_sq = out_f32_atomic ? nullptr : stat_sq;
+    dim3 grid(prm.tiles_q * prm.tiles_p * prm.tiles_n, (Cout + block_n - 1) / block_n, splits);
+    return launch<MODE_FPROP>(maps, prm, grid, block_n, static_cast<cudaStream_t>(stream));
+}
+
+// dX = conv_dgrad(dY, W) [+ conv_dgrad(dY2, W2) for a second conv reading the same input].
+extern "C" int dpt_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin,
+                              int Cout, int R, int S, int stride, int pad, const void* dy2,
+                              const void* w2, int R2, int S2, int pad2, void* stream) {
+    if (Cin % 8 != 0 || Cout % 8 != 0 || (stride != 1 && stride != 2)) return DPT_ERR_SHAPE;
+    const int P = (H + 2 * pad - R) / stride + 1, Q = (W + 2 * pad - S) / stride + 1;
+    IgemmMaps maps;
+    IgemmParams prm;
+    memset(&prm, 0, sizeof(prm));
+    // Row space: dX pixels of one parity class (all pixels for stride 1).
+    const int HC = (H + stride - 1) / stride, WC = (W + stride - 1) / stride;
+    pick_box(kTileM, WC, HC, N, &prm.bq, &prm.bp, &prm.bn);
+    const int box[4] = {64, prm.bq, prm.bp, prm.bn};
+    {
+        const long long dims[4] = {Cout, Q, P, N};
+        const long long str[3] = {Cout, (long long)Q * Cout, (long long)P * Q * Cout};
+        int e = make_tmap(&maps.a[0], dy, 4, dims, str, box);
+        if (e) return e;
+        maps.a[1] = maps.a[0];
+        if (dy2 != nullptr) {
+            const int P2 = (H + 2 * pad2 - R2) / stride + 1, Q2 = (W + 2 * pad2 - S2) / stride + 1;
+            if (P2 != P || Q2 != Q) return DPT_ERR_SHAPE;
+            e = make_tmap(&maps.a[1], dy2, 4, dims, str, box);
+            if (e) return e;
+        }
+        maps.a[2] = maps.a[3] = maps.a[0];
+    }
+    const int block_n = (Cin >= 128) ? 128 : 64;
+    {
+        const long long dims[2] = {(long long)R * S * Cin, Cout};
+        const long long str[1] = {(long long)R * S * Cin};
+        const int bbox[2] = {64, 64};
+        int e = make_tmap(&maps.b[0], w, 2, dims, str, bbox);
+        if (e) return e;
+        maps.b[1] = maps.b[0];
+        if (dy2 != nullptr) {
+            const long long dims2[2] = {(long long)R2 * S2 * Cin, Cout};
+            const long long str2[1] = {(long long)R2 * S2 * Cin};
+            e = make_tmap(&maps.b[1], w2, 2, dims2, str2, bbox);
+            if (e) return e;
+        }
+        maps.b[2] = maps.b[3] = maps.b[0];
+    }
+    // taps per parity class: dX[h] gets dY[(h + pad - r)/stride] * W[r] when divisible
+    const int ncls = (stride == 1) ? 1 : 4;
+    int nt = 0;
+    for (int c = 0; c < ncls; ++c) {
+        prm.cls_begin[c] = nt;
+        const int hp = (stride == 1) ? 0 : (c >> 1), wp = (stride == 1) ? 0 : (c & 1);
+        for (int which = 0; which < (dy2 ? 2 : 1); ++which) {
+            const int RR = which ? R2 : R, SS = which ? S2 : S, PD = which ? pad2 : pad;
+            for (int r = 0; r < RR; ++r)
+                for (int s = 0; s < SS; ++s) {
+                    if (fmod_pos(hp + PD - r, stride) != 0 || fmod_pos(wp + PD - s, stride) != 0)
+                        continue;
+                    const int dh = fdiv(hp + PD - r, stride), dw = fdiv(wp + PD - s, stride);
+                    // range of dY rows touched: i + dh for i in [0, HC)
+                    if (dh + HC - 1 < 0 || dh >= P || dw + WC - 1 < 0 || dw >= Q) continue;
+                    if (nt >= kMaxTaps) return DPT_ERR_SHAPE;
+                    IgemmTap t{};
+                    t.a_map = which;
+                    t.b_map = which;
+                    t.dh = dh;
+                    t.dw = dw;
+                    t.koff = (r * SS + s) * Cin;
+                    prm.taps[nt++] = t;
+                }
+        }
+    }
+    for (int c = ncls; c < 5; ++c) prm.cls_begin[c] = nt;
+    prm.tiles_q = (WC + prm.bq - 1) / prm.bq;
+    prm.tiles_p = (HC + prm.bp - 1) / prm.bp;
+    prm.tiles_n = (N + prm.bn - 1) / prm.bn;
+    prm.Q = WC;
+    prm.P = HC;
+    prm.NB = N;
+    // (odd H/W with stride 2: classes hp=1 have one row fewer; mask through OH/OW below)
+    prm.chunks = (Cout + 63) / 64;
+    prm.splits = 1;
+    prm.nclasses = ncls;
+    prm.n_total = Cin;
+    prm.out = dx;
+    prm.out_mode = OUT_BF16;
+    prm.ldo = Cin;
+    prm.OH = H;
+    prm.OW = W;
+    prm.osh = stride;
+    prm.osw = stride;
+    if (stride == 2 && ((H & 1) || (W & 1))) return DPT_ERR_SHAPE;  // TODO: odd sizes
+    dim3 grid(prm.tiles_q * prm.tiles_p * prm.tiles_n, (Cin + block_n - 1) / block_n, ncls);
+    return launch<MODE_DGRAD>(maps, prm, grid, block_n, static_cast<cudaStream_t>(stream));
+}
+
+// dW[Cout][R][S][Cin] (fp32) += dY^T * im2col(X), reduced across pixel-tile splits with RED.
+extern "C" int dpt_conv_wgrad(const void* dy, const void* x, float* dw, int N, int H, int W,
+                              int Cin, int Cout, int R, int S, int stride, int pad, int splits,
+                              void* stream) {
+    if (Cin % 8 != 0 || Cout % 8 != 0 || (stride != 1 && stride != 2)) return DPT_ERR_SHAPE;
+    const int P = (H + 2 * pad - R) / stride + 1, Q = (W + 2 * pad - S) / stride + 1;
+    IgemmMaps maps;
+    IgemmParams prm;
+    memset(&prm, 0, sizeof(prm));
+    pick_box(kKBlk, Q, P, N, &prm.bq, &prm.bp, &prm.bn);
+    const int box[4] = {64, prm.bq, prm.bp, prm.bn};
+    {
+        const long long dims[4] = {Cout, Q, P, N};
+        const long long str[3] = {Cout, (long long)Q * Cout, (long long)P * Q * Cout};
+        int e = make_tmap(&maps.a[0], dy, 4, dims, str, box);
+        if (e) return e;
+        for (int i = 1; i < 4; ++i) maps.a[i] = maps.a[0];
+    }
+    int e = build_act_maps(maps.b, x, N, H, W, Cin, stride, kKBlk, prm.bq, prm.bp, prm.bn);
+    if (e) return e;
+    TapBuilder tb;
+    fprop_taps(&tb, H, W, P, Q, Cin, R, S, stride, pad, 0);
+    if (tb.ntaps == 0) return DPT_ERR_SHAPE;
+    for (int i = 0; i < tb.ntaps; ++i) {
+        tb.taps[i].b_map = tb.taps[i].a_map;  // activation parity view lives on the B side here
+    }
+    memcpy(prm.taps, tb.taps, sizeof(IgemmTap) * tb.ntaps);
+    const int block_n = (Cin >= 128) ? 128 : 64;
+    prm.tiles_q = (Q + prm.bq - 1) / prm.bq;
+    prm.tiles_p = (P + prm.bp - 1) / prm.bp;
+    prm.tiles_n = (N + prm.bn - 1) / prm.bn;
+    const int mtiles = prm.tiles_q * prm.tiles_p * prm.tiles_n;
+    prm.ntile_per_tap = (Cin + block_n - 1) / block_n;
+    const int out_tiles = tb.ntaps * prm.ntile_per_tap * ((Cout + kTileM - 1) / kTileM);
+    if (splits <= 0) {
+        // fill ~2 waves of the 148 SMs, but keep at least 2 pixel tiles per CTA
+        splits = (296 + out_tiles - 1) / out_tiles;
+        if (splits > (mtiles + 1) / 2) splits = (mtiles + 1) / 2;
+    }
+    if (splits < 1) splits = 1;
+    if (splits > mtiles) splits = mtiles;
+    {
+        int per = (mtiles + splits - 1) / splits;
+        splits = (mtiles + per - 1) / per;
+    }
+    prm.splits = splits;
+    prm.nclasses = 1;
+    prm.n_total = Cin;
+    prm.m_total = Cout;
+    prm.out = dw;
+    prm.out_mode = OUT_F32_ATOMIC;
+    prm.ldo = (long long)R * S * Cin;
+    dim3 grid(tb.ntaps * prm.ntile_per_tap, (Cout + kTileM - 1) / kTileM, splits);
+    return launch<MODE_WGRAD>(maps, prm, grid, block_n, static_cast<cudaStream_t>(stream));
+}
+
+// Plain bf16 GEMMs, fp32 accumulate.  Row-major everywhere.
+//   op 0 (NT): C[M,N] = A[M,K] * B[N,K]^T        (linear forward, im2col conv forward)
+//   op 1 (NN): C[M,N] = A[M,K] * B[K,N]          (linear dgrad)
+//   op 2 (TN): C[M,N] = A[K,M]^T * B[K,N]        (linear / im2col wgrad; split over K with RED)
+// out_mode: 0 bf16 store, 1 fp32 store, 2 fp32 atomic accumulate.
+extern "C" int dpt_gemm_bf16(int op, const void* A, const void* B, void* C, int M, int N, int K,
+                             long long lda, long long ldb, long long ldc, int out_mode,
+                             const float* bias, float* stat_sum, float* stat_sq, int splits,
+                             void* stream) {
+    if (lda % 8 != 0 || ldb % 8 != 0 || op < 0 || op > 2) return DPT_ERR_SHAPE;
+    IgemmMaps maps;
+    IgemmParams prm;
+    memset(&prm, 0, sizeof(prm));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int block_n = (N >= 128) ? 128 : 64;
+    prm.nclasses = 1;
+    prm.cls_begin[0] = 0;
+    for (int c = 1; c < 5; ++c) prm.cls_begin[c] = 1;
+    prm.n_total = N;
+    prm.out = C;
+    prm.ldo = ldc;
+    prm.bias = bias;
+    prm.OH = 1;
+    prm.osh = prm.osw = 1;
+    prm.bp = prm.bn = 1;
+    prm.tiles_p = prm.tiles_n = 1;
+    prm.P = prm.NB = 1;
+    if (splits < 1) splits = 1;
+    if (op == 0 || op == 1) {
+        const long long dims[4] = {K, M, 1, 1};
+        const long long str[3] = {lda, lda * M, lda * M};
+        const int box[4] = {64, kTileM, 1, 1};
+        int e = make_tmap(&maps.a[0], A, 4, dims, str, box);
+        if (e) return e;
+        if (op == 0) {
+            const long long bd[2] = {K, N};
+            const long long bs[1] = {ldb};
+            const int bb[2] = {64, block_n};
+            e = make_tmap(&maps.b[0], B, 2, bd, bs, bb);
+        } else {
+            const long long bd[2] = {N, K};
+            const long long bs[1] = {ldb};
+            const int bb[2] = {64, 64};
+            e = make_tmap(&maps.b[0], B, 2, bd, bs, bb);
+        }
+        if (e) return e;
+        for (int i = 1; i < 4; ++i) {
+            maps.a[i] = maps.a[0];
+            maps.b[i] = maps.b[0];
+        }
+        prm.bq = kTileM;
+        prm.tiles_q = (M + kTileM - 1) / kTileM;
+        prm.Q = M;
+        prm.OW = M;
+        prm.chunks = (K + 63) / 64;
+        if (out_mode != OUT_F32_ATOMIC) splits = 1;
+        if (splits > prm.chunks) splits = prm.chunks;
+        {
+            int per = (prm.chunks + splits - 1) / splits;
+            splits = (prm.chunks + per - 1) / per;
+        }
+        prm.splits = splits;
+        prm.out_mode = out_mode;
+        prm.stat_sum = (op == 0 && out_mode != OUT_F32_ATOMIC) ? stat_sum : nullptr;
+        prm.stat_sq = (op == 0 && out_mode != OUT_F32_ATOMIC) ? stat_sq : nullptr;
+        dim3 grid(prm.tiles_q, (N + block_n - 1) / block_n, splits);
+        if (op == 0) return launch<MODE_FPROP>(maps, prm, grid, block_n, st);
+        return launch<MODE_DGRAD>(maps, prm, grid, block_n, st);
+    }
+    // op 2: reduction over the rows of both operands
+    {
+        const long long ad[4] = {M, K, 1, 1};
+        const long long as[3] = {lda, lda * K, lda * K};
+        const long long bd[4] = {N, K, 1, 1};
+        const long long bs[3] = {ldb, ldb * K, ldb * K};
+        const int box[4] = {64, kKBlk, 1, 1};
+        int e = make_tmap(&maps.a[0], A, 4, ad, as, box);
+        if (e) return e;
+        e = make_tmap(&maps.b[0], B, 4, bd, bs, box);
+        if (e) return e;
+        for (int i = 1; i < 4; ++i) {
+            maps.a[i] = maps.a[0];
+            maps.b[i] = maps.b[0];
+        }
+    }
+    prm.bq = kKBlk;
+    prm.tiles_q = (K + kKBlk - 1) / kKBlk;
+    prm.m_total = M;
+    prm.ntile_per_tap = (N + block_n - 1) / block_n;
+    if (out_mode != OUT_F32_ATOMIC) splits = 1;
+    if (splits > prm.tiles_q) splits = prm.tiles_q;
+    {
+        int per = (prm.tiles_q + splits - 1) / splits;
+        splits = (prm.tiles_q + per - 1) / per;
+    }
+    prm.splits = splits;
+    prm.out_mode = out_mode;
+    dim3 grid(prm.ntile_per_tap, (M + kTileM - 1) / kTileM, splits);
+    return launch<MODE_WGRAD>(maps, prm, grid, block_n, st);
+}

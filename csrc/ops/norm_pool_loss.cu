@@ -1,0 +1,710 @@
+// Bandwidth-bound model kernels for sm_100a: BatchNorm (training fwd / bwd with fused ReLU and
+// residual add, eval fold), 3x3/2 max-pool, global-average-pool + linear head, fused
+// cross-entropy (+loss scale, +top-1 count), im2col for the RGB stem.
+//
+// All activations are NHWC bf16 with C % 8 == 0, processed as 16-byte vectors; statistics and
+// parameters are fp32.  These kernels replace cuDNN/ATen batch_norm(+backward), relu_/
+// threshold_backward, add_, max_pool2d_with_indices(+backward), mean.dim, addmm/mm,
+// _log_softmax/nll_loss(+backward) on the reference's path (train_ddp.py:205-207, 211-213 via
+// torchvision resnet._forward_impl).
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "../../include/dptb200.h"
+#include "../common/ptx.cuh"
+
+namespace dpt {
+
+struct alignas(16) bf16x8 {
+    __nv_bfloat162 v[4];
+};
+
+__device__ __forceinline__ void unpack8(const bf16x8& b, float (&f)[8]) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        float2 t = __bfloat1622float2(b.v[i]);
+        f[2 * i] = t.x;
+        f[2 * i + 1] = t.y;
+    }
+}
+__device__ __forceinline__ bf16x8 pack8(const float (&f)[8]) {
+    bf16x8 b;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) b.v[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+    return b;
+}
+
+constexpr int kEwThreads = 256;
+
+static inline int ew_grid(long long nvec, int cvec) {
+    // Threads are bound to a fixed channel group: total thread count must be a multiple of
+    // cvec (= C/8).  256 % cvec == 0 is checked by the callers.
+    (void)cvec;
+    long long blocks = (nvec + kEwThreads - 1) / kEwThreads;
+    const long long cap = 148LL * 8;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    return static_cast<int>(blocks);
+}
+
+// ------------------------------------------------------------------------------------ BN stats
+// sum[c] += sum_m x[m,c]; sq[c] += sum_m x[m,c]^2   (buffers zeroed by the caller)
+__global__ void __launch_bounds__(kEwThreads) bn_stats_kernel(const bf16x8* __restrict__ x,
+                                                              float* __restrict__ sum,
+                                                              float* __restrict__ sq, long long nvec,
+                                                              int cvec) {
+    __shared__ float sh[2][kEwThreads][8 + 1];
+    const long long stride = static_cast<long long>(gridDim.x) * kEwThreads;
+    long long i = static_cast<long long>(blockIdx.x) * kEwThreads + threadIdx.x;
+    float s1[8] = {0, 0, 0, 0, 0, 0, 0, 0}, s2[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (; i < nvec; i += stride) {
+        float f[8];
+        unpack8(x[i], f);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            s1[k] += f[k];
+            s2[k] += f[k] * f[k];
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        sh[0][threadIdx.x][k] = s1[k];
+        sh[1][threadIdx.x][k] = s2[k];
+    }
+    __syncthreads();
+    // threads t, t+cvec, t+2cvec ... share a channel group
+    if (threadIdx.x < cvec) {
+        for (int t = threadIdx.x + cvec; t < kEwThreads; t += cvec) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                s1[k] += sh[0][t][k];
+                s2[k] += sh[1][t][k];
+            }
+        }
+        const int cg = static_cast<int>((static_cast<long long>(blockIdx.x) * kEwThreads + threadIdx.x) % cvec);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            atomicAdd(sum + cg * 8 + k, s1[k]);
+            atomicAdd(sq + cg * 8 + k, s2[k]);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------ BN fwd
+// y = relu?( (x - mean) * invstd * gamma + beta (+ residual) ), batch statistics from sum/sq.
+// Block 0 also writes save_mean / save_invstd and updates the running statistics.
+__global__ void __launch_bounds__(kEwThreads)
+bn_fwd_kernel(const bf16x8* __restrict__ x, const float* __restrict__ sum,
+              const float* __restrict__ sq, const float* __restrict__ gamma,
+              const float* __restrict__ beta, const bf16x8* __restrict__ residual,
+              bf16x8* __restrict__ y, float* __restrict__ save_mean,
+              float* __restrict__ save_invstd, float* __restrict__ running_mean,
+              float* __restrict__ running_var, long long* __restrict__ num_batches_tracked,
+              long long nvec, int cvec, float inv_m, float unbias, float momentum, float eps,
+              int relu) {
+    const long long stride = static_cast<long long>(gridDim.x) * kEwThreads;
+    long long i = static_cast<long long>(blockIdx.x) * kEwThreads + threadIdx.x;
+    const int cg = static_cast<int>(i % cvec);
+    float sc[8], sf[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const int c = cg * 8 + k;
+        const float mean = sum[c] * inv_m;
+        const float var = fmaxf(sq[c] * inv_m - mean * mean, 0.f);
+        const float invstd = rsqrtf(var + eps);
+        sc[k] = gamma[c] * invstd;
+        sf[k] = beta[c] - mean * sc[k];
+        if (blockIdx.x == 0 && threadIdx.x < cvec) {
+            save_mean[c] = mean;
+            save_invstd[c] = invstd;
+            if (running_mean != nullptr) {
+                running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+                running_var[c] = (1.f - momentum) * running_var[c] + momentum * var * unbias;
+            }
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0 && num_batches_tracked != nullptr)
+        *num_batches_tracked += 1;
+    for (; i < nvec; i += stride) {
+        float f[8];
+        unpack8(x[i], f);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) f[k] = fmaf(f[k], sc[k], sf[k]);
+        if (residual != nullptr) {
+            float r[8];
+            unpack8(residual[i], r);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) f[k] += r[k];
+        }
+        if (relu) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) f[k] = fmaxf(f[k], 0.f);
+        }
+        y[i] = pack8(f);
+    }
+}
+
+// Eval mode: y = relu?(x * scale + shift (+ residual)) with scale/shift folded from running stats.
+__global__ void __launch_bounds__(kEwThreads)
+bn_eval_kernel(const bf16x8* __restrict__ x, const float* __restrict__ gamma,
+               const float* __restrict__ beta, const float* __restrict__ running_mean,
+               const float* __restrict__ running_var, const bf16x8* __restrict__ residual,
+               bf16x8* __restrict__ y, long long nvec, int cvec, float eps, int relu) {
+    const long long stride = static_cast<long long>(gridDim.x) * kEwThreads;
+    long long i = static_cast<long long>(blockIdx.x) * kEwThreads + threadIdx.x;
+    const int cg = static_cast<int>(i % cvec);
+    float sc[8], sf[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const int c = cg * 8 + k;
+        sc[k] = gamma[c] * rsqrtf(running_var[c] + eps);
+        sf[k] = beta[c] - running_mean[c] * sc[k];
+    }
+    for (; i < nvec; i += stride) {
+        float f[8];
+        unpack8(x[i], f);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) f[k] = fmaf(f[k], sc[k], sf[k]);
+        if (residual != nullptr) {
+            float r[8];
+            unpack8(residual[i], r);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) f[k] += r[k];
+        }
+        if (relu) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) f[k] = fmaxf(f[k], 0.f);
+        }
+        y[i] = pack8(f);
+    }
+}
+
+// ------------------------------------------------------------------------------------ BN bwd
+// Pass 1: g = (dy1 + dy2) * [y > 0];  dbeta[c] += sum g;  dgamma[c] += sum g * xhat.
+// Writes g (bf16) for pass 2 and for the residual branch.
+__global__ void __launch_bounds__(kEwThreads)
+bn_bwd_reduce_kernel(const bf16x8* __restrict__ dy1, const bf16x8* __restrict__ dy2,
+                     const bf16x8* __restrict__ y, const bf16x8* __restrict__ x,
+                     const float* __restrict__ save_mean, const float* __restrict__ save_invstd,
+                     bf16x8* __restrict__ g_out, float* __restrict__ dgamma,
+                     float* __restrict__ dbeta, long long nvec, int cvec) {
+    __shared__ float sh[2][kEwThreads][8 + 1];
+    const long long stride = static_cast<long long>(gridDim.x) * kEwThreads;
+    long long i = static_cast<long long>(blockIdx.x) * kEwThreads + threadIdx.x;
+    const int cg = static_cast<int>(i % cvec);
+    float mean[8], istd[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        mean[k] = save_mean[cg * 8 + k];
+        istd[k] = save_invstd[cg * 8 + k];
+    }
+    float s1[8] = {0, 0, 0, 0, 0, 0, 0, 0}, s2[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (; i < nvec; i += stride) {
+        float g[8], xv[8];
+        unpack8(dy1[i], g);
+        if (dy2 != nullptr) {
+            float t[8];
+            unpack8(dy2[i], t);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) g[k] += t[k];
+        }
+        if (y != nullptr) {
+            float yv[8];
+            unpack8(y[i], yv);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) g[k] = yv[k] > 0.f ? g[k] : 0.f;
+        }
+        if (g_out != nullptr) {
+            const bf16x8 gb = pack8(g);
+            g_out[i] = gb;
+            unpack8(gb, g);  // reduce exactly what pass 2 will read
+        }
+        unpack8(x[i], xv);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            s1[k] += g[k];
+            s2[k] += g[k] * (xv[k] - mean[k]) * istd[k];
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        sh[0][threadIdx.x][k] = s1[k];
+        sh[1][threadIdx.x][k] = s2[k];
+    }
+    __syncthreads();
+    if (threadIdx.x < cvec) {
+        for (int t = threadIdx.x + cvec; t < kEwThreads; t += cvec) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                s1[k] += sh[0][t][k];
+                s2[k] += sh[1][t][k];
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            atomicAdd(dbeta + cg * 8 + k, s1[k]);
+            atomicAdd(dgamma + cg * 8 + k, s2[k]);
+        }
+    }
+}
+
+// Pass 2: dx = gamma * invstd * (g - dbeta/M - xhat * dgamma/M)
+__global__ void __launch_bounds__(kEwThreads)
+bn_bwd_apply_kernel(const bf16x8* __restrict__ g, const bf16x8* __restrict__ x,
+                    const float* __restrict__ save_mean, const float* __restrict__ save_invstd,
+                    const float* __restrict__ gamma, const float* __restrict__ dgamma,
+                    const float* __restrict__ dbeta, bf16x8* __restrict__ dx, long long nvec,
+                    int cvec, float inv_m, float grad_unscale) {
+    const long long stride = static_cast<long long>(gridDim.x) * kEwThreads;
+    long long i = static_cast<long long>(blockIdx.x) * kEwThreads + threadIdx.x;
+    const int cg = static_cast<int>(i % cvec);
+    float mean[8], istd[8], a[8], b[8], c2[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const int c = cg * 8 + k;
+        mean[k] = save_mean[c];
+        istd[k] = save_invstd[c];
+        a[k] = gamma[c] * istd[k];
+        b[k] = dbeta[c] * inv_m * grad_unscale;
+        c2[k] = dgamma[c] * inv_m * grad_unscale;
+    }
+    for (; i < nvec; i += stride) {
+        float gv[8], xv[8], o[8];
+        unpack8(g[i], gv);
+        unpack8(x[i], xv);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const float xh = (xv[k] - mean[k]) * istd[k];
+            o[k] = a[k] * (gv[k] - b[k] - xh * c2[k]);
+        }
+        dx[i] = pack8(o);
+    }
+}
+
+// ------------------------------------------------------------------------------------ max pool
+// 3x3, stride 2, pad 1 (NHWC).  idx holds the winning tap (0..8) for the backward pass.
+__global__ void __launch_bounds__(kEwThreads)
+maxpool_fwd_kernel(const bf16x8* __restrict__ x, bf16x8* __restrict__ y, uint8_t* __restrict__ idx,
+                   int N, int H, int W, int cvec, int P, int Q) {
+    const long long total = static_cast<long long>(N) * P * Q * cvec;
+    for (long long i = static_cast<long long>(blockIdx.x) * kEwThreads + threadIdx.x; i < total;
+         i += static_cast<long long>(gridDim.x) * kEwThreads) {
+        const int cg = static_cast<int>(i % cvec);
+        long long t = i / cvec;
+        const int q = static_cast<int>(t % Q);
+        t /= Q;
+        const int p = static_cast<int>(t % P);
+        const int n = static_cast<int>(t / P);
+        float best[8];
+        int bi[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            best[k] = -INFINITY;
+            bi[k] = 0;
+        }
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {
+            const int h = p * 2 - 1 + r;
+            if (h < 0 || h >= H) continue;
+#pragma unroll
+            for (int s = 0; s < 3; ++s) {
+                const int w = q * 2 - 1 + s;
+                if (w < 0 || w >= W) continue;
+                float f[8];
+                unpack8(x[((static_cast<long long>(n) * H + h) * W + w) * cvec + cg], f);
+#pragma unroll
+                for (int k = 0; k < 8; ++k)
+                    if (f[k] > best[k]) {
+                        best[k] = f[k];
+                        bi[k] = r * 3 + s;
+                    }
+            }
+        }
+        y[i] = pack8(best);
+        uint2 packed;
+        packed.x = bi[0] | (bi[1] << 8) | (bi[2] << 16) | (bi[3] << 24);
+        packed.y = bi[4] | (bi[5] << 8) | (bi[6] << 16) | (bi[7] << 24);
+        reinterpret_cast<uint2*>(idx)[i] = packed;
+    }
+}
+
+__global__ void __launch_bounds__(kEwThreads)
+maxpool_bwd_kernel(const bf16x8* __restrict__ dy, const uint8_t* __restrict__ idx,
+                   bf16x8* __restrict__ dx, int N, int H, int W, int cvec, int P, int Q) {
+    const long long total = static_cast<long long>(N) * H * W * cvec;
+    for (long long i = static_cast<long long>(blockIdx.x) * kEwThreads + threadIdx.x; i < total;
+         i += static_cast<long long>(gridDim.x) * kEwThreads) {
+        const int cg = static_cast<int>(i % cvec);
+        long long t = i / cvec;
+        const int w = static_cast<int>(t % W);
+        t /= W;
+        const int h = static_cast<int>(t % H);
+        const int n = static_cast<int>(t / H);
+        float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        // output rows p with 2p-1 <= h <= 2p+1
+        for (int p = h / 2; p <= (h + 1) / 2; ++p) {
+            if (p < 0 || p >= P) continue;
+            const int r = h - (p * 2 - 1);
+            if (r < 0 || r > 2) continue;
+            for (int q = w / 2; q <= (w + 1) / 2; ++q) {
+                if (q < 0 || q >= Q) continue;
+                const int s = w - (q * 2 - 1);
+                if (s < 0 || s > 2) continue;
+                const long long o = ((static_cast<long long>(n) * P + p) * Q + q) * cvec + cg;
+                const uint2 pk = reinterpret_cast<const uint2*>(idx)[o];
+                float g[8];
+                unpack8(dy[o], g);
+                const int tap = r * 3 + s;
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const uint32_t word = k < 4 ? pk.x : pk.y;
+                    const int sel = (word >> (8 * (k & 3))) & 0xff;
+                    if (sel == tap) acc[k] += g[k];
+                }
+            }
+        }
+        dx[i] = pack8(acc);
+    }
+}
+
+// ------------------------------------------------------------------------------------ head
+// pooled[n,c] = mean_{hw} x[n,hw,c];  logits[n,k] = sum_c pooled[n,c] * w[k,c] + b[k]
+__global__ void __launch_bounds__(256)
+head_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w,
+                const float* __restrict__ b, float* __restrict__ pooled,
+                float* __restrict__ logits, int HW, int C, int K) {
+    extern __shared__ float sp[];
+    const int n = blockIdx.x;
+    const float inv = 1.f / HW;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        float s = 0.f;
+        for (int i = 0; i < HW; ++i) s += __bfloat162float(x[(static_cast<long long>(n) * HW + i) * C + c]);
+        s *= inv;
+        sp[c] = s;
+        pooled[static_cast<long long>(n) * C + c] = s;
+    }
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+    for (int k = warp; k < K; k += nw) {
+        float s = 0.f;
+        for (int c = lane; c < C; c += 32) s += sp[c] * w[static_cast<long long>(k) * C + c];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (lane == 0) logits[static_cast<long long>(n) * K + k] = s + (b ? b[k] : 0.f);
+    }
+}
+
+// dx[n,hw,c] = (sum_k dlogits[n,k] w[k,c]) / HW
+__global__ void __launch_bounds__(256)
+head_bwd_dx_kernel(const float* __restrict__ dlogits, const float* __restrict__ w,
+                   __nv_bfloat16* __restrict__ dx, int HW, int C, int K) {
+    extern __shared__ float sd[];
+    const int n = blockIdx.x;
+    for (int k = threadIdx.x; k < K; k += blockDim.x) sd[k] = dlogits[static_cast<long long>(n) * K + k];
+    __syncthreads();
+    const float inv = 1.f / HW;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        float s = 0.f;
+        for (int k = 0; k < K; ++k) s += sd[k] * w[static_cast<long long>(k) * C + c];
+        const __nv_bfloat16 v = __float2bfloat16_rn(s * inv);
+        for (int i = 0; i < HW; ++i) dx[(static_cast<long long>(n) * HW + i) * C + c] = v;
+    }
+}
+
+// dw[k,c] += sum_n dlogits[n,k] pooled[n,c];  db[k] += sum_n dlogits[n,k]
+__global__ void __launch_bounds__(256)
+head_bwd_dw_kernel(const float* __restrict__ dlogits, const float* __restrict__ pooled,
+                   float* __restrict__ dw, float* __restrict__ db, int B, int C, int K,
+                   float unscale) {
+    const int k = blockIdx.y;
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c < C) {
+        float s = 0.f;
+        for (int n = 0; n < B; ++n)
+            s += dlogits[static_cast<long long>(n) * K + k] * pooled[static_cast<long long>(n) * C + c];
+        dw[static_cast<long long>(k) * C + c] += s * unscale;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0 && db != nullptr) {
+        float s = 0.f;
+        for (int n = 0; n < B; ++n) s += dlogits[static_cast<long long>(n) * K + k];
+        db[k] += s * unscale;
+    }
+}
+
+// ------------------------------------------------------------------------------------ CE
+// loss = mean_n (logsumexp(z_n) - z_n[t_n]);  dz = (softmax - onehot) * scale / B.
+// One block, one warp per row (looped).  Also accumulates epoch metrics on the device:
+// metrics[0] += loss * B (f64), metrics[1] += #correct, metrics[2] += B.
+__global__ void __launch_bounds__(1024)
+ce_fwd_bwd_kernel(const float* __restrict__ logits, const long long* __restrict__ target,
+                  float* __restrict__ loss_out, float* __restrict__ dlogits,
+                  const float* __restrict__ loss_scale, double* __restrict__ metrics, int B, int K) {
+    __shared__ float s_loss[32];
+    __shared__ int s_corr[32];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+    const float scale = (loss_scale != nullptr ? *loss_scale : 1.f) / B;
+    float wl = 0.f;
+    int wc = 0;
+    for (int n = warp; n < B; n += nw) {
+        const float* z = logits + static_cast<long long>(n) * K;
+        float mx = -INFINITY;
+        int am = 0;
+        for (int k = lane; k < K; k += 32) {
+            const float v = z[k];
+            if (v > mx) {
+                mx = v;
+                am = k;
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float om = __shfl_xor_sync(0xffffffffu, mx, o);
+            const int oa = __shfl_xor_sync(0xffffffffu, am, o);
+            if (om > mx || (om == mx && oa < am)) {
+                mx = om;
+                am = oa;
+            }
+        }
+        float se = 0.f;
+        for (int k = lane; k < K; k += 32) se += __expf(z[k] - mx);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) se += __shfl_xor_sync(0xffffffffu, se, o);
+        const int t = static_cast<int>(target[n]);
+        const float lse = mx + __logf(se);
+        if (dlogits != nullptr) {
+            const float inv = 1.f / se;
+            for (int k = lane; k < K; k += 32) {
+                const float p = __expf(z[k] - mx) * inv;
+                dlogits[static_cast<long long>(n) * K + k] = (p - (k == t ? 1.f : 0.f)) * scale;
+            }
+        }
+        if (lane == 0) {
+            wl += lse - z[t];
+            wc += (am == t);
+        }
+    }
+    if (lane == 0) {
+        s_loss[warp] = wl;
+        s_corr[warp] = wc;
+    }
+    __syncthreads();
+    if (warp == 0) {
+        float l = lane < nw ? s_loss[lane] : 0.f;
+        int c = lane < nw ? s_corr[lane] : 0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            l += __shfl_xor_sync(0xffffffffu, l, o);
+            c += __shfl_xor_sync(0xffffffffu, c, o);
+        }
+        if (lane == 0) {
+            loss_out[0] = l / B;
+            if (metrics != nullptr) {
+                metrics[0] += static_cast<double>(l);
+                metrics[1] += static_cast<double>(c);
+                metrics[2] += static_cast<double>(B);
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------ stem
+// NCHW fp32 image -> im2col rows [N*P*Q][ldk] bf16, column (r*S+s)*C + c (KRSC order);
+// columns >= R*S*C are zero.
+__global__ void __launch_bounds__(kEwThreads)
+im2col_nchw_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ out, int N, int C,
+                   int H, int W, int R, int S, int stride, int pad, int P, int Q, int ldk) {
+    const long long total = static_cast<long long>(N) * P * Q * ldk;
+    const int K = R * S * C;
+    for (long long i = static_cast<long long>(blockIdx.x) * kEwThreads + threadIdx.x; i < total;
+         i += static_cast<long long>(gridDim.x) * kEwThreads) {
+        const int col = static_cast<int>(i % ldk);
+        long long t = i / ldk;
+        const int q = static_cast<int>(t % Q);
+        t /= Q;
+        const int p = static_cast<int>(t % P);
+        const int n = static_cast<int>(t / P);
+        float v = 0.f;
+        if (col < K) {
+            const int c = col % C;
+            const int rs = col / C;
+            const int s = rs % S, r = rs / S;
+            const int h = p * stride - pad + r, w = q * stride - pad + s;
+            if (h >= 0 && h < H && w >= 0 && w < W)
+                v = x[((static_cast<long long>(n) * C + c) * H + h) * W + w];
+        }
+        out[i] = __float2bfloat16_rn(v);
+    }
+}
+
+// fp32 [rows][cols] -> bf16 [rows][ld] (zero padded); used for the stem weight whose 147-wide
+// rows are not 16-byte aligned.
+__global__ void __launch_bounds__(kEwThreads)
+pad_rows_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int rows, int cols,
+                int ld) {
+    const int total = rows * ld;
+    for (int i = blockIdx.x * kEwThreads + threadIdx.x; i < total; i += gridDim.x * kEwThreads) {
+        const int c = i % ld, r = i / ld;
+        dst[i] = __float2bfloat16_rn(c < cols ? src[r * cols + c] : 0.f);
+    }
+}
+
+// NCHW fp32 -> NHWC bf16 (general layout change for inputs with C % 8 == 0 handled by callers)
+__global__ void __launch_bounds__(kEwThreads)
+nchw_to_nhwc_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y, int N, int C, int H,
+                    int W) {
+    const long long total = static_cast<long long>(N) * C * H * W;
+    for (long long i = static_cast<long long>(blockIdx.x) * kEwThreads + threadIdx.x; i < total;
+         i += static_cast<long long>(gridDim.x) * kEwThreads) {
+        const int c = static_cast<int>(i % C);
+        long long t = i / C;
+        const int w = static_cast<int>(t % W);
+        t /= W;
+        const int h = static_cast<int>(t % H);
+        const int n = static_cast<int>(t / H);
+        y[i] = __float2bfloat16_rn(x[((static_cast<long long>(n) * C + c) * H + h) * W + w]);
+    }
+}
+
+}  // namespace dpt
+
+using namespace dpt;
+
+#define DPT_CHECK_LAUNCH() return static_cast<int>(cudaGetLastError())
+
+static inline bool cvec_ok(int C) { return C % 8 == 0 && (kEwThreads % (C / 8)) == 0; }
+
+extern "C" int dpt_bn_stats(const void* x, float* sum, float* sq, long long M, int C, void* stream) {
+    if (!cvec_ok(C)) return DPT_ERR_SHAPE;
+    const long long nvec = M * (C / 8);
+    bn_stats_kernel<<<ew_grid(nvec, C / 8), kEwThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const bf16x8*>(x), sum, sq, nvec, C / 8);
+    DPT_CHECK_LAUNCH();
+}
+
+extern "C" int dpt_bn_fwd_train(const void* x, const float* sum, const float* sq, const float* gamma,
+                                const float* beta, const void* residual, void* y, float* save_mean,
+                                float* save_invstd, float* running_mean, float* running_var,
+                                long long* num_batches_tracked, long long M, int C, float momentum,
+                                float eps, int relu, void* stream) {
+    if (!cvec_ok(C)) return DPT_ERR_SHAPE;
+    const long long nvec = M * (C / 8);
+    const float unbias = M > 1 ? static_cast<float>(M) / static_cast<float>(M - 1) : 1.f;
+    bn_fwd_kernel<<<ew_grid(nvec, C / 8), kEwThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const bf16x8*>(x), sum, sq, gamma, beta, static_cast<const bf16x8*>(residual),
+        static_cast<bf16x8*>(y), save_mean, save_invstd, running_mean, running_var,
+        num_batches_tracked, nvec, C / 8, 1.f / static_cast<float>(M), unbias, momentum, eps, relu);
+    DPT_CHECK_LAUNCH();
+}
+
+extern "C" int dpt_bn_fwd_eval(const void* x, const float* gamma, const float* beta,
+                               const float* running_mean, const float* running_var,
+                               const void* residual, void* y, long long M, int C, float eps,
+                               int relu, void* stream) {
+    if (!cvec_ok(C)) return DPT_ERR_SHAPE;
+    const long long nvec = M * (C / 8);
+    bn_eval_kernel<<<ew_grid(nvec, C / 8), kEwThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const bf16x8*>(x), gamma, beta, running_mean, running_var,
+        static_cast<const bf16x8*>(residual), static_cast<bf16x8*>(y), nvec, C / 8, eps, relu);
+    DPT_CHECK_LAUNCH();
+}
+
+extern "C" int dpt_bn_bwd_reduce(const void* dy1, const void* dy2, const void* y, const void* x,
+                                 const float* save_mean, const float* save_invstd, void* g_out,
+                                 float* dgamma, float* dbeta, long long M, int C, void* stream) {
+    if (!cvec_ok(C)) return DPT_ERR_SHAPE;
+    const long long nvec = M * (C / 8);
+    bn_bwd_reduce_kernel<<<ew_grid(nvec, C / 8), kEwThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const bf16x8*>(dy1), static_cast<const bf16x8*>(dy2),
+        static_cast<const bf16x8*>(y), static_cast<const bf16x8*>(x), save_mean, save_invstd,
+        static_cast<bf16x8*>(g_out), dgamma, dbeta, nvec, C / 8);
+    DPT_CHECK_LAUNCH();
+}
+
+extern "C" int dpt_bn_bwd_apply(const void* g, const void* x, const float* save_mean,
+                                const float* save_invstd, const float* gamma, const float* dgamma,
+                                const float* dbeta, void* dx, long long M, int C, void* stream) {
+    if (!cvec_ok(C)) return DPT_ERR_SHAPE;
+    const long long nvec = M * (C / 8);
+    bn_bwd_apply_kernel<<<ew_grid(nvec, C / 8), kEwThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const bf16x8*>(g), static_cast<const bf16x8*>(x), save_mean, save_invstd, gamma,
+        dgamma, dbeta, static_cast<bf16x8*>(dx), nvec, C / 8, 1.f / static_cast<float>(M), 1.f);
+    DPT_CHECK_LAUNCH();
+}
+
+extern "C" int dpt_maxpool3x3s2_fwd(const void* x, void* y, void* idx, int N, int H, int W, int C,
+                                    void* stream) {
+    if (C % 8 != 0) return DPT_ERR_SHAPE;
+    const int P = (H + 2 - 3) / 2 + 1, Q = (W + 2 - 3) / 2 + 1;
+    const long long total = static_cast<long long>(N) * P * Q * (C / 8);
+    maxpool_fwd_kernel<<<ew_grid(total, 1), kEwThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const bf16x8*>(x), static_cast<bf16x8*>(y), static_cast<uint8_t*>(idx), N, H, W,
+        C / 8, P, Q);
+    DPT_CHECK_LAUNCH();
+}
+
+extern "C" int dpt_maxpool3x3s2_bwd(const void* dy, const void* idx, void* dx, int N, int H, int W,
+                                    int C, void* stream) {
+    if (C % 8 != 0) return DPT_ERR_SHAPE;
+    const int P = (H + 2 - 3) / 2 + 1, Q = (W + 2 - 3) / 2 + 1;
+    const long long total = static_cast<long long>(N) * H * W * (C / 8);
+    maxpool_bwd_kernel<<<ew_grid(total, 1), kEwThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const bf16x8*>(dy), static_cast<const uint8_t*>(idx), static_cast<bf16x8*>(dx),
+        N, H, W, C / 8, P, Q);
+    DPT_CHECK_LAUNCH();
+}
+
+extern "C" int dpt_head_fwd(const void* x, const float* w, const float* b, float* pooled,
+                            float* logits, int B, int HW, int C, int K, void* stream) {
+    head_fwd_kernel<<<B, 256, C * sizeof(float), static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __nv_bfloat16*>(x), w, b, pooled, logits, HW, C, K);
+    DPT_CHECK_LAUNCH();
+}
+
+extern "C" int dpt_head_bwd(const float* dlogits, const float* w, const float* pooled, void* dx,
+                            float* dw, float* db, int B, int HW, int C, int K, void* stream) {
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (dx != nullptr)
+        head_bwd_dx_kernel<<<B, 256, K * sizeof(float), st>>>(
+            dlogits, w, static_cast<__nv_bfloat16*>(dx), HW, C, K);
+    dim3 grid((C + 255) / 256, K);
+    head_bwd_dw_kernel<<<grid, 256, 0, st>>>(dlogits, pooled, dw, db, B, C, K, 1.f);
+    DPT_CHECK_LAUNCH();
+}
+
+extern "C" int dpt_cross_entropy(const float* logits, const long long* target, float* loss,
+                                 float* dlogits, const float* loss_scale, double* metrics, int B,
+                                 int K, void* stream) {
+    int threads = B * 32;
+    if (threads > 1024) threads = 1024;
+    if (threads < 32) threads = 32;
+    ce_fwd_bwd_kernel<<<1, threads, 0, static_cast<cudaStream_t>(stream)>>>(
+        logits, target, loss, dlogits, loss_scale, metrics, B, K);
+    DPT_CHECK_LAUNCH();
+}
+
+extern "C" int dpt_im2col_nchw_f32(const float* x, void* out, int N, int C, int H, int W, int R,
+                                   int S, int stride, int pad, int ldk, void* stream) {
+    const int P = (H + 2 * pad - R) / stride + 1, Q = (W + 2 * pad - S) / stride + 1;
+    const long long total = static_cast<long long>(N) * P * Q * ldk;
+    im2col_nchw_kernel<<<ew_grid(total, 1), kEwThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+        x, static_cast<__nv_bfloat16*>(out), N, C, H, W, R, S, stride, pad, P, Q, ldk);
+    DPT_CHECK_LAUNCH();
+}
+
+extern "C" int dpt_pad_rows_f32_to_bf16(const float* src, void* dst, int rows, int cols, int ld,
+                                        void* stream) {
+    pad_rows_kernel<<<ew_grid(static_cast<long long>(rows) * ld, 1), kEwThreads, 0,
+                      static_cast<cudaStream_t>(stream)>>>(src, static_cast<__nv_bfloat16*>(dst),
+                                                           rows, cols, ld);
+    DPT_CHECK_LAUNCH();
+}
+
+extern "C" int dpt_nchw_f32_to_nhwc_bf16(const float* x, void* y, int N, int C, int H, int W,
+                                         void* stream) {
+    const long long total = static_cast<long long>(N) * C * H * W;
+    nchw_to_nhwc_kernel<<<ew_grid(total, 1), kEwThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+        x, static_cast<__nv_bfloat16*>(y), N, C, H, W);
+    DPT_CHECK_LAUNCH();
+}

@@ -1,0 +1,243 @@
+"""Raw (non-autograd) Python entry points of the sm_100a kernels.
+
+Tensors are NHWC bf16 activations ``[N, H, W, C]`` and KRSC conv weights ``[Cout, R, S, Cin]``
+unless stated otherwise.  Every function enqueues on the current CUDA stream and returns
+immediately; outputs may be passed in (``out=``) so that callers with a static memory plan
+(CUDA-graph capture) allocate nothing.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _lib
+from ._lib import call, count, ptr, stream
+
+BF16 = torch.bfloat16
+
+
+def conv_out_hw(H: int, W: int, R: int, S: int, stride: int, pad: int) -> tuple[int, int]:
+    return (H + 2 * pad - R) // stride + 1, (W + 2 * pad - S) // stride + 1
+
+
+def conv_fprop(x, w, stride=1, pad=0, *, out=None, stats=None, splits=1):
+    """y = conv(x, w).  ``stats=(sum, sq)`` (fp32 [Cout], pre-zeroed) receives the per-channel
+    sum / sum of squares of y for the following BatchNorm.  ``splits>1`` accumulates into an
+    fp32 ``out`` (pre-zeroed) with split-K atomics instead of storing bf16."""
+    N, H, W, Cin = x.shape
+    Cout, R, S, _ = w.shape
+    P, Q = conv_out_hw(H, W, R, S, stride, pad)
+    atomic = splits > 1
+    if out is None:
+        out = (torch.zeros if atomic else torch.empty)(
+            (N, P, Q, Cout), device=x.device, dtype=torch.float32 if atomic else BF16)
+    s1, s2 = stats if stats is not None else (None, None)
+    call("dpt_conv_fprop", ptr(x), ptr(w), ptr(out), N, H, W, Cin, Cout, R, S, stride, pad,
+         ptr(s1), ptr(s2), int(atomic), splits, stream())
+    count()
+    return out
+
+
+def conv_dgrad(dy, w, x_shape, stride=1, pad=0, *, out=None, dy2=None, w2=None, pad2=0):
+    """dx = conv_backward_data(dy, w) [+ conv_backward_data(dy2, w2)] for convs sharing x."""
+    N, H, W, Cin = x_shape
+    Cout, R, S, _ = w.shape
+    if out is None:
+        out = torch.empty((N, H, W, Cin), device=dy.device, dtype=BF16)
+    R2, S2 = (w2.shape[1], w2.shape[2]) if w2 is not None else (0, 0)
+    call("dpt_conv_dgrad", ptr(dy), ptr(w), ptr(out), N, H, W, Cin, Cout, R, S, stride, pad,
+         ptr(dy2), ptr(w2), R2, S2, pad2, stream())
+    count()
+    return out
+
+
+def conv_wgrad(dy, x, w_shape, stride=1, pad=0, *, out=None, splits=0):
+    """dw (fp32, KRSC) += conv_backward_filter(dy, x).  ``out`` must be zeroed (or hold a
+    gradient to accumulate into) before the call."""
+    N, H, W, Cin = x.shape
+    Cout, R, S, _ = w_shape
+    if out is None:
+        out = torch.zeros((Cout, R, S, Cin), device=dy.device, dtype=torch.float32)
+    call("dpt_conv_wgrad", ptr(dy), ptr(x), ptr(out), N, H, W, Cin, Cout, R, S, stride, pad,
+         splits, stream())
+    count()
+    return out
+
+
+def gemm(op, A, B, C, M, N, K, lda, ldb, ldc, *, out_mode=0, bias=None, stats=None, splits=1):
+    s1, s2 = stats if stats is not None else (None, None)
+    call("dpt_gemm_bf16", op, ptr(A), ptr(B), ptr(C), M, N, K, lda, ldb, ldc, out_mode, ptr(bias),
+         ptr(s1), ptr(s2), splits, stream())
+    count()
+    return C
+
+
+def bn_stats(x, sum_, sq):
+    C_ = x.shape[-1]
+    call("dpt_bn_stats", ptr(x), ptr(sum_), ptr(sq), x.numel() // C_, C_, stream())
+    count()
+
+
+def bn_fwd_train(x, sum_, sq, gamma, beta, *, residual=None, relu=False, out=None, save_mean=None,
+                 save_invstd=None, running_mean=None, running_var=None, num_batches_tracked=None,
+                 momentum=0.1, eps=1e-5):
+    C_ = x.shape[-1]
+    M = x.numel() // C_
+    if out is None:
+        out = torch.empty_like(x)
+    if save_mean is None:
+        save_mean = torch.empty(C_, device=x.device, dtype=torch.float32)
+        save_invstd = torch.empty(C_, device=x.device, dtype=torch.float32)
+    call("dpt_bn_fwd_train", ptr(x), ptr(sum_), ptr(sq), ptr(gamma), ptr(beta), ptr(residual),
+         ptr(out), ptr(save_mean), ptr(save_invstd), ptr(running_mean), ptr(running_var),
+         ptr(num_batches_tracked), M, C_, momentum, eps, int(relu), stream())
+    count()
+    return out, save_mean, save_invstd
+
+
+def bn_fwd_eval(x, gamma, beta, running_mean, running_var, *, residual=None, relu=False, out=None,
+                eps=1e-5):
+    C_ = x.shape[-1]
+    if out is None:
+        out = torch.empty_like(x)
+    call("dpt_bn_fwd_eval", ptr(x), ptr(gamma), ptr(beta), ptr(running_mean), ptr(running_var),
+         ptr(residual), ptr(out), x.numel() // C_, C_, eps, int(relu), stream())
+    count()
+    return out
+
+
+def bn_bwd(dy, x, save_mean, save_invstd, gamma, dgamma, dbeta, *, dy2=None, y=None, g_out=None,
+           dx=None):
+    """Fused (residual-sum + ReLU mask +) BatchNorm backward.  ``dgamma``/``dbeta`` are
+    accumulated into (zero them first).  Returns (dx, g) where g is the masked incoming gradient
+    (what flows into the residual branch)."""
+    C_ = x.shape[-1]
+    M = x.numel() // C_
+    need_g = (dy2 is not None) or (y is not None)
+    if need_g and g_out is None:
+        g_out = torch.empty_like(x)
+    call("dpt_bn_bwd_reduce", ptr(dy), ptr(dy2), ptr(y), ptr(x), ptr(save_mean), ptr(save_invstd),
+         ptr(g_out), ptr(dgamma), ptr(dbeta), M, C_, stream())
+    g = g_out if need_g else dy
+    if dx is None:
+        dx = torch.empty_like(x)
+    call("dpt_bn_bwd_apply", ptr(g), ptr(x), ptr(save_mean), ptr(save_invstd), ptr(gamma),
+         ptr(dgamma), ptr(dbeta), ptr(dx), M, C_, stream())
+    count(2)
+    return dx, g
+
+
+def maxpool_fwd(x, *, out=None, idx=None):
+    N, H, W, C_ = x.shape
+    P, Q = conv_out_hw(H, W, 3, 3, 2, 1)
+    if out is None:
+        out = torch.empty((N, P, Q, C_), device=x.device, dtype=BF16)
+    if idx is None:
+        idx = torch.empty((N, P, Q, C_), device=x.device, dtype=torch.uint8)
+    call("dpt_maxpool3x3s2_fwd", ptr(x), ptr(out), ptr(idx), N, H, W, C_, stream())
+    count()
+    return out, idx
+
+
+def maxpool_bwd(dy, idx, x_shape, *, out=None):
+    N, H, W, C_ = x_shape
+    if out is None:
+        out = torch.empty(x_shape, device=dy.device, dtype=BF16)
+    call("dpt_maxpool3x3s2_bwd", ptr(dy), ptr(idx), ptr(out), N, H, W, C_, stream())
+    count()
+    return out
+
+
+def head_fwd(x, w, b, *, pooled=None, logits=None):
+    """Global average pool over HW + linear: x [N,H,W,C] bf16, w [K,C] fp32, b [K] fp32."""
+    N, H, W, C_ = x.shape
+    K = w.shape[0]
+    if pooled is None:
+        pooled = torch.empty((N, C_), device=x.device, dtype=torch.float32)
+    if logits is None:
+        logits = torch.empty((N, K), device=x.device, dtype=torch.float32)
+    call("dpt_head_fwd", ptr(x), ptr(w), ptr(b), ptr(pooled), ptr(logits), N, H * W, C_, K, stream())
+    count()
+    return logits, pooled
+
+
+def head_bwd(dlogits, w, pooled, x_shape, dw, db, *, dx=None):
+    N, H, W, C_ = x_shape
+    K = w.shape[0]
+    if dx is None:
+        dx = torch.empty(x_shape, device=dlogits.device, dtype=BF16)
+    call("dpt_head_bwd", ptr(dlogits), ptr(w), ptr(pooled), ptr(dx), ptr(dw), ptr(db), N, H * W, C_,
+         K, stream())
+    count(2)
+    return dx
+
+
+def cross_entropy(logits, target, *, loss=None, dlogits=None, loss_scale=None, metrics=None,
+                  need_grad=True):
+    B, K = logits.shape
+    if loss is None:
+        loss = torch.empty((), device=logits.device, dtype=torch.float32)
+    if need_grad and dlogits is None:
+        dlogits = torch.empty_like(logits)
+    call("dpt_cross_entropy", ptr(logits), ptr(target), ptr(loss), ptr(dlogits) if need_grad else None,
+         ptr(loss_scale), ptr(metrics), B, K, stream())
+    count()
+    return loss, dlogits
+
+
+def im2col_nchw(x, R, S, stride, pad, ldk, *, out=None):
+    N, C_, H, W = x.shape
+    P, Q = conv_out_hw(H, W, R, S, stride, pad)
+    if out is None:
+        out = torch.empty((N * P * Q, ldk), device=x.device, dtype=BF16)
+    call("dpt_im2col_nchw_f32", ptr(x), ptr(out), N, C_, H, W, R, S, stride, pad, ldk, stream())
+    count()
+    return out
+
+
+def pad_rows_to_bf16(src, rows, cols, ld, *, out=None):
+    if out is None:
+        out = torch.empty((rows, ld), device=src.device, dtype=BF16)
+    call("dpt_pad_rows_f32_to_bf16", ptr(src), ptr(out), rows, cols, ld, stream())
+    count()
+    return out
+
+
+def nchw_to_nhwc_bf16(x, *, out=None):
+    N, C_, H, W = x.shape
+    if out is None:
+        out = torch.empty((N, H, W, C_), device=x.device, dtype=BF16)
+    call("dpt_nchw_f32_to_nhwc_bf16", ptr(x), ptr(out), N, C_, H, W, stream())
+    count()
+    return out
+
+
+def sgd_flat(p, g, m, shadow, lr, momentum=0.0, dampening=0.0, weight_decay=0.0, nesterov=False,
+             grad_scale=None, found_inf=None):
+    call("dpt_sgd_flat", ptr(p), ptr(g), ptr(m), ptr(shadow), p.numel(), lr, momentum, dampening,
+         weight_decay, int(nesterov), ptr(grad_scale), ptr(found_inf), stream())
+    count()
+
+
+def adam_flat(p, g, m, v, shadow, step_count, lr, beta1=0.9, beta2=0.999, eps=1e-8,
+              weight_decay=0.0, decoupled=False, grad_scale=None, found_inf=None):
+    call("dpt_adam_flat", ptr(p), ptr(g), ptr(m), ptr(v), ptr(shadow), p.numel(), lr, beta1, beta2,
+         eps, weight_decay, int(decoupled), ptr(step_count), ptr(grad_scale), ptr(found_inf),
+         stream())
+    count(2)
+
+
+def amp_unscale(g, inv_scale, found_inf):
+    call("dpt_amp_unscale", ptr(g), g.numel(), ptr(inv_scale), ptr(found_inf), stream())
+    count()
+
+
+def amp_update_scale(scale, growth_tracker, found_inf, inv_scale_out, growth_factor=2.0,
+                     backoff_factor=0.5, growth_interval=2000):
+    call("dpt_amp_update_scale", ptr(scale), ptr(growth_tracker), ptr(found_inf),
+         ptr(inv_scale_out), growth_factor, backoff_factor, growth_interval, stream())
+    count()
+
+
+def cast_to_bf16(src, dst):
+    call("dpt_cast_f32_to_bf16", ptr(src), ptr(dst), src.numel(), stream())
+    count()

@@ -1,0 +1,142 @@
+"""tcgen05 implicit-GEMM conv / GEMM kernels vs a plain PyTorch fp32 reference of the same op."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _F():
+    from dpt_b200.ops import functional as Fn
+    return Fn
+
+
+def _mk(shape, scale=1.0, seed=0):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    return (torch.randn(shape, device="cuda", generator=g) * scale).to(torch.bfloat16)
+
+
+def _ref_conv(x_nhwc, w_krsc, stride, pad):
+    x = x_nhwc.float().permute(0, 3, 1, 2)
+    w = w_krsc.float().permute(0, 3, 1, 2)
+    return F.conv2d(x, w, stride=stride, padding=pad)  # NCHW fp32
+
+
+def _close(got, ref, tol, what):
+    err = (got.float() - ref).abs().max().item()
+    den = ref.abs().max().item() + 1e-6
+    assert err / den < tol, f"{what}: max abs err {err:.4g} vs ref max {den:.4g}"
+
+
+# (N, H, W, Cin, Cout, k, stride, pad)
+CONV_CASES = [
+    (8, 8, 8, 64, 64, 3, 1, 1),       # layer1
+    (8, 8, 8, 64, 128, 3, 2, 1),      # layer2.0.conv1
+    (8, 8, 8, 64, 128, 1, 2, 0),      # layer2.0.downsample
+    (16, 4, 4, 128, 128, 3, 1, 1),    # layer2
+    (32, 2, 2, 256, 256, 3, 1, 1),    # layer3
+    (128, 1, 1, 512, 512, 3, 1, 1),   # layer4 (only the centre tap is live)
+    (4, 14, 14, 72, 96, 3, 1, 1),     # ragged tiles, Cin/Cout not multiples of 64
+    (2, 56, 56, 64, 64, 1, 1, 0),     # resnet50 1x1
+    (3, 16, 16, 64, 256, 3, 2, 1),    # batch tail (N not a multiple of the box)
+]
+
+
+@pytest.mark.parametrize("case", CONV_CASES)
+def test_conv_fprop(case):
+    Fn = _F()
+    N, H, W, Cin, Cout, k, s, p = case
+    x = _mk((N, H, W, Cin), 1.0, 1)
+    w = _mk((Cout, k, k, Cin), 0.05, 2)
+    ssum = torch.zeros(Cout, device="cuda")
+    ssq = torch.zeros(Cout, device="cuda")
+    y = Fn.conv_fprop(x, w, s, p, stats=(ssum, ssq))
+    torch.cuda.synchronize()
+    ref = _ref_conv(x, w, s, p)
+    _close(y.permute(0, 3, 1, 2), ref, 1e-2, "fprop")
+    _close(ssum, ref.sum(dim=(0, 2, 3)), 5e-3, "stat sum")
+    _close(ssq, (ref * ref).sum(dim=(0, 2, 3)), 5e-3, "stat sq")
+
+
+@pytest.mark.parametrize("case", CONV_CASES[:6])
+def test_conv_fprop_splitk(case):
+    Fn = _F()
+    N, H, W, Cin, Cout, k, s, p = case
+    x = _mk((N, H, W, Cin), 1.0, 3)
+    w = _mk((Cout, k, k, Cin), 0.05, 4)
+    y = Fn.conv_fprop(x, w, s, p, splits=4)
+    torch.cuda.synchronize()
+    assert y.dtype == torch.float32
+    _close(y.permute(0, 3, 1, 2), _ref_conv(x, w, s, p), 2e-3, "fprop split-k")
+
+
+@pytest.mark.parametrize("case", CONV_CASES)
+def test_conv_dgrad(case):
+    Fn = _F()
+    N, H, W, Cin, Cout, k, s, p = case
+    if s == 2 and (H % 2 or W % 2):
+        pytest.skip("odd stride-2 input")
+    P, Q = Fn.conv_out_hw(H, W, k, k, s, p)
+    dy = _mk((N, P, Q, Cout), 1.0, 5)
+    w = _mk((Cout, k, k, Cin), 0.05, 6)
+    dx = Fn.conv_dgrad(dy, w, (N, H, W, Cin), s, p)
+    torch.cuda.synchronize()
+    ref = torch.nn.grad.conv2d_input((N, Cin, H, W), w.float().permute(0, 3, 1, 2),
+                                     dy.float().permute(0, 3, 1, 2), stride=s, padding=p)
+    _close(dx.permute(0, 3, 1, 2), ref, 1e-2, "dgrad")
+
+
+def test_conv_dgrad_fused_downsample():
+    """3x3/2 conv and the 1x1/2 downsample that read the same block input, one kernel."""
+    Fn = _F()
+    N, H, W, Cin, Cout = 8, 8, 8, 64, 128
+    dy = _mk((N, 4, 4, Cout), 1.0, 7)
+    dy2 = _mk((N, 4, 4, Cout), 1.0, 8)
+    w = _mk((Cout, 3, 3, Cin), 0.05, 9)
+    w2 = _mk((Cout, 1, 1, Cin), 0.05, 10)
+    dx = Fn.conv_dgrad(dy, w, (N, H, W, Cin), 2, 1, dy2=dy2, w2=w2, pad2=0)
+    torch.cuda.synchronize()
+    ref = torch.nn.grad.conv2d_input((N, Cin, H, W), w.float().permute(0, 3, 1, 2),
+                                     dy.float().permute(0, 3, 1, 2), stride=2, padding=1)
+    ref = ref + torch.nn.grad.conv2d_input((N, Cin, H, W), w2.float().permute(0, 3, 1, 2),
+                                           dy2.float().permute(0, 3, 1, 2), stride=2, padding=0)
+    _close(dx.permute(0, 3, 1, 2), ref, 1e-2, "fused dgrad")
+
+
+@pytest.mark.parametrize("case", CONV_CASES)
+def test_conv_wgrad(case):
+    Fn = _F()
+    N, H, W, Cin, Cout, k, s, p = case
+    P, Q = Fn.conv_out_hw(H, W, k, k, s, p)
+    dy = _mk((N, P, Q, Cout), 1.0, 11)
+    x = _mk((N, H, W, Cin), 1.0, 12)
+    dw = Fn.conv_wgrad(dy, x, (Cout, k, k, Cin), s, p)
+    torch.cuda.synchronize()
+    ref = torch.nn.grad.conv2d_weight(x.float().permute(0, 3, 1, 2), (Cout, Cin, k, k),
+                                      dy.float().permute(0, 3, 1, 2), stride=s, padding=p)
+    _close(dw.permute(0, 3, 1, 2), ref, 2e-3, "wgrad")
+
+
+@pytest.mark.parametrize("mnk", [(256, 64, 147), (300, 200, 520), (128, 1000, 2048), (4096, 64, 152)])
+def test_gemm_ops(mnk):
+    Fn = _F()
+    M, N, K = mnk
+    ld = lambda v: (v + 7) // 8 * 8  # noqa: E731
+    A = _mk((M, ld(K)), 1.0, 13)
+    B = _mk((N, ld(K)), 0.05, 14)
+    C = torch.empty((M, N), device="cuda", dtype=torch.float32)
+    Fn.gemm(0, A, B, C, M, N, K, ld(K), ld(K), N, out_mode=1)
+    torch.cuda.synchronize()
+    _close(C, A[:, :K].float() @ B[:, :K].float().t(), 2e-3, "gemm NT")
+
+    B1 = _mk((K, ld(N)), 0.05, 15)
+    C1 = torch.empty((M, N), device="cuda", dtype=torch.float32)
+    Fn.gemm(1, A, B1, C1, M, N, K, ld(K), ld(N), N, out_mode=1)
+    torch.cuda.synchronize()
+    _close(C1, A[:, :K].float() @ B1[:, :N].float(), 2e-3, "gemm NN")
+
+    A2 = _mk((K, ld(M)), 1.0, 16)
+    C2 = torch.zeros((M, N), device="cuda", dtype=torch.float32)
+    Fn.gemm(2, A2, B1, C2, M, N, K, ld(M), ld(N), N, out_mode=2, splits=3)
+    torch.cuda.synchronize()
+    _close(C2, A2[:, :M].float().t() @ B1[:, :N].float(), 2e-3, "gemm TN split")
