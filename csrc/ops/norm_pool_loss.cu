@@ -331,7 +331,8 @@ maxpool_fwd_kernel(const bf16x8* __restrict__ x, bf16x8* __restrict__ y, uint8_t
 }
 
 __global__ void __launch_bounds__(kEwThreads)
-maxpool_bwd_kernel(const bf16x8* __restrict__ dy, const uint8_t* __restrict__ idx,
+maxpool_bwd_kernel(const bf16x8* __restrict__ dy, const bf16x8* __restrict__ dy2,
+                   const uint8_t* __restrict__ idx,
                    bf16x8* __restrict__ dx, int N, int H, int W, int cvec, int P, int Q) {
     const long long total = static_cast<long long>(N) * H * W * cvec;
     for (long long i = static_cast<long long>(blockIdx.x) * kEwThreads + threadIdx.x; i < total;
@@ -356,6 +357,12 @@ maxpool_bwd_kernel(const bf16x8* __restrict__ dy, const uint8_t* __restrict__ id
                 const uint2 pk = reinterpret_cast<const uint2*>(idx)[o];
                 float g[8];
                 unpack8(dy[o], g);
+                if (dy2 != nullptr) {
+                    float g2[8];
+                    unpack8(dy2[o], g2);
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) g[k] += g2[k];
+                }
                 const int tap = r * 3 + s;
 #pragma unroll
                 for (int k = 0; k < 8; ++k) {
@@ -644,14 +651,14 @@ extern "C" int dpt_maxpool3x3s2_fwd(const void* x, void* y, void* idx, int N, in
     DPT_CHECK_LAUNCH();
 }
 
-extern "C" int dpt_maxpool3x3s2_bwd(const void* dy, const void* idx, void* dx, int N, int H, int W,
-                                    int C, void* stream) {
+extern "C" int dpt_maxpool3x3s2_bwd(const void* dy, const void* dy2, const void* idx, void* dx,
+                                    int N, int H, int W, int C, void* stream) {
     if (C % 8 != 0) return DPT_ERR_SHAPE;
     const int P = (H + 2 - 3) / 2 + 1, Q = (W + 2 - 3) / 2 + 1;
     const long long total = static_cast<long long>(N) * H * W * (C / 8);
     maxpool_bwd_kernel<<<ew_grid(total, 1), kEwThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-        static_cast<const bf16x8*>(dy), static_cast<const uint8_t*>(idx), static_cast<bf16x8*>(dx),
-        N, H, W, C / 8, P, Q);
+        static_cast<const bf16x8*>(dy), static_cast<const bf16x8*>(dy2),
+        static_cast<const uint8_t*>(idx), static_cast<bf16x8*>(dx), N, H, W, C / 8, P, Q);
     DPT_CHECK_LAUNCH();
 }
 

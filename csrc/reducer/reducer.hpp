@@ -1,0 +1,106 @@
+// C++ gradient reducer over CUDA streams/events (no torch Reducer, no ProcessGroup on the hot
+// path).  Stands in for torch's c10d::Reducer as driven by the reference through
+// DistributedDataParallel (train_ddp.py:303-311; torch reducer.hpp:45-584):
+//   * parameters are grouped into size-capped buckets (first bucket small, then bucket_cap);
+//   * a bucket is launched the moment its last gradient is ready, strictly in bucket order;
+//   * the launch is ONE peer-memory all-reduce kernel (csrc/comm) on a dedicated high-priority
+//     stream, ordered after the producing kernels with an event, so it overlaps the rest of
+//     backward; 1/world averaging, AMP unscale, the non-finite check and optionally the SGD
+//     update are fused into that kernel;
+//   * gradients are born in the bucket (the arena slice), so there is no copy-in / copy-out;
+//   * per-bucket device timing (CUDA events) feeds the gradient-sync profiler.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <string>
+#include <vector>
+
+struct dpt_comm;
+
+namespace dptr {
+
+// Greedy size-capped bucket assignment, same contract as
+// torch.distributed._compute_bucket_assignment_by_size (reducer.hpp:586-598) for dense
+// same-device tensors: tensors are appended in order; when the accumulated bytes reach the
+// current limit the bucket is closed and the next limit (if any) becomes current.
+// `dtype_key[i]` separates tensors that may not share a bucket.
+std::vector<std::vector<int64_t>> compute_bucket_assignment(const std::vector<int64_t>& nbytes,
+                                                            const std::vector<int64_t>& dtype_key,
+                                                            const std::vector<int64_t>& limits);
+
+struct BucketSpec {
+    int64_t offset;  // first element (fp32) of the bucket inside the gradient arena
+    int64_t numel;   // padded to a multiple of 4
+    std::vector<int> params;
+};
+
+struct SgdFusion {
+    bool enabled = false;
+    std::vector<uintptr_t> param_ptrs;   // per rank: fp32 master arena base
+    std::vector<uintptr_t> shadow_ptrs;  // per rank: bf16 shadow arena base
+    uintptr_t momentum = 0;              // local fp32 momentum arena base
+    float lr = 0, mu = 0, wd = 0;
+    int nesterov = 0;
+};
+
+struct BucketTiming {
+    float ready_ms;  // bwd start -> bucket ready (compute stream)
+    float start_ms;  // bwd start -> all-reduce kernel start (comm stream)
+    float end_ms;    // bwd start -> all-reduce kernel end
+    int64_t bytes;
+};
+
+class Reducer {
+  public:
+    Reducer(std::vector<BucketSpec> buckets, int num_params, uintptr_t comm, int world,
+            std::vector<uintptr_t> grad_ptrs, std::vector<uintptr_t> found_inf_ptrs,
+            uintptr_t inv_scale_ptr, int ctas, bool profile);
+    ~Reducer();
+
+    void set_fusion(const SgdFusion& f) { fusion_ = f; }
+    void set_lr(float lr) { fusion_.lr = lr; }
+    void set_scale_options(uintptr_t inv_scale_ptr, bool check_finite) {
+        inv_scale_ = inv_scale_ptr;
+        check_finite_ = check_finite;
+    }
+    void set_enabled(bool on) { enabled_ = on; }  // no_sync()
+
+    void prepare_for_backward(uintptr_t compute_stream);
+    void mark_ready(int param_index, uintptr_t compute_stream);
+    // Makes `compute_stream` wait for every launched bucket.  Returns the number launched.
+    int finalize(uintptr_t compute_stream);
+    bool all_launched() const { return next_bucket_ == static_cast<int>(buckets_.size()); }
+
+    std::vector<BucketTiming> timings();  // synchronises; valid when profile == true
+    float backward_ms();                  // bwd start -> finalize on the compute stream
+    int64_t launches() const { return launches_; }
+    uintptr_t comm_stream() const { return reinterpret_cast<uintptr_t>(comm_stream_); }
+    const std::vector<BucketSpec>& buckets() const { return buckets_; }
+
+  private:
+    void launch_bucket(int b, cudaStream_t compute);
+
+    std::vector<BucketSpec> buckets_;
+    std::vector<int> param_bucket_;
+    std::vector<int> pending_;
+    std::vector<char> ready_;
+    std::vector<char> param_ready_;
+    int next_bucket_ = 0;
+    dpt_comm* comm_;
+    int world_;
+    std::vector<uintptr_t> grad_ptrs_, found_inf_ptrs_;
+    uintptr_t inv_scale_;
+    bool check_finite_ = false;
+    int ctas_;
+    bool profile_;
+    bool enabled_ = true;
+    bool armed_ = false;
+    SgdFusion fusion_;
+    cudaStream_t comm_stream_ = nullptr;
+    std::vector<cudaEvent_t> ev_ready_, ev_start_, ev_done_;
+    cudaEvent_t ev_bwd_start_ = nullptr, ev_bwd_end_ = nullptr;
+    int64_t launches_ = 0;
+};
+
+}  // namespace dptr

@@ -1,0 +1,166 @@
+"""Data pipeline: DistributedSampler, synthetic CIFAR-shaped data, CIFAR-10 file reader.
+
+Reference: train_ddp.py:81-150 (CIFAR-10 via torchvision, RandomCrop(32, pad 4) + HFlip +
+Normalize for train, Normalize for test, DistributedSampler(shuffle=True) for train only, the
+validation loader is NOT sharded, batch_size is per GPU, drop_last=False).
+"""
+from __future__ import annotations
+
+import math
+import os
+import pickle
+from typing import Iterator, Optional
+
+import numpy as np
+import torch
+from torch.utils.data import DataLoader, Dataset, Sampler
+
+CIFAR_MEAN = (0.4914, 0.4822, 0.4465)
+CIFAR_STD = (0.2470, 0.2435, 0.2616)
+
+
+class DistributedSampler(Sampler[int]):
+    """Index-stream-identical re-implementation of torch.utils.data.DistributedSampler
+    (torch/utils/data/distributed.py:66-157): ceil(len/world) samples per rank, a
+    ``randperm(len, Generator(seed + epoch))`` shared by all ranks, head-wrap padding,
+    ``indices[rank::world]``."""
+
+    def __init__(self, dataset, num_replicas: Optional[int] = None, rank: Optional[int] = None,
+                 shuffle: bool = True, seed: int = 0, drop_last: bool = False) -> None:
+        if num_replicas is None or rank is None:
+            import torch.distributed as dist
+            if not (dist.is_available() and dist.is_initialized()):
+                raise RuntimeError("Requires distributed package to be available")
+            num_replicas = dist.get_world_size() if num_replicas is None else num_replicas
+            rank = dist.get_rank() if rank is None else rank
+        if rank >= num_replicas or rank < 0:
+            raise ValueError(f"Invalid rank {rank}, rank should be in [0, {num_replicas - 1}]")
+        self.dataset = dataset
+        self.num_replicas = num_replicas
+        self.rank = rank
+        self.epoch = 0
+        self.drop_last = drop_last
+        n = len(self.dataset)
+        if self.drop_last and n % self.num_replicas != 0:
+            self.num_samples = math.ceil((n - self.num_replicas) / self.num_replicas)
+        else:
+            self.num_samples = math.ceil(n / self.num_replicas)
+        self.total_size = self.num_samples * self.num_replicas
+        self.shuffle = shuffle
+        self.seed = seed
+
+    def __iter__(self) -> Iterator[int]:
+        n = len(self.dataset)
+        if self.shuffle:
+            g = torch.Generator()
+            g.manual_seed(self.seed + self.epoch)
+            indices = torch.randperm(n, generator=g).tolist()
+        else:
+            indices = list(range(n))
+        if not self.drop_last:
+            padding = self.total_size - len(indices)
+            if padding <= len(indices):
+                indices += indices[:padding]
+            else:
+                indices += (indices * math.ceil(padding / len(indices)))[:padding]
+        else:
+            indices = indices[: self.total_size]
+        assert len(indices) == self.total_size
+        indices = indices[self.rank: self.total_size: self.num_replicas]
+        assert len(indices) == self.num_samples
+        return iter(indices)
+
+    def __len__(self) -> int:
+        return self.num_samples
+
+    def set_epoch(self, epoch: int) -> None:
+        self.epoch = epoch
+
+
+class SyntheticImages(Dataset):
+    """Deterministic random images with the post-transform CIFAR shape/dtype: float32
+    ``[3, S, S]`` (already normalised) and an int64 label."""
+
+    def __init__(self, size: int = 50000, image_size: int = 32, num_classes: int = 10,
+                 seed: int = 1234) -> None:
+        g = torch.Generator().manual_seed(seed)
+        # a modest pool reused cyclically keeps host memory small for ImageNet-sized images
+        pool = min(size, 4096 if image_size <= 64 else 512)
+        self.images = torch.randn(pool, 3, image_size, image_size, generator=g)
+        self.labels = torch.randint(0, num_classes, (size,), generator=g)
+        self.size = size
+        self.pool = pool
+
+    def __len__(self) -> int:
+        return self.size
+
+    def __getitem__(self, i: int):
+        return self.images[i % self.pool], self.labels[i]
+
+
+class CIFAR10Files(Dataset):
+    """CIFAR-10 from the standard ``cifar-10-batches-py`` pickles (no torchvision, no download)."""
+
+    def __init__(self, root: str, train: bool, augment: bool, seed: int = 0) -> None:
+        base = os.path.join(root, "cifar-10-batches-py")
+        names = [f"data_batch_{i}" for i in range(1, 6)] if train else ["test_batch"]
+        data, labels = [], []
+        for n in names:
+            with open(os.path.join(base, n), "rb") as f:
+                d = pickle.load(f, encoding="latin1")
+            data.append(np.asarray(d["data"], dtype=np.uint8).reshape(-1, 3, 32, 32))
+            labels.extend(d["labels"] if "labels" in d else d["fine_labels"])
+        self.data = torch.from_numpy(np.concatenate(data))
+        self.labels = torch.tensor(labels, dtype=torch.int64)
+        self.augment = augment
+        self.mean = torch.tensor(CIFAR_MEAN).view(3, 1, 1)
+        self.std = torch.tensor(CIFAR_STD).view(3, 1, 1)
+
+    @staticmethod
+    def available(root: str) -> bool:
+        return os.path.isfile(os.path.join(root, "cifar-10-batches-py", "data_batch_1"))
+
+    def __len__(self) -> int:
+        return self.data.shape[0]
+
+    def __getitem__(self, i: int):
+        img = self.data[i]
+        if self.augment:
+            # RandomCrop(32, padding=4) + RandomHorizontalFlip (train_ddp.py:91-96)
+            padded = torch.zeros(3, 40, 40, dtype=torch.uint8)
+            padded[:, 4:36, 4:36] = img
+            dy, dx = torch.randint(0, 9, (2,)).tolist()
+            img = padded[:, dy:dy + 32, dx:dx + 32]
+            if torch.rand(()) < 0.5:
+                img = img.flip(2)
+        x = img.float().div_(255.0)
+        x = (x - self.mean) / self.std
+        return x, self.labels[i]
+
+
+def build_datasets(args):
+    if getattr(args, "synthetic", False) or not CIFAR10Files.available(args.data_dir):
+        if not getattr(args, "synthetic", False):
+            print(f"[data] no CIFAR-10 files under {args.data_dir!r}: using synthetic data")
+        size = getattr(args, "synthetic_size", 50000)
+        img = getattr(args, "image_size", 32)
+        ncls = getattr(args, "num_classes", 10)
+        return (SyntheticImages(size, img, ncls, seed=1234),
+                SyntheticImages(max(size // 5, 1), img, ncls, seed=4321))
+    return (CIFAR10Files(args.data_dir, train=True, augment=True),
+            CIFAR10Files(args.data_dir, train=False, augment=False))
+
+
+def get_dataloaders(args, rank: int, world_size: int):
+    """(train_loader, val_loader, train_sampler) — reference train_ddp.py:81-150."""
+    train_ds, test_ds = build_datasets(args)
+    distributed = world_size > 1
+    sampler = DistributedSampler(train_ds, num_replicas=world_size, rank=rank,
+                                 shuffle=True) if distributed else None
+    pin = torch.cuda.is_available()
+    train_loader = DataLoader(train_ds, batch_size=args.batch_size, shuffle=(sampler is None),
+                              sampler=sampler, num_workers=args.workers, pin_memory=pin,
+                              drop_last=False)
+    val_loader = DataLoader(test_ds, batch_size=args.batch_size, shuffle=False,
+                            num_workers=args.workers, pin_memory=pin, drop_last=False)
+    return train_loader, val_loader, sampler

@@ -1,0 +1,188 @@
+"""TrainStep — the whole training step as one static kernel sequence, optionally one CUDA graph.
+
+Reference hot loop (train_ddp.py:195-226): H2D copy, zero_grad, autocast forward, loss,
+scaler.scale(loss).backward() (DDP all-reduce overlapped), scaler.step, scaler.update, then two
+``.item()`` host syncs for the running metrics — ~190 kernel launches, 3 host syncs, 2 buffer
+broadcasts and 3 NCCL all-reduces per step, all issued from Python.
+
+Here the same step is a fixed plan over preallocated buffers:
+    [H2D] -> memset(grad arena, BN stats) -> engine.forward -> fused CE (+loss scale, +metrics)
+          -> engine.backward (bucket all-reduces on the comm stream as buckets close)
+          -> flat optimizer kernel (reads found_inf on the device) -> scaler update kernel
+with no allocation and no host synchronisation, so it can be captured once
+(``cuda_graph=True``) and replayed with a single launch per step.  Loss / accuracy accumulate in
+a device-side ``metrics`` vector that the host reads only when it wants to print.
+"""
+from __future__ import annotations
+
+import torch
+
+from .models.resnet import ResNet
+from .parallel.ddp import DistributedDataParallel
+
+
+class TrainStep:
+    def __init__(self, model, optimizer, scaler=None, *, batch_shape, cuda_graph: bool = True,
+                 warmup: int = 2) -> None:
+        self.ddp = model if isinstance(model, DistributedDataParallel) else None
+        self.net = model.module if self.ddp is not None else model
+        if not isinstance(self.net, ResNet):
+            raise TypeError("TrainStep drives models with a native engine (dpt_b200 ResNet)")
+        from .ops import functional as Fn
+        self.Fn = Fn
+        self.optimizer = optimizer
+        self.scaler = scaler if (scaler is not None and scaler.is_enabled()) else None
+        self.arena = getattr(optimizer, "arena", None)
+        if self.arena is None or not getattr(optimizer, "_flat", False):
+            raise RuntimeError("TrainStep needs a flat-arena optimizer (dpt_b200.optim)")
+        dev = self.arena.param.device
+        self.device = dev
+        B = batch_shape[0]
+        K = self.net.fc.out_features
+        self.batch_shape = tuple(batch_shape)
+        self.x = torch.zeros(self.batch_shape, device=dev, dtype=torch.float32)
+        self.t = torch.zeros(B, device=dev, dtype=torch.int64)
+        self.loss = torch.zeros((), device=dev, dtype=torch.float32)
+        self.dlogits = torch.zeros((B, K), device=dev, dtype=torch.float32)
+        self.metrics = torch.zeros(3, device=dev, dtype=torch.float64)
+        self.net.train()
+        self.eng = self.net.engine_for(self.batch_shape, True)
+        self.fused_scaler = False
+        if self.scaler is not None:
+            self.scaler._lazy_init(dev)
+            if self.ddp is not None and self.ddp.backend == "native":
+                self.ddp.bind_scaler(self.scaler)
+                self.fused_scaler = True
+        # pinned ring for lagged loss reads (no per-step host stall)
+        self._ring = 4
+        self.loss_host = torch.zeros(self._ring, dtype=torch.float32).pin_memory() \
+            if dev.type == "cuda" else torch.zeros(self._ring)
+        self._events = [None] * self._ring
+        self._slot = 0
+        self.steps = 0
+        self.graph = None
+        self.launches_per_step = 0
+        if cuda_graph and dev.type == "cuda":
+            self._capture(warmup)
+
+    # ------------------------------------------------------------------ the step
+    def _body(self) -> None:
+        Fn = self.Fn
+        ddp = self.ddp
+        if ddp is not None:
+            ddp.sync_buffers()
+            ddp.prepare_for_backward()
+        self.arena.grad.zero_()
+        logits = self.eng.forward(self.x)
+        Fn.cross_entropy(logits, self.t, loss=self.loss, dlogits=self.dlogits,
+                         loss_scale=self.scaler.scale_tensor if self.scaler is not None else None,
+                         metrics=self.metrics)
+        self.eng.backward(self.dlogits)
+        if ddp is not None:
+            ddp.finalize_backward()
+        sc = self.scaler
+        if sc is None:
+            self.optimizer.step()
+        else:
+            if not self.fused_scaler:
+                Fn.amp_unscale(self.arena.grad, sc.inv_scale, sc.found_inf)
+            self.optimizer.step(found_inf=sc.found_inf)
+            sc.update()
+
+    def _snapshot(self):
+        snap = {"param": self.arena.param.clone(), "metrics": self.metrics.clone()}
+        snap["bufs"] = [b.clone() for b in self.net.buffers()]
+        snap["opt"] = {k: v.clone() for k, v in self._opt_state().items()}
+        if self.scaler is not None:
+            snap["scaler"] = (self.scaler._scale.clone(), self.scaler._growth_tracker.clone(),
+                              self.scaler._inv_scale.clone())
+        return snap
+
+    def _opt_state(self) -> dict:
+        o = self.optimizer
+        out = {}
+        for name in ("_momentum_flat", "_m", "_v", "_step"):
+            t = getattr(o, name, None)
+            if torch.is_tensor(t):
+                out[name] = t
+        return out
+
+    def _restore(self, snap) -> None:
+        self.arena.param.copy_(snap["param"])
+        self.arena.refresh_shadow()
+        self.metrics.copy_(snap["metrics"])
+        for b, s in zip(self.net.buffers(), snap["bufs"]):
+            b.copy_(s)
+        for k, v in self._opt_state().items():
+            if k in snap["opt"]:
+                v.copy_(snap["opt"][k])
+            else:
+                v.zero_()
+        if self.scaler is not None:
+            s, g, i = snap["scaler"]
+            self.scaler._scale.copy_(s)
+            self.scaler._growth_tracker.copy_(g)
+            self.scaler._inv_scale.copy_(i)
+            self.scaler.found_inf.zero_()
+
+    def _capture(self, warmup: int) -> None:
+        from .ops import _lib
+        snap = self._snapshot()
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(max(1, warmup)):
+                self._body()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        before = _lib.LAUNCHES
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, capture_error_mode="thread_local"):
+            self._body()
+        self.launches_per_step = _lib.LAUNCHES - before + 2  # + the two memsets
+        self.graph = g
+        self._restore(snap)
+        torch.cuda.synchronize()
+        if self.ddp is not None and self.ddp.comm is not None:
+            self.ddp.comm.check_health()
+
+    # ------------------------------------------------------------------ public call
+    def __call__(self, images: torch.Tensor, targets: torch.Tensor) -> torch.Tensor:
+        """Runs one optimisation step on a (host-pinned or device) batch; returns the device
+        loss scalar (valid until the next call).  Never blocks the host."""
+        self.x.copy_(images, non_blocking=True)
+        self.t.copy_(targets, non_blocking=True)
+        if self.graph is not None:
+            self.graph.replay()
+        else:
+            from .ops import _lib
+            before = _lib.LAUNCHES
+            self._body()
+            self.launches_per_step = _lib.LAUNCHES - before + 2
+        slot = self._slot
+        self.loss_host[slot:slot + 1].copy_(self.loss.view(1), non_blocking=True)
+        if self.device.type == "cuda":
+            ev = self._events[slot]
+            if ev is None:
+                ev = self._events[slot] = torch.cuda.Event()
+            ev.record()
+        self._slot = (slot + 1) % self._ring
+        self.steps += 1
+        return self.loss
+
+    def read_loss(self, lag: int = 1) -> float | None:
+        """Host value of the loss from ``lag`` steps ago (waits only for that step)."""
+        if self.steps <= lag:
+            return None
+        slot = (self._slot - 1 - lag) % self._ring
+        ev = self._events[slot]
+        if ev is not None:
+            ev.synchronize()
+        return float(self.loss_host[slot])
+
+    def read_metrics(self, reset: bool = False) -> tuple[float, float, float]:
+        """(sum of loss*B, #correct, #samples) accumulated on the device since the last reset."""
+        m = self.metrics.tolist()
+        if reset:
+            self.metrics.zero_()
+        return m[0], m[1], m[2]

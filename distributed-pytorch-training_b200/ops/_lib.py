@@ -32,7 +32,7 @@ _SIGS = {
     "dpt_bn_bwd_reduce": [vp, vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, vp],
     "dpt_bn_bwd_apply": [vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, vp],
     "dpt_maxpool3x3s2_fwd": [vp, vp, vp, i32, i32, i32, i32, vp],
-    "dpt_maxpool3x3s2_bwd": [vp, vp, vp, i32, i32, i32, i32, vp],
+    "dpt_maxpool3x3s2_bwd": [vp, vp, vp, vp, i32, i32, i32, i32, vp],
     "dpt_head_fwd": [vp, vp, vp, vp, vp, i32, i32, i32, i32, vp],
     "dpt_head_bwd": [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, vp],
     "dpt_cross_entropy": [vp, vp, vp, vp, vp, vp, i32, i32, vp],

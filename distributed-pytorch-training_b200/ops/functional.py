@@ -138,11 +138,11 @@ def maxpool_fwd(x, *, out=None, idx=None):
     return out, idx
 
 
-def maxpool_bwd(dy, idx, x_shape, *, out=None):
+def maxpool_bwd(dy, idx, x_shape, *, out=None, dy2=None):
     N, H, W, C_ = x_shape
     if out is None:
         out = torch.empty(x_shape, device=dy.device, dtype=BF16)
-    call("dpt_maxpool3x3s2_bwd", ptr(dy), ptr(idx), ptr(out), N, H, W, C_, stream())
+    call("dpt_maxpool3x3s2_bwd", ptr(dy), ptr(dy2), ptr(idx), ptr(out), N, H, W, C_, stream())
     count()
     return out
 

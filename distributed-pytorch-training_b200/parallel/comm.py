@@ -1,0 +1,179 @@
+"""Communicator: symmetric (peer-mapped) device memory + the NVLink peer-memory collectives.
+
+This is the data plane that stands in for ProcessGroupNCCL on the gradient path (reference
+train_ddp.py:65 ``init_process_group("nccl")`` -> DDP Reducer -> ncclAllReduce).  The torch
+process group is still used, but only to *bootstrap*: CUDA IPC handles of each rank's arenas are
+exchanged once through it (``all_gather_object``); after that every collective is one of the
+kernels in csrc/comm/p2p_collectives.cu reading / writing peers' memory directly.
+
+Scope: one node, <= 8 GPUs, all peer-accessible (NVSwitch).  Anything else uses the
+torch.distributed fallback in ``parallel/ddp.py``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+
+import torch
+import torch.distributed as dist
+
+from ..ops import _lib
+
+
+class _RawCuda:
+    """Expose a raw device allocation through __cuda_array_interface__ (zero-copy torch view)."""
+
+    def __init__(self, ptr: int, nbytes: int) -> None:
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1",
+                                         "data": (ptr, False), "version": 2}
+
+
+@dataclass
+class SymmBuffer:
+    """One allocation per rank, same size everywhere; ``peer_ptrs[r]`` is this process's mapping
+    of rank r's copy (``peer_ptrs[rank]`` is the local allocation)."""
+    nbytes: int
+    local: torch.Tensor          # uint8 view of the local allocation
+    peer_ptrs: list[int]
+    _opened: list[int] = field(default_factory=list)
+
+    def ptrs(self, byte_offset: int = 0):
+        arr = (C.c_void_p * len(self.peer_ptrs))()
+        for i, p in enumerate(self.peer_ptrs):
+            arr[i] = p + byte_offset
+        return arr
+
+    def view(self, dtype: torch.dtype, byte_offset: int = 0, numel: int | None = None):
+        t = self.local[byte_offset:]
+        item = torch.empty((), dtype=dtype).element_size()
+        n = (t.numel() // item) if numel is None else numel
+        return t[: n * item].view(dtype)
+
+
+class Communicator:
+    def __init__(self, group=None, timeout_s: float = 30.0) -> None:
+        if not torch.cuda.is_available():
+            raise RuntimeError("the native communicator needs CUDA devices")
+        self.group = group
+        if dist.is_available() and dist.is_initialized():
+            self.rank = dist.get_rank(group)
+            self.world = dist.get_world_size(group)
+        else:
+            self.rank, self.world = 0, 1
+        if self.world > 8:
+            raise RuntimeError("native backend is single-node (<= 8 GPUs); use --backend nccl")
+        self.lib = _lib.lib()
+        self.device = torch.device("cuda", torch.cuda.current_device())
+        self._buffers: list[SymmBuffer] = []
+        self.flags = self.alloc(int(self.lib.dpt_comm_flag_bytes()))
+        handle = C.c_void_p()
+        _lib.check(self.lib.dpt_comm_create(self.rank, self.world, self.flags.ptrs(), float(timeout_s),
+                                            C.byref(handle)), "dpt_comm_create")
+        self.handle = handle
+        # tiny symmetric scratch: found_inf word (+ room for packed scalar reductions)
+        self.scalars = self.alloc(256)
+        self.found_inf = self.scalars.view(torch.float32, 0, 1)[0]
+        self.launches = 0
+        torch.cuda.synchronize()
+        self.host_barrier()
+
+    # ------------------------------------------------------------------ memory
+    def alloc(self, nbytes: int) -> SymmBuffer:
+        nbytes = (int(nbytes) + 255) // 256 * 256
+        ptr = C.c_void_p()
+        handle = (C.c_ubyte * 64)()
+        _lib.check(self.lib.dpt_symm_alloc(nbytes, C.byref(ptr), handle), "dpt_symm_alloc")
+        local = torch.as_tensor(_RawCuda(ptr.value, nbytes), device=self.device)
+        peer_ptrs = [0] * self.world
+        peer_ptrs[self.rank] = ptr.value
+        opened = []
+        if self.world > 1:
+            mine = (self.device.index, bytes(handle))
+            everyone = [None] * self.world
+            dist.all_gather_object(everyone, mine, group=self.group)
+            for r, (dev, h) in enumerate(everyone):
+                if r == self.rank:
+                    continue
+                p = C.c_void_p()
+                buf = (C.c_ubyte * 64).from_buffer_copy(h)
+                _lib.check(self.lib.dpt_symm_open(buf, C.byref(p)), f"dpt_symm_open(rank {r})")
+                peer_ptrs[r] = p.value
+                opened.append(p.value)
+        sb = SymmBuffer(nbytes, local, peer_ptrs, opened)
+        self._buffers.append(sb)
+        return sb
+
+    def host_barrier(self) -> None:
+        if self.world > 1:
+            dist.barrier(group=self.group)
+
+    # ------------------------------------------------------------------ collectives
+    def allreduce_(self, buf: SymmBuffer, byte_offset: int, numel: int, *, scale: float | None = None,
+                   inv_scale: torch.Tensor | None = None, check_finite: bool = False,
+                   ctas: int = 0, stream: int | None = None, sgd: dict | None = None) -> None:
+        """In-place fused all-reduce of ``numel`` fp32 values at ``byte_offset`` of ``buf``."""
+        if scale is None:
+            scale = 1.0 / self.world
+        st = _lib.stream() if stream is None else stream
+        fi = self.scalars.ptrs(0) if check_finite else None
+        if sgd is not None:
+            args = (sgd["param"].ptrs(sgd["byte_offset"]), sgd["shadow"].ptrs(sgd["byte_offset"] // 2),
+                    sgd["momentum"], sgd["lr"], sgd["momentum_coef"], sgd["weight_decay"],
+                    int(sgd.get("nesterov", False)))
+        else:
+            args = (None, None, None, 0.0, 0.0, 0.0, 0)
+        _lib.check(self.lib.dpt_allreduce_fused(self.handle, buf.ptrs(byte_offset), numel, scale,
+                                                _lib.ptr(inv_scale), fi, *args, ctas, st),
+                   "dpt_allreduce_fused")
+        self.launches += 1
+        _lib.count()
+
+    def allreduce_oneshot(self, buf: SymmBuffer, byte_offset: int, out: torch.Tensor, *,
+                          scale: float | None = None, ctas: int = 0, stream: int | None = None):
+        if scale is None:
+            scale = 1.0 / self.world
+        st = _lib.stream() if stream is None else stream
+        _lib.check(self.lib.dpt_allreduce_oneshot(self.handle, buf.ptrs(byte_offset), out.data_ptr(),
+                                                  out.numel(), scale, None, None, ctas, st),
+                   "dpt_allreduce_oneshot")
+        self.launches += 1
+        _lib.count()
+        return out
+
+    def broadcast_(self, buf: SymmBuffer, byte_offset: int, nbytes: int, src: int = 0,
+                   ctas: int = 0, stream: int | None = None) -> None:
+        if self.world == 1:
+            return
+        st = _lib.stream() if stream is None else stream
+        _lib.check(self.lib.dpt_broadcast(self.handle, buf.ptrs(byte_offset), nbytes, src, ctas, st),
+                   "dpt_broadcast")
+        self.launches += 1
+        _lib.count()
+
+    def barrier(self, stream: int | None = None) -> None:
+        st = _lib.stream() if stream is None else stream
+        _lib.check(self.lib.dpt_barrier(self.handle, st), "dpt_barrier")
+
+    # ------------------------------------------------------------------ health
+    def check_health(self) -> None:
+        """Raises when a device-side flag wait timed out (a peer died or stalled)."""
+        code = int(self.lib.dpt_comm_error(self.handle))
+        if code:
+            peer = (code >> 24) & 0x7F
+            raise RuntimeError(f"[rank {self.rank}] peer-memory collective timed out waiting for "
+                               f"rank {peer} (epoch {code & 0xFFFFFF}); a rank died or stalled")
+
+    def close(self) -> None:
+        if getattr(self, "handle", None) is None:
+            return
+        torch.cuda.synchronize()
+        self.host_barrier()
+        for sb in self._buffers:
+            for p in sb._opened:
+                self.lib.dpt_symm_close(p)
+        self.host_barrier()
+        for sb in self._buffers:
+            self.lib.dpt_symm_free(sb.peer_ptrs[self.rank])
+        self._buffers.clear()
+        self.lib.dpt_comm_destroy(self.handle)
+        self.handle = None

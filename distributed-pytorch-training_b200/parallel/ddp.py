@@ -1,0 +1,489 @@
+"""DistributedDataParallel — DDP-compatible wrapper over the native gradient path.
+
+API parity with ``torch.nn.parallel.DistributedDataParallel`` as the reference uses it
+(train_ddp.py:303-311: ``DDP(model, device_ids=[local_rank], output_device=local_rank,
+find_unused_parameters=False)``): same constructor keywords, ``.module``, ``module.``-prefixed
+``state_dict``, ``no_sync()``, ``register_comm_hook()``, ``join()``, ``_get_ddp_logging_data()``;
+construction broadcasts rank 0's parameters and buffers, every training forward re-broadcasts
+rank 0's buffers (``broadcast_buffers=True``, torch distributed.py:2214-2257).
+
+What is different underneath:
+  * parameters / gradients live in flat symmetric arenas mapped by every peer over NVLink;
+  * buckets are contiguous arena slices planned once in gradient-ready order (static graph);
+  * ``backend="native"``: the C++ reducer (csrc/reducer) launches one fused peer-memory
+    all-reduce kernel per bucket on a high-priority stream as soon as the bucket's last
+    gradient is produced; parameter/buffer broadcast is a P2P-store kernel;
+  * ``backend="nccl"|"gloo"``: same bucketing, collectives through torch.distributed — the
+    in-repo baseline and the CPU plumbing path.
+"""
+from __future__ import annotations
+
+import contextlib
+import hashlib
+from typing import Any, Callable, Optional
+
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+
+from .arena import ParamArena
+from .bucket import (DEFAULT_BUCKET_BYTES_CAP, DEFAULT_FIRST_BUCKET_BYTES, ext, ext_available,
+                     plan_arena_buckets)
+
+
+class GradBucket:
+    """Bucket view handed to communication hooks (torch c10d/comm.hpp:20-93 surface)."""
+
+    def __init__(self, index, buffer, grads, params, is_last):
+        self._index, self._buffer, self._grads, self._params, self._is_last = (
+            index, buffer, grads, params, is_last)
+
+    def index(self):
+        return self._index
+
+    def buffer(self):
+        return self._buffer
+
+    def gradients(self):
+        return self._grads
+
+    def parameters(self):
+        return self._params
+
+    def is_last(self):
+        return self._is_last
+
+    def set_buffer(self, t):
+        self._buffer.copy_(t)
+
+
+class _TorchReducer:
+    """Bucketed reducer over torch.distributed collectives (gloo / nccl).  Python hooks, async
+    all_reduce per bucket in bucket order, finalize waits on the works."""
+
+    def __init__(self, arena: ParamArena, plans, group, world):
+        self.arena, self.plans, self.group, self.world = arena, plans, group, world
+        self.param_bucket = {}
+        for b, pl in enumerate(plans):
+            for i in pl["params"]:
+                self.param_bucket[i] = b
+        self.enabled = True
+        self.armed = False
+        self.comm_hook: Optional[tuple[Any, Callable]] = None
+        self.works: list = []
+        self.launch_count = 0
+        self._cb_queued = False
+        for i, p in enumerate(arena.order):
+            p.register_post_accumulate_grad_hook(self._make_hook(i))
+
+    def _make_hook(self, i):
+        def hook(p):
+            slot = self.arena.grad_view(p)
+            if p.grad is not None and p.grad.data_ptr() != slot.data_ptr():
+                slot.copy_(p.grad)
+                p.grad = slot
+            self.mark_ready(i, from_autograd=True)
+        return hook
+
+    def prepare_for_backward(self):
+        self.pending = [len(pl["params"]) for pl in self.plans]
+        self.ready = [False] * len(self.plans)
+        self.seen = set()
+        self.next_bucket = 0
+        self.works = []
+        self.armed = True
+        self._cb_queued = False
+
+    def mark_ready(self, i, from_autograd=False):
+        if not (self.enabled and self.armed) or i in self.seen:
+            return
+        if from_autograd and not self._cb_queued:
+            self._cb_queued = True
+            torch.autograd.Variable._execution_engine.queue_callback(self.finalize)
+        self.seen.add(i)
+        b = self.param_bucket[i]
+        self.pending[b] -= 1
+        if self.pending[b] == 0:
+            self.ready[b] = True
+            while self.next_bucket < len(self.plans) and self.ready[self.next_bucket]:
+                self._launch(self.next_bucket)
+                self.next_bucket += 1
+
+    def _launch(self, b):
+        pl = self.plans[b]
+        buf = self.arena.grad[pl["offset"]: pl["offset"] + pl["numel"]]
+        self.launch_count += 1
+        if self.comm_hook is not None:
+            state, hook = self.comm_hook
+            params = [self.arena.order[i] for i in pl["params"]]
+            gb = GradBucket(b, buf, [self.arena.grad_view(p) for p in params], params,
+                            b == len(self.plans) - 1)
+            fut = hook(state, gb)
+            self.works.append(("future", fut, buf))
+            return
+        buf.div_(self.world)  # torch divides before the all-reduce too (default_comm_hooks.hpp:38-52)
+        self.works.append(("work", dist.all_reduce(buf, group=self.group, async_op=True), buf))
+
+    def finalize(self):
+        if not self.armed:
+            return 0
+        if self.enabled:
+            while self.next_bucket < len(self.plans):
+                self._launch(self.next_bucket)
+                self.next_bucket += 1
+        for kind, w, buf in self.works:
+            if kind == "work":
+                w.wait()
+            else:
+                res = w.wait() if hasattr(w, "wait") else w
+                res = res[0] if isinstance(res, (list, tuple)) else res
+                if torch.is_tensor(res) and res.data_ptr() != buf.data_ptr():
+                    buf.copy_(res)
+        n = len(self.works)
+        self.works = []
+        self.armed = False
+        return n
+
+
+class DistributedDataParallel(nn.Module):
+    def __init__(self, module: nn.Module, device_ids=None, output_device=None, dim=0,
+                 broadcast_buffers=True, init_sync=True, process_group=None, bucket_cap_mb=None,
+                 find_unused_parameters=False, check_reduction=False,
+                 gradient_as_bucket_view=True, static_graph=True, *, backend: str = "native",
+                 comm=None, fused_optimizer=False, profile=False, comm_ctas: int = 0,
+                 comm_timeout: float = 30.0, first_bucket_mb: float = 1.0):
+        super().__init__()
+        self.module = module
+        self.device_ids = device_ids
+        self.output_device = output_device
+        self.dim = dim
+        self.broadcast_buffers = broadcast_buffers
+        self.find_unused_parameters = find_unused_parameters
+        self.gradient_as_bucket_view = gradient_as_bucket_view
+        self.static_graph = static_graph
+        self.process_group = process_group
+        self.require_backward_grad_sync = True
+        self.require_forward_param_sync = True
+        params = [(n, p) for n, p in module.named_parameters() if p.requires_grad]
+        if not params:
+            raise RuntimeError("DistributedDataParallel is not needed when a module doesn't have "
+                               "any parameter that requires a gradient.")
+        self.device = params[0][1].device
+        if dist.is_available() and dist.is_initialized():
+            self.rank = dist.get_rank(process_group)
+            self.world_size = dist.get_world_size(process_group)
+        else:
+            self.rank, self.world_size = 0, 1
+        cuda = self.device.type == "cuda"
+        if backend in (None, "auto"):
+            backend = "native"
+        if backend == "native" and (not cuda or not ext_available()):
+            backend = "gloo" if not cuda else "nccl"
+        self.backend = backend
+        self.bucket_bytes_cap = int((bucket_cap_mb if bucket_cap_mb is not None else 25) * 1024 * 1024)
+        self.first_bucket_bytes = int(first_bucket_mb * 1024 * 1024)
+        self.profile = profile
+        self.fused_optimizer = fused_optimizer
+        self._fusion_cfg = None
+        self._iter = 0
+        self._logging: dict = {}
+
+        self._verify_params_across_processes(params)
+        # ---- arenas ---------------------------------------------------------------------
+        self.comm = comm
+        if backend == "native" and self.comm is None:
+            from .comm import Communicator
+            self.comm = Communicator(process_group, timeout_s=comm_timeout)
+        self.arena = ParamArena(params, self.device, comm=self.comm if backend == "native" else None)
+        self._buffer_arena_init()
+        if init_sync:
+            self._sync_module_states()
+        # ---- reducer --------------------------------------------------------------------
+        self.plans = plan_arena_buckets(self.arena, self.bucket_bytes_cap, self.first_bucket_bytes)
+        self._param_index = {id(p): i for i, p in enumerate(self.arena.order)}
+        self._cb_queued = False
+        if backend == "native":
+            E = ext()
+            specs = []
+            for pl in self.plans:
+                s = E.BucketSpec()
+                s.offset, s.numel, s.params = pl["offset"], pl["numel"], pl["params"]
+                specs.append(s)
+            found = [p for p in self.comm.scalars.peer_ptrs]
+            self.reducer = E.Reducer(specs, len(self.arena.order), self.comm.handle.value or 0,
+                                     self.world_size, list(self.arena.grad_buf.peer_ptrs), found, 0,
+                                     comm_ctas, bool(profile))
+            E.register_hooks(self.reducer, list(self.arena.order),
+                             [self.arena.grad_view(p) for p in self.arena.order])
+        else:
+            self.reducer = _TorchReducer(self.arena, self.plans, process_group, self.world_size) \
+                if self.world_size > 1 else None
+        if hasattr(module, "_grad_sink"):
+            module._grad_sink = self._sink
+
+    # ------------------------------------------------------------------ construction helpers
+    def _verify_params_across_processes(self, params) -> None:
+        """torch verifies shapes with an allgather + broadcast (reducer.hpp:602-605); a digest
+        through the object store is enough."""
+        if self.world_size == 1:
+            return
+        desc = ";".join(f"{n}:{tuple(p.shape)}:{p.dtype}" for n, p in params)
+        digest = hashlib.sha1(desc.encode()).hexdigest()
+        gathered = [None] * self.world_size
+        dist.all_gather_object(gathered, digest, group=self.process_group)
+        if any(d != gathered[0] for d in gathered):
+            raise RuntimeError("DDP expects same model across all ranks, but parameter "
+                               f"shapes/dtypes differ (digests {gathered})")
+
+    def _buffer_arena_init(self) -> None:
+        """Module buffers (BN running stats, num_batches_tracked) are moved into one flat
+        (symmetric, when native) allocation so the per-forward buffer sync is one kernel."""
+        bufs = [(n, b) for n, b in self.module.named_buffers() if b is not None]
+        self._buffers = bufs
+        self.buffer_buf = None
+        if not bufs:
+            return
+        sizes = [(b.numel() * b.element_size() + 15) // 16 * 16 for _, b in bufs]
+        total = sum(sizes)
+        if self.backend == "native":
+            self.buffer_buf = self.comm.alloc(total)
+            flat = self.buffer_buf.local
+        else:
+            flat = torch.zeros(total, dtype=torch.uint8, device=self.device)
+        self._buffer_flat = flat
+        self._buffer_bytes = total
+        off = 0
+        with torch.no_grad():
+            for (name, b), sz in zip(bufs, sizes):
+                n = b.numel() * b.element_size()
+                view = flat[off: off + n].view(b.dtype).view(b.shape)
+                view.copy_(b)
+                b.data = view
+                off += sz
+
+    def _sync_module_states(self) -> None:
+        """Broadcast rank 0's parameters and buffers (torch distributed.py:883-890)."""
+        if self.world_size == 1:
+            return
+        if self.backend == "native":
+            torch.cuda.current_stream().synchronize()
+            self.comm.broadcast_(self.arena.param_buf, 0, self.arena.numel * 4, src=0)
+            if self.buffer_buf is not None:
+                self.comm.broadcast_(self.buffer_buf, 0, self._buffer_bytes, src=0)
+            self.arena.refresh_shadow()
+            torch.cuda.current_stream().synchronize()
+            self.comm.check_health()
+        else:
+            dist.broadcast(self.arena.param, src=self._global_src(), group=self.process_group)
+            if self._buffers:
+                dist.broadcast(self._buffer_flat, src=self._global_src(), group=self.process_group)
+            self.arena.refresh_shadow()
+
+    def _global_src(self) -> int:
+        return dist.get_global_rank(self.process_group, 0) if self.process_group is not None else 0
+
+    def sync_after_load(self) -> None:
+        """Call after ``load_state_dict``: refresh the shadow weights and re-sync replicas."""
+        self.arena.refresh_shadow()
+        self._sync_module_states()
+
+    # ------------------------------------------------------------------ fused optimizer
+    def enable_fused_sgd(self, optimizer) -> bool:
+        """Apply the SGD update inside the all-reduce kernel (K-AR-F2).  Only valid without
+        dynamic loss scaling (bf16 / FP32); returns False when not applicable."""
+        if self.backend != "native" or self.world_size == 1:
+            return False
+        g = optimizer.param_groups[0]
+        if g.get("dampening", 0) != 0 or g["momentum"] == 0:
+            return False
+        E = ext()
+        f = E.SgdFusion()
+        f.enabled = True
+        f.param_ptrs = list(self.arena.param_buf.peer_ptrs)
+        f.shadow_ptrs = list(self.arena.shadow_buf.peer_ptrs)
+        f.momentum = optimizer._flat_momentum().data_ptr()
+        f.lr, f.mu, f.wd, f.nesterov = g["lr"], g["momentum"], g["weight_decay"], int(g["nesterov"])
+        self.reducer.set_fusion(f)
+        optimizer.skip_update = True
+        self._fusion_cfg = f
+        return True
+
+    def bind_scaler(self, scaler) -> None:
+        """Fuse AMP unscale + non-finite check into the all-reduce epilogue."""
+        if scaler is None or not scaler.is_enabled():
+            return
+        if self.backend == "native":
+            scaler.bind_found_inf(self.comm.found_inf)
+            self.reducer.set_scale_options(scaler.inv_scale.data_ptr(), True)
+            self._scaler_fused = True
+
+    # ------------------------------------------------------------------ gradient path
+    def _stream(self) -> int:
+        return torch.cuda.current_stream().cuda_stream
+
+    def _sink(self, params) -> None:
+        """Called by engines that write gradients straight into the arena."""
+        if self.reducer is None or not self.require_backward_grad_sync:
+            return
+        if self.backend == "native":
+            st = self._stream()
+            for p in params:
+                self.reducer.mark_ready(self._param_index[id(p)], st)
+        else:
+            for p in params:
+                self.reducer.mark_ready(self._param_index[id(p)])
+
+    def prepare_for_backward(self) -> None:
+        if self.reducer is None:
+            return
+        if self.backend == "native":
+            self.reducer.set_enabled(self.require_backward_grad_sync)
+            self.reducer.prepare_for_backward(self._stream())
+        else:
+            self.reducer.enabled = self.require_backward_grad_sync
+            self.reducer.prepare_for_backward()
+
+    def finalize_backward(self) -> int:
+        """Make the compute stream wait for all bucket kernels (torch: finalize_backward)."""
+        if self.reducer is None:
+            return 0
+        if self.backend == "native":
+            return self.reducer.finalize(self._stream())
+        return self.reducer.finalize()
+
+    def sync_buffers(self) -> None:
+        if not (self.broadcast_buffers and self._buffers and self.world_size > 1):
+            return
+        if self.backend == "native":
+            self.comm.broadcast_(self.buffer_buf, 0, self._buffer_bytes, src=0, ctas=1)
+        else:
+            dist.broadcast(self._buffer_flat, src=self._global_src(), group=self.process_group)
+
+    def forward(self, *inputs, **kwargs):
+        grad_mode = torch.is_grad_enabled() and self.module.training
+        if grad_mode:
+            self._iter += 1
+            if self.require_forward_param_sync:
+                self.sync_buffers()
+            self.prepare_for_backward()
+            if self.reducer is not None and self.backend == "native":
+                # queue finalize at the end of this backward pass from the first gradient hook
+                self._arm_autograd_finalize()
+        elif self.require_forward_param_sync and self.module.training is False and self._iter > 0:
+            # first eval forward after training syncs buffers once (torch distributed.py:1637-1650)
+            self.sync_buffers()
+            self.require_forward_param_sync = False
+        out = self.module(*inputs, **kwargs)
+        if grad_mode:
+            self.require_forward_param_sync = True
+        return out
+
+    def _arm_autograd_finalize(self) -> None:
+        """Attach a backward-time callback: a zero-cost identity autograd node on the output
+        is avoided; instead the first gradient event queues the engine callback."""
+        self._cb_queued = False
+        if not hasattr(self, "_finalize_hook_installed"):
+            self._finalize_hook_installed = True
+            for p in self.arena.order:
+                p.register_hook(self._queue_finalize_once)
+            mod = self.module
+            if hasattr(mod, "_grad_sink"):
+                orig = self._sink
+
+                def sink(params, _orig=orig):
+                    self._queue_finalize_once(None)
+                    _orig(params)
+                mod._grad_sink = sink
+
+    def _queue_finalize_once(self, grad):
+        if not self._cb_queued and self.require_backward_grad_sync:
+            try:
+                torch.autograd.Variable._execution_engine.queue_callback(self._autograd_finalize)
+                self._cb_queued = True
+            except RuntimeError:
+                pass  # not inside an autograd backward (direct engine use): caller finalizes
+        return grad
+
+    def _autograd_finalize(self):
+        self._cb_queued = False
+        self.finalize_backward()
+
+    @contextlib.contextmanager
+    def no_sync(self):
+        old = self.require_backward_grad_sync
+        self.require_backward_grad_sync = False
+        try:
+            yield
+        finally:
+            self.require_backward_grad_sync = old
+
+    @contextlib.contextmanager
+    def join(self, *args, **kwargs):
+        """Uneven-input join is not needed with DistributedSampler's padding; accepted for API
+        compatibility and behaves as a plain context."""
+        yield
+
+    def register_comm_hook(self, state, hook) -> None:
+        """Escape hatch with torch's GradBucket surface.  Custom hooks run on the
+        torch.distributed reducer (the native fused kernels are the default 'hook')."""
+        if self.world_size == 1:
+            return
+        if not isinstance(self.reducer, _TorchReducer):
+            self.reducer = _TorchReducer(self.arena, self.plans, self.process_group, self.world_size)
+            self.backend = "nccl" if self.device.type == "cuda" else "gloo"
+            if hasattr(self.module, "_grad_sink"):
+                self.module._grad_sink = self._sink
+        self.reducer.comm_hook = (state, hook)
+
+    # ------------------------------------------------------------------ introspection
+    def bucket_sizes(self):
+        return [pl["bytes"] for pl in self.plans]
+
+    def _get_ddp_logging_data(self) -> dict:
+        """Static + runtime statistics under the key names torch's DDP Logger uses
+        (logger.hpp:42-138)."""
+        order = self.arena.order
+        data = {
+            "world_size": self.world_size,
+            "rank": self.rank,
+            "backend_name": self.backend,
+            "num_parameter_tensors": len(order),
+            "total_parameter_size_bytes": sum(p.numel() * 4 for p in order),
+            "bucket_cap_bytes": self.bucket_bytes_cap,
+            "bucket_sizes": ", ".join(str(b) for b in self.bucket_sizes()),
+            "rebuilt_bucket_sizes": ", ".join(str(b) for b in self.bucket_sizes()),
+            "has_rebuilt_buckets": 1,
+            "broadcast_buffers": int(self.broadcast_buffers),
+            "gradient_as_bucket_view": 1,
+            "find_unused_parameters": int(self.find_unused_parameters),
+            "static_graph": int(self.static_graph),
+            "has_sync_bn": 0,
+            "iteration": self._iter,
+        }
+        data.update(self._logging)
+        return data
+
+    def sync_timings(self) -> dict:
+        """Per-bucket device timings of the last backward (needs profile=True, eager mode)."""
+        if self.backend != "native" or self.reducer is None or not self.profile:
+            return {}
+        ts = self.reducer.timings()
+        return {"backward_ms": self.reducer.backward_ms(),
+                "buckets": [{"ready_ms": t.ready_ms, "start_ms": t.start_ms, "end_ms": t.end_ms,
+                             "bytes": t.bytes} for t in ts]}
+
+    def shutdown(self) -> None:
+        if self.comm is not None:
+            self.comm.close()
+            self.comm = None
+
+
+def maybe_wrap_ddp(model, device, local_rank, **kwargs):
+    """Reference train_ddp.py:303-311: wrap only when distributed."""
+    from ..runtime import is_distributed
+    if is_distributed() and dist.is_initialized():
+        if device.type == "cuda":
+            return DistributedDataParallel(model, device_ids=[local_rank], output_device=local_rank,
+                                           find_unused_parameters=False, **kwargs)
+        return DistributedDataParallel(model, find_unused_parameters=False, **kwargs)
+    return model

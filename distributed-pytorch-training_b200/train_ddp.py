@@ -1,0 +1,99 @@
+"""Entry point with the reference's orchestration (train_ddp.py:314-386): parse flags, mkdir,
+process-group bootstrap, ``seed + rank`` seeding, device pick, loaders, model, DDP wrap, CE loss,
+SGD(lr .1, momentum .9, wd 5e-4, constant LR), GradScaler(enabled=--amp), rank-0 CSV, epoch loop
+train -> validate -> print -> CSV, teardown.  Run with ``python`` (single process) or
+``torchrun --nproc_per_node=N`` / ``dpt_b200.launcher.spawn``.
+"""
+from __future__ import annotations
+
+from pathlib import Path
+
+import torch
+
+from . import metrics as M
+from .amp import GradScaler
+from .checkpoint import load_checkpoint, save_checkpoint
+from .cli import parse_args
+from .data import get_dataloaders
+from .models.resnet import build_model
+from .ops.loss import CrossEntropyLoss
+from .optim import build_optimizer
+from .parallel.ddp import DistributedDataParallel, maybe_wrap_ddp
+from .profiler import GradSyncProfiler
+from .runtime import cleanup_distributed, pick_device, set_seed, setup_distributed
+from .trainer import train_one_epoch, validate
+
+
+def main(argv=None):
+    args = parse_args(argv)
+    Path(args.output_dir).mkdir(parents=True, exist_ok=True)
+
+    rank, world_size, local_rank = setup_distributed(args.backend)
+    set_seed(args.seed, rank)
+    device = pick_device(local_rank)
+    if rank == 0:
+        print(M.banner(device, world_size, args.amp))
+
+    train_loader, val_loader, train_sampler = get_dataloaders(args, rank, world_size)
+
+    model = build_model(device, args.arch, args.num_classes)
+    model = maybe_wrap_ddp(model, device, local_rank, backend=args.backend,
+                           bucket_cap_mb=args.bucket_cap_mb, profile=args.profile_sync,
+                           comm_timeout=args.comm_timeout)
+    ddp = model if isinstance(model, DistributedDataParallel) else None
+
+    criterion = CrossEntropyLoss().to(device)
+    optimizer = build_optimizer(args.optimizer, model.parameters(), args.lr, args.momentum,
+                                args.weight_decay)
+    fp16 = args.amp and args.amp_dtype == "fp16"
+    scaler = GradScaler(device=device, enabled=fp16 and device.type == "cuda")
+    if ddp is not None and args.fused_optimizer and not scaler.is_enabled() and args.optimizer == "sgd":
+        ddp.enable_fused_sgd(optimizer)
+
+    start_epoch = 0
+    if args.resume:
+        payload = load_checkpoint(args.resume, model, optimizer, scaler)
+        start_epoch = int(payload.get("epoch", 0))
+        if rank == 0:
+            print(f"Resumed from {args.resume} at epoch {start_epoch}")
+
+    train_step = None
+    native_ok = device.type == "cuda" and args.amp and args.amp_dtype == "bf16"
+    if args.cuda_graph and native_ok and getattr(optimizer, "_flat", False):
+        from .graph_step import TrainStep
+        shape = (args.batch_size, 3, args.image_size, args.image_size)
+        train_step = TrainStep(model, optimizer, scaler, batch_shape=shape, cuda_graph=True)
+    profiler = GradSyncProfiler(ddp) if args.profile_sync else None
+
+    csv = M.MetricsCSV(args.output_dir, enabled=(rank == 0))
+    js = M.MetricsJSON(args.metrics_json, enabled=(rank == 0))
+
+    for epoch in range(start_epoch, args.epochs):
+        train_loss, train_acc, epoch_time = train_one_epoch(
+            epoch, model, train_loader, optimizer, criterion, device, args, rank, world_size,
+            scaler=scaler, train_sampler=train_sampler, train_step=train_step, profiler=profiler)
+        if args.no_validate:
+            val_loss, val_acc = (float("nan"), float("nan")) if rank == 0 else (None, None)
+        else:
+            val_loss, val_acc = validate(model, val_loader, criterion, device, rank, world_size, args)
+        sync = profiler.summary() if profiler is not None else {}
+        if rank == 0:
+            print(M.epoch_line(epoch, args.epochs, train_loss, train_acc, val_loss, val_acc,
+                               epoch_time))
+            csv.append(epoch, train_loss, train_acc, val_loss, val_acc, epoch_time)
+            js.append({"epoch": epoch + 1, "train_loss": train_loss, "train_acc": train_acc,
+                       "val_loss": val_loss, "val_acc": val_acc, "epoch_time_seconds": epoch_time,
+                       "grad_sync": sync})
+            if sync:
+                print("[grad-sync] " + "  ".join(f"{k}={v:.3f}" for k, v in sync.items()))
+        if args.save_every and (epoch + 1) % args.save_every == 0:
+            save_checkpoint(str(Path(args.output_dir) / "checkpoint.pt"), model, optimizer, scaler,
+                            epoch + 1, args, rank)
+
+    if ddp is not None:
+        ddp.shutdown()
+    cleanup_distributed()
+
+
+if __name__ == "__main__":
+    main()

@@ -10,6 +10,8 @@
 #ifndef DPTB200_H_
 #define DPTB200_H_
 
+#include <stddef.h>
+
 #ifdef __cplusplus
 extern "C" {
 #endif
@@ -36,6 +38,80 @@ int dpt_conv_wgrad(const void* dy, const void* x, float* dw, int N, int H, int W
 int dpt_gemm_bf16(int op, const void* A, const void* B, void* C, int M, int N, int K,
                   long long lda, long long ldb, long long ldc, int out_mode, const float* bias,
                   float* stat_sum, float* stat_sq, int splits, void* stream);
+
+
+/* ---- BatchNorm / pooling / head / loss (csrc/ops/norm_pool_loss.cu) --------------------------
+ * Stand in for ATen/cuDNN native_batch_norm(+backward), relu_/threshold_backward, add_,
+ * max_pool2d_with_indices(+backward), mean.dim + addmm (+mm x2), _log_softmax + nll_loss
+ * (+backward) as dispatched by torchvision's resnet18 and nn.CrossEntropyLoss on the reference
+ * path (train_ddp.py:205-207, 211-213, 338).  x/y are NHWC bf16 viewed as [M, C]. */
+int dpt_bn_stats(const void* x, float* sum, float* sq, long long M, int C, void* stream);
+int dpt_bn_fwd_train(const void* x, const float* sum, const float* sq, const float* gamma,
+                     const float* beta, const void* residual, void* y, float* save_mean,
+                     float* save_invstd, float* running_mean, float* running_var,
+                     long long* num_batches_tracked, long long M, int C, float momentum, float eps,
+                     int relu, void* stream);
+int dpt_bn_fwd_eval(const void* x, const float* gamma, const float* beta, const float* running_mean,
+                    const float* running_var, const void* residual, void* y, long long M, int C,
+                    float eps, int relu, void* stream);
+int dpt_bn_bwd_reduce(const void* dy1, const void* dy2, const void* y, const void* x,
+                      const float* save_mean, const float* save_invstd, void* g_out, float* dgamma,
+                      float* dbeta, long long M, int C, void* stream);
+int dpt_bn_bwd_apply(const void* g, const void* x, const float* save_mean, const float* save_invstd,
+                     const float* gamma, const float* dgamma, const float* dbeta, void* dx,
+                     long long M, int C, void* stream);
+int dpt_maxpool3x3s2_fwd(const void* x, void* y, void* idx, int N, int H, int W, int C, void* stream);
+int dpt_maxpool3x3s2_bwd(const void* dy, const void* dy2, const void* idx, void* dx, int N, int H,
+                         int W, int C, void* stream);
+int dpt_head_fwd(const void* x, const float* w, const float* b, float* pooled, float* logits, int B,
+                 int HW, int C, int K, void* stream);
+int dpt_head_bwd(const float* dlogits, const float* w, const float* pooled, void* dx, float* dw,
+                 float* db, int B, int HW, int C, int K, void* stream);
+/* loss = mean CE; dlogits = (softmax - onehot) * (*loss_scale) / B; metrics[3] (f64) accumulate
+ * loss*B, #top-1 correct, B (the host-synchronising .item() calls of train_ddp.py:216-222). */
+int dpt_cross_entropy(const float* logits, const long long* target, float* loss, float* dlogits,
+                      const float* loss_scale, double* metrics, int B, int K, void* stream);
+int dpt_im2col_nchw_f32(const float* x, void* out, int N, int C, int H, int W, int R, int S,
+                        int stride, int pad, int ldk, void* stream);
+int dpt_pad_rows_f32_to_bf16(const float* src, void* dst, int rows, int cols, int ld, void* stream);
+int dpt_nchw_f32_to_nhwc_bf16(const float* x, void* y, int N, int C, int H, int W, void* stream);
+
+/* ---- flat-arena optimizer / AMP (csrc/ops/optim.cu) ------------------------------------------
+ * torch.optim.SGD foreach path (train_ddp.py:339-344, 214), GradScaler unscale_/step/update
+ * (train_ddp.py:207-209, 346) without the found_inf.item() host sync. */
+int dpt_amp_unscale(float* g, long long n, const float* inv_scale, float* found_inf, void* stream);
+int dpt_amp_update_scale(float* scale, int* growth_tracker, float* found_inf, float* inv_scale_out,
+                         float growth_factor, float backoff_factor, int growth_interval,
+                         void* stream);
+int dpt_sgd_flat(float* p, const float* g, float* m, void* shadow_bf16, long long n, float lr,
+                 float momentum, float dampening, float wd, int nesterov, const float* grad_scale,
+                 const float* found_inf, void* stream);
+int dpt_adam_flat(float* p, const float* g, float* m, float* v, void* shadow_bf16, long long n,
+                  float lr, float beta1, float beta2, float eps, float wd, int decoupled,
+                  int* step_count, const float* grad_scale, const float* found_inf, void* stream);
+int dpt_cast_f32_to_bf16(const float* src, void* dst, long long n, void* stream);
+
+/* ---- NVLink peer-memory collectives (csrc/comm/p2p_collectives.cu) ---------------------------
+ * Stand in for ProcessGroupNCCL allreduce / broadcast / barrier as driven by torch DDP on the
+ * reference path (train_ddp.py:65, 112, 166, 305-310).  dpt_symm_alloc is the only call in this
+ * header that allocates device memory (cudaMalloc + IPC export). */
+typedef struct dpt_comm dpt_comm;
+int dpt_symm_alloc(size_t bytes, void** ptr, void* ipc_handle_64);
+int dpt_symm_open(const void* ipc_handle_64, void** ptr);
+int dpt_symm_close(void* ptr);
+int dpt_symm_free(void* ptr);
+size_t dpt_comm_flag_bytes(void);
+int dpt_comm_create(int rank, int world, void* const* flags, double timeout_s, dpt_comm** out);
+int dpt_comm_destroy(dpt_comm* c);
+unsigned dpt_comm_error(const dpt_comm* c);
+int dpt_allreduce_fused(dpt_comm* c, void* const* bufs, long long n, float scale,
+                        const float* inv_scale, void* const* found_inf, void* const* param,
+                        void* const* shadow, float* momentum, float lr, float mu, float wd,
+                        int nesterov, int ctas, void* stream);
+int dpt_allreduce_oneshot(dpt_comm* c, void* const* in, float* out, long long n, float scale,
+                          const float* inv_scale, void* const* found_inf, int ctas, void* stream);
+int dpt_broadcast(dpt_comm* c, void* const* bufs, long long bytes, int src, int ctas, void* stream);
+int dpt_barrier(dpt_comm* c, void* stream);
 
 #ifdef __cplusplus
 }

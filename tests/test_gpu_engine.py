@@ -1,0 +1,128 @@
+"""ResNet engine (native sm_100a kernels) vs the same network through PyTorch fp32 ops."""
+import copy
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _cos(a, b):
+    a, b = a.flatten().float(), b.flatten().float()
+    return float(torch.dot(a, b) / (a.norm() * b.norm() + 1e-12))
+
+
+@pytest.mark.parametrize("arch,bs,img,ncls", [("resnet18", 32, 32, 10), ("resnet50", 8, 64, 100)])
+def test_engine_matches_torch_fp32(arch, bs, img, ncls):
+    from dpt_b200.models.resnet import build_model
+    torch.manual_seed(0)
+    dev = torch.device("cuda")
+    model = build_model(dev, arch, ncls)
+    ref = copy.deepcopy(model)
+    ref.native = "never"
+    model.native = "always"
+    x = torch.randn(bs, 3, img, img, device=dev)
+    t = torch.randint(0, ncls, (bs,), device=dev)
+    model.train()
+    ref.train()
+    # reference on the bf16-representable input / weights in fp32 math
+    with torch.no_grad():
+        for p in ref.parameters():
+            if p.dim() == 4:
+                p.copy_(p.bfloat16().float())
+    for p, q in zip(model.parameters(), ref.parameters()):
+        with torch.no_grad():
+            p.copy_(q)
+    out = model(x)
+    loss = F.cross_entropy(out, t)
+    loss.backward()
+    out_r = ref(x.bfloat16().float())
+    loss_r = F.cross_entropy(out_r, t)
+    loss_r.backward()
+    torch.cuda.synchronize()
+    assert abs(loss.item() - loss_r.item()) < 0.05 * max(1.0, abs(loss_r.item())), (loss.item(), loss_r.item())
+    assert _cos(out, out_r) > 0.99
+    worst = 1.0
+    for (n, p), q in zip(model.named_parameters(), ref.parameters()):
+        assert p.grad is not None, n
+        c = _cos(p.grad, q.grad)
+        worst = min(worst, c)
+        assert c > 0.95, f"{n}: grad cosine {c:.4f}"
+    # running statistics follow the same momentum update
+    for (n, b), br in zip(model.named_buffers(), ref.named_buffers()):
+        if "running" in n:
+            assert _cos(b, br[1]) > 0.99, n
+        elif "num_batches" in n:
+            assert int(b) == int(br[1]) == 1
+
+
+def test_eval_forward_matches():
+    from dpt_b200.models.resnet import build_model
+    torch.manual_seed(1)
+    dev = torch.device("cuda")
+    model = build_model(dev, "resnet18", 10)
+    model.eval()
+    x = torch.randn(16, 3, 32, 32, device=dev)
+    with torch.no_grad():
+        model.native = "always"
+        a = model(x).clone()
+        model.native = "never"
+        b = model(x)
+    assert _cos(a, b) > 0.995
+
+
+def test_trainstep_graph_equals_eager_and_learns():
+    from dpt_b200.graph_step import TrainStep
+    from dpt_b200.models.resnet import build_model
+    from dpt_b200.optim import SGD
+    dev = torch.device("cuda")
+    shape = (32, 3, 32, 32)
+    x = torch.randn(shape).pin_memory()
+    t = torch.randint(0, 10, (32,)).pin_memory()
+    results = []
+    for graph in (False, True):
+        torch.manual_seed(7)
+        model = build_model(dev, "resnet18", 10)
+        opt = SGD(model.parameters(), lr=0.05, momentum=0.9, weight_decay=5e-4)
+        step = TrainStep(model, opt, None, batch_shape=shape, cuda_graph=graph)
+        losses = []
+        for _ in range(6):
+            step(x, t)
+            losses.append(step.read_loss(lag=0))
+        torch.cuda.synchronize()
+        results.append((losses, opt.arena.param.clone(), step.read_metrics()))
+    (l0, p0, m0), (l1, p1, m1) = results
+    assert l0[-1] < l0[0] and l1[-1] < l1[0], (l0, l1)
+    # split-K atomics make the two runs differ in the last bits only
+    assert abs(l0[0] - l1[0]) < 1e-2
+    assert _cos(p0, p1) > 0.9999
+    assert m0[2] == m1[2] == 6 * 32
+
+
+def test_compat_loop_with_scaler_and_autocast():
+    """Reference-style loop (autocast + GradScaler API) drives the native engine."""
+    from dpt_b200.amp import GradScaler
+    from dpt_b200.models.resnet import build_model
+    from dpt_b200.ops.loss import CrossEntropyLoss
+    from dpt_b200.optim import SGD
+    dev = torch.device("cuda")
+    torch.manual_seed(3)
+    model = build_model(dev, "resnet18", 10)
+    opt = SGD(model.parameters(), lr=0.05, momentum=0.9, weight_decay=5e-4)
+    crit = CrossEntropyLoss()
+    scaler = GradScaler(device=dev, init_scale=1024.0, enabled=True)
+    x = torch.randn(16, 3, 32, 32, device=dev)
+    t = torch.randint(0, 10, (16,), device=dev)
+    losses = []
+    for _ in range(5):
+        opt.zero_grad(set_to_none=True)
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            out = model(x)
+            loss = crit(out, t)
+        scaler.scale(loss).backward()
+        scaler.step(opt)
+        scaler.update()
+        losses.append(loss.item())
+    assert losses[-1] < losses[0], losses
+    assert scaler.get_scale() == 1024.0
