@@ -49,13 +49,59 @@ static inline int ew_grid(long long nvec, int cvec) {
     return static_cast<int>(blocks);
 }
 
+
+// Block-level reduction for kernels whose threads are bound to a channel group
+// (thread t handles channels 8*(t % cvec) .. +7; cvec is a power of two dividing 256).
+// Lanes of a warp that share a group are combined with shuffles, the <= 8 remaining partials
+// per group through shared memory.  On return threads t < cvec hold the block totals.
+__device__ __forceinline__ void block_reduce_cg(float (&s1)[8], float (&s2)[8], int cvec,
+                                                float (*sh)[kEwThreads / 32][32][8 + 1]) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int off = 16; off >= cvec; off >>= 1) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            s1[k] += __shfl_xor_sync(0xffffffffu, s1[k], off);
+            s2[k] += __shfl_xor_sync(0xffffffffu, s2[k], off);
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        sh[0][warp][lane][k] = s1[k];
+        sh[1][warp][lane][k] = s2[k];
+    }
+    __syncthreads();
+    if (threadIdx.x < cvec) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) s1[k] = s2[k] = 0.f;
+        if (cvec <= 32) {
+            // group g lives in lane g of every warp
+            for (int w = 0; w < kEwThreads / 32; ++w) {
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    s1[k] += sh[0][w][threadIdx.x][k];
+                    s2[k] += sh[1][w][threadIdx.x][k];
+                }
+            }
+        } else {
+            // group g lives in threads g, g + cvec, ...
+            for (int t = threadIdx.x; t < kEwThreads; t += cvec) {
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    s1[k] += sh[0][t >> 5][t & 31][k];
+                    s2[k] += sh[1][t >> 5][t & 31][k];
+                }
+            }
+        }
+    }
+}
+
 // ------------------------------------------------------------------------------------ BN stats
 // sum[c] += sum_m x[m,c]; sq[c] += sum_m x[m,c]^2   (buffers zeroed by the caller)
 __global__ void __launch_bounds__(kEwThreads) bn_stats_kernel(const bf16x8* __restrict__ x,
                                                               float* __restrict__ sum,
                                                               float* __restrict__ sq, long long nvec,
                                                               int cvec) {
-    __shared__ float sh[2][kEwThreads][8 + 1];
+    __shared__ float sh[2][kEwThreads / 32][32][8 + 1];
     const long long stride = static_cast<long long>(gridDim.x) * kEwThreads;
     long long i = static_cast<long long>(blockIdx.x) * kEwThreads + threadIdx.x;
     float s1[8] = {0, 0, 0, 0, 0, 0, 0, 0}, s2[8] = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -68,22 +114,9 @@ __global__ void __launch_bounds__(kEwThreads) bn_stats_kernel(const bf16x8* __re
             s2[k] += f[k] * f[k];
         }
     }
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        sh[0][threadIdx.x][k] = s1[k];
-        sh[1][threadIdx.x][k] = s2[k];
-    }
-    __syncthreads();
-    // threads t, t+cvec, t+2cvec ... share a channel group
+    block_reduce_cg(s1, s2, cvec, sh);
     if (threadIdx.x < cvec) {
-        for (int t = threadIdx.x + cvec; t < kEwThreads; t += cvec) {
-#pragma unroll
-            for (int k = 0; k < 8; ++k) {
-                s1[k] += sh[0][t][k];
-                s2[k] += sh[1][t][k];
-            }
-        }
-        const int cg = static_cast<int>((static_cast<long long>(blockIdx.x) * kEwThreads + threadIdx.x) % cvec);
+        const int cg = threadIdx.x;
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
             atomicAdd(sum + cg * 8 + k, s1[k]);
@@ -190,7 +223,7 @@ bn_bwd_reduce_kernel(const bf16x8* __restrict__ dy1, const bf16x8* __restrict__ 
                      const float* __restrict__ save_mean, const float* __restrict__ save_invstd,
                      bf16x8* __restrict__ g_out, float* __restrict__ dgamma,
                      float* __restrict__ dbeta, long long nvec, int cvec) {
-    __shared__ float sh[2][kEwThreads][8 + 1];
+    __shared__ float sh[2][kEwThreads / 32][32][8 + 1];
     const long long stride = static_cast<long long>(gridDim.x) * kEwThreads;
     long long i = static_cast<long long>(blockIdx.x) * kEwThreads + threadIdx.x;
     const int cg = static_cast<int>(i % cvec);
@@ -228,20 +261,8 @@ bn_bwd_reduce_kernel(const bf16x8* __restrict__ dy1, const bf16x8* __restrict__ 
             s2[k] += g[k] * (xv[k] - mean[k]) * istd[k];
         }
     }
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        sh[0][threadIdx.x][k] = s1[k];
-        sh[1][threadIdx.x][k] = s2[k];
-    }
-    __syncthreads();
+    block_reduce_cg(s1, s2, cvec, sh);
     if (threadIdx.x < cvec) {
-        for (int t = threadIdx.x + cvec; t < kEwThreads; t += cvec) {
-#pragma unroll
-            for (int k = 0; k < 8; ++k) {
-                s1[k] += sh[0][t][k];
-                s2[k] += sh[1][t][k];
-            }
-        }
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
             atomicAdd(dbeta + cg * 8 + k, s1[k]);
@@ -421,7 +442,7 @@ head_bwd_dx_kernel(const float* __restrict__ dlogits, const float* __restrict__ 
 }
 
 // dw[k,c] += sum_n dlogits[n,k] pooled[n,c];  db[k] += sum_n dlogits[n,k]
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(64)
 head_bwd_dw_kernel(const float* __restrict__ dlogits, const float* __restrict__ pooled,
                    float* __restrict__ dw, float* __restrict__ db, int B, int C, int K,
                    float unscale) {
@@ -429,8 +450,10 @@ head_bwd_dw_kernel(const float* __restrict__ dlogits, const float* __restrict__ 
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c < C) {
         float s = 0.f;
+#pragma unroll 16
         for (int n = 0; n < B; ++n)
-            s += dlogits[static_cast<long long>(n) * K + k] * pooled[static_cast<long long>(n) * C + c];
+            s += __ldg(dlogits + static_cast<long long>(n) * K + k) *
+                 __ldg(pooled + static_cast<long long>(n) * C + c);
         dw[static_cast<long long>(k) * C + c] += s * unscale;
     }
     if (blockIdx.x == 0 && threadIdx.x == 0 && db != nullptr) {
@@ -522,26 +545,34 @@ ce_fwd_bwd_kernel(const float* __restrict__ logits, const long long* __restrict_
 __global__ void __launch_bounds__(kEwThreads)
 im2col_nchw_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ out, int N, int C,
                    int H, int W, int R, int S, int stride, int pad, int P, int Q, int ldk) {
-    const long long total = static_cast<long long>(N) * P * Q * ldk;
+    // one thread = 8 consecutive columns of one row (ldk % 8 == 0): a single 16-byte store
+    const int cv = ldk / 8;
+    const long long total = static_cast<long long>(N) * P * Q * cv;
     const int K = R * S * C;
     for (long long i = static_cast<long long>(blockIdx.x) * kEwThreads + threadIdx.x; i < total;
          i += static_cast<long long>(gridDim.x) * kEwThreads) {
-        const int col = static_cast<int>(i % ldk);
-        long long t = i / ldk;
+        const int col0 = static_cast<int>(i % cv) * 8;
+        long long t = i / cv;
         const int q = static_cast<int>(t % Q);
         t /= Q;
         const int p = static_cast<int>(t % P);
         const int n = static_cast<int>(t / P);
-        float v = 0.f;
-        if (col < K) {
-            const int c = col % C;
-            const int rs = col / C;
-            const int s = rs % S, r = rs / S;
-            const int h = p * stride - pad + r, w = q * stride - pad + s;
-            if (h >= 0 && h < H && w >= 0 && w < W)
-                v = x[((static_cast<long long>(n) * C + c) * H + h) * W + w];
+        float v[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            const int col = col0 + e;
+            float val = 0.f;
+            if (col < K) {
+                const int c = col % C;
+                const int rs = col / C;
+                const int s = rs % S, r = rs / S;
+                const int h = p * stride - pad + r, w = q * stride - pad + s;
+                if (h >= 0 && h < H && w >= 0 && w < W)
+                    val = __ldg(x + ((static_cast<long long>(n) * C + c) * H + h) * W + w);
+            }
+            v[e] = val;
         }
-        out[i] = __float2bfloat16_rn(v);
+        reinterpret_cast<bf16x8*>(out)[i] = pack8(v);
     }
 }
 
@@ -675,8 +706,8 @@ extern "C" int dpt_head_bwd(const float* dlogits, const float* w, const float* p
     if (dx != nullptr)
         head_bwd_dx_kernel<<<B, 256, K * sizeof(float), st>>>(
             dlogits, w, static_cast<__nv_bfloat16*>(dx), HW, C, K);
-    dim3 grid((C + 255) / 256, K);
-    head_bwd_dw_kernel<<<grid, 256, 0, st>>>(dlogits, pooled, dw, db, B, C, K, 1.f);
+    dim3 grid((C + 63) / 64, K);
+    head_bwd_dw_kernel<<<grid, 64, 0, st>>>(dlogits, pooled, dw, db, B, C, K, 1.f);
     DPT_CHECK_LAUNCH();
 }
 
@@ -694,7 +725,8 @@ extern "C" int dpt_cross_entropy(const float* logits, const long long* target, f
 extern "C" int dpt_im2col_nchw_f32(const float* x, void* out, int N, int C, int H, int W, int R,
                                    int S, int stride, int pad, int ldk, void* stream) {
     const int P = (H + 2 * pad - R) / stride + 1, Q = (W + 2 * pad - S) / stride + 1;
-    const long long total = static_cast<long long>(N) * P * Q * ldk;
+    if (ldk % 8 != 0) return DPT_ERR_SHAPE;
+    const long long total = static_cast<long long>(N) * P * Q * (ldk / 8);
     im2col_nchw_kernel<<<ew_grid(total, 1), kEwThreads, 0, static_cast<cudaStream_t>(stream)>>>(
         x, static_cast<__nv_bfloat16*>(out), N, C, H, W, R, S, stride, pad, P, Q, ldk);
     DPT_CHECK_LAUNCH();

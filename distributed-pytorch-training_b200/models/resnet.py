@@ -281,6 +281,11 @@ class ResNetEngine:
         self.logits = torch.empty((N, K), **f32)
         self.d_feat = torch.empty(shape, **bf) if training else None
         self._last_input = None
+        # weight-gradient kernels are off the critical path (nothing in backward consumes
+        # them): they run on a second stream, concurrently with the dgrad / BN-backward chain
+        self.side = torch.cuda.Stream(device=self.dev) if training else None
+        self._ev_pool = [torch.cuda.Event() for _ in range(64)] if training else []
+        self._ev_i = 0
 
     # ------------------------------------------------------------------ planning
     def _unit(self, name, conv, bn, x_shape, y_shape, relu) -> _Unit:
@@ -437,12 +442,21 @@ class ResNetEngine:
                        g_out=u.g if masked else None, dx=u.d_raw)
         return u.d_raw
 
+    def _fork_side(self):
+        """Side stream picks up everything enqueued on the current stream so far."""
+        ev = self._ev_pool[self._ev_i % len(self._ev_pool)]
+        self._ev_i += 1
+        ev.record(torch.cuda.current_stream())
+        self.side.wait_event(ev)
+        return torch.cuda.stream(self.side)
+
     def _wgrad(self, u: _Unit, x_in):
         conv = u.conv
         Cout, Cin, R, S = conv.weight.shape
-        self.Fn.conv_wgrad(u.d_raw, x_in, (Cout, R, S, Cin), conv.stride, conv.padding,
-                           out=self._gw(conv.weight))
-        self._ready(conv.weight, u.bn.weight, u.bn.bias)
+        with self._fork_side():
+            self.Fn.conv_wgrad(u.d_raw, x_in, (Cout, R, S, Cin), conv.stride, conv.padding,
+                               out=self._gw(conv.weight))
+            self._ready(conv.weight, u.bn.weight, u.bn.bias)
 
     def _dgrad(self, u: _Unit, x_shape, out, u2: Optional[_Unit] = None):
         conv = u.conv
@@ -488,7 +502,8 @@ class ResNetEngine:
         dlogits = dlogits.contiguous()
         Fn.head_bwd(dlogits, m.fc.weight, self.pooled, self.feat_shape, self._gw(m.fc.weight),
                     self._gw(m.fc.bias), dx=self.d_feat)
-        self._ready(m.fc.weight, m.fc.bias)
+        with self._fork_side():
+            self._ready(m.fc.weight, m.fc.bias)
         dy, dy2 = self.d_feat, None
         for b in reversed(self.blocks):
             dy, dy2 = self._bwd_block(b, dy, dy2)
@@ -498,6 +513,8 @@ class ResNetEngine:
         self._bn_bwd(st, self.d_pool_in)
         N, P, Q, _ = st.y_shape
         M = N * P * Q
-        Fn.gemm(2, st.d_raw, self.cols, self._gw(m.conv1.weight), 64, 147, M, 64, self.STEM_LDK, 147,
-                out_mode=2, splits=max(1, min(64, M // 512)))
-        self._ready(m.conv1.weight, m.bn1.weight, m.bn1.bias)
+        with self._fork_side():
+            Fn.gemm(2, st.d_raw, self.cols, self._gw(m.conv1.weight), 64, 147, M, 64, self.STEM_LDK,
+                    147, out_mode=2, splits=max(1, min(64, M // 512)))
+            self._ready(m.conv1.weight, m.bn1.weight, m.bn1.bias)
+        torch.cuda.current_stream().wait_stream(self.side)   # join
