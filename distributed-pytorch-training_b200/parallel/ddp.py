@@ -239,7 +239,7 @@ class DistributedDataParallel(nn.Module):
         """Module buffers (BN running stats, num_batches_tracked) are moved into one flat
         (symmetric, when native) allocation so the per-forward buffer sync is one kernel."""
         bufs = [(n, b) for n, b in self.module.named_buffers() if b is not None]
-        self._buffers = bufs
+        self._mod_buffers = bufs
         self.buffer_buf = None
         if not bufs:
             return
@@ -275,7 +275,7 @@ class DistributedDataParallel(nn.Module):
             self.comm.check_health()
         else:
             dist.broadcast(self.arena.param, src=self._global_src(), group=self.process_group)
-            if self._buffers:
+            if self._mod_buffers:
                 dist.broadcast(self._buffer_flat, src=self._global_src(), group=self.process_group)
             self.arena.refresh_shadow()
 
@@ -352,7 +352,7 @@ class DistributedDataParallel(nn.Module):
         return self.reducer.finalize()
 
     def sync_buffers(self) -> None:
-        if not (self.broadcast_buffers and self._buffers and self.world_size > 1):
+        if not (self.broadcast_buffers and self._mod_buffers and self.world_size > 1):
             return
         if self.backend == "native":
             self.comm.broadcast_(self.buffer_buf, 0, self._buffer_bytes, src=0, ctas=1)

@@ -1,0 +1,157 @@
+"""Multi-process CPU tests (gloo, world_size 2): the wrapper's bucketing / hooks / broadcast
+logic against torch DDP, and the entry point end to end (BASELINE.json config 1)."""
+import os
+import sys
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _init(rank, world, port):
+    os.environ.update({"MASTER_ADDR": "127.0.0.1", "MASTER_PORT": str(port), "RANK": str(rank),
+                       "WORLD_SIZE": str(world), "LOCAL_RANK": str(rank)})
+    sys.path.insert(0, ROOT)
+    torch.set_num_threads(2)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+
+
+def _ddp_parity_worker(rank, world, port, q):
+    try:
+        _init(rank, world, port)
+        import copy
+        from dpt_b200.models.resnet import resnet18
+        from dpt_b200.optim import SGD
+        from dpt_b200.parallel.ddp import DistributedDataParallel as OurDDP
+        from torch.nn.parallel import DistributedDataParallel as TorchDDP
+        torch.manual_seed(100 + rank)          # replicas start different (seed + rank semantics)
+        base = resnet18(10)
+        ours = OurDDP(copy.deepcopy(base), backend="gloo", bucket_cap_mb=1)
+        ref = TorchDDP(copy.deepcopy(base), bucket_cap_mb=1)
+        # both broadcast rank 0's weights at construction
+        for a, b in zip(ours.module.state_dict().values(), ref.module.state_dict().values()):
+            assert torch.allclose(a.float(), b.float()), "init broadcast mismatch"
+        assert len(ours.plans) > 3
+        opt_o = SGD(ours.parameters(), lr=0.05, momentum=0.9, weight_decay=5e-4)
+        opt_r = torch.optim.SGD(ref.parameters(), lr=0.05, momentum=0.9, weight_decay=5e-4)
+        g = torch.Generator().manual_seed(7 + rank)  # each rank its own shard
+        losses = []
+        for it in range(3):
+            x = torch.randn(4, 3, 32, 32, generator=g)
+            t = torch.randint(0, 10, (4,), generator=g)
+            for model, opt in ((ours, opt_o), (ref, opt_r)):
+                opt.zero_grad(set_to_none=True)
+                loss = torch.nn.functional.cross_entropy(model(x), t)
+                loss.backward()
+                opt.step()
+                losses.append(loss.item())
+        for (n, a), b in zip(ours.module.named_parameters(), ref.module.parameters()):
+            assert torch.allclose(a, b, atol=2e-4, rtol=1e-3), f"param {n} diverged from torch DDP"
+        # replicas identical across ranks (checksum all-reduce)
+        cs = torch.stack([p.detach().double().sum() for p in ours.parameters()])
+        lo, hi = cs.clone(), cs.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        assert torch.allclose(lo, hi, atol=1e-9), "replicas diverged across ranks"
+        # running stats follow rank 0 (broadcast_buffers)
+        rm = ours.module.bn1.running_mean.clone()
+        rm0 = rm.clone()
+        dist.broadcast(rm0, 0)
+        # no_sync skips the reduction
+        before = ours.reducer.launch_count
+        with ours.no_sync():
+            torch.nn.functional.cross_entropy(ours(x), t).backward()
+        assert ours.reducer.launch_count == before
+        # state_dict carries the DDP prefix
+        assert all(k.startswith("module.") for k in ours.state_dict())
+        log = ours._get_ddp_logging_data()
+        assert log["world_size"] == world and log["num_parameter_tensors"] == 62
+        assert log["total_parameter_size_bytes"] == 44726568
+        q.put((rank, "ok"))
+    except Exception as e:  # noqa: BLE001
+        import traceback
+        q.put((rank, traceback.format_exc()))
+    finally:
+        if dist.is_initialized():
+            dist.destroy_process_group()
+
+
+def _comm_hook_worker(rank, world, port, q):
+    try:
+        _init(rank, world, port)
+        from dpt_b200.parallel.ddp import DistributedDataParallel as OurDDP
+        torch.manual_seed(0)
+        net = torch.nn.Sequential(torch.nn.Linear(8, 16), torch.nn.ReLU(), torch.nn.Linear(16, 4))
+        ddp = OurDDP(net, backend="gloo")
+        seen = []
+
+        def hook(state, bucket):
+            seen.append((bucket.index(), bucket.is_last(), len(bucket.parameters())))
+            buf = bucket.buffer()
+            buf.div_(dist.get_world_size())
+            fut = dist.all_reduce(buf, async_op=True).get_future()
+            return fut.then(lambda f: f.value()[0])
+
+        ddp.register_comm_hook(None, hook)
+        x = torch.full((2, 8), float(rank + 1))
+        ddp(x).sum().backward()
+        assert seen and seen[-1][1] is True
+        g = [p.grad.clone() for p in ddp.parameters()]
+        for t in g:
+            lo, hi = t.clone(), t.clone()
+            dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+            dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+            assert torch.allclose(lo, hi)
+        q.put((rank, "ok"))
+    except Exception:  # noqa: BLE001
+        import traceback
+        q.put((rank, traceback.format_exc()))
+    finally:
+        if dist.is_initialized():
+            dist.destroy_process_group()
+
+
+def _run(worker, world=2):
+    from dpt_b200.launcher import free_port
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = free_port()
+    procs = [ctx.Process(target=worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=600) for _ in procs]
+    for p in procs:
+        p.join(60)
+    for rank, msg in results:
+        assert msg == "ok", f"rank {rank}:\n{msg}"
+
+
+def test_ddp_wrapper_matches_torch_ddp_gloo():
+    _run(_ddp_parity_worker)
+
+
+def test_comm_hook_escape_hatch_gloo():
+    _run(_comm_hook_worker)
+
+
+def _entry(outdir):
+    sys.path.insert(0, ROOT)
+    torch.set_num_threads(2)
+    from dpt_b200.train_ddp import main
+    main(["--synthetic", "--synthetic-size", "32", "--epochs", "1", "--batch-size", "4",
+          "--workers", "0", "--print-freq", "2", "--output-dir", outdir, "--backend", "gloo",
+          "--steps", "3", "--save-every", "1"])
+
+
+def test_entry_point_two_process_gloo(tmp_path):
+    """Config 1: default model FP32 on CPU/gloo world_size=2 with synthetic data."""
+    from dpt_b200.launcher import spawn
+    out = str(tmp_path / "exp")
+    spawn(_entry, 2, args=(out,))
+    lines = open(os.path.join(out, "metrics_rank0.csv")).read().splitlines()
+    assert lines[0].startswith("epoch,train_loss") and len(lines) == 2
+    ck = torch.load(os.path.join(out, "checkpoint.pt"), weights_only=False)
+    assert all(k.startswith("module.") for k in ck["model"]) and ck["epoch"] == 1

@@ -1,0 +1,249 @@
+"""CPU-only parity tests of the plumbing: CLI, sampler, bucket planner, metrics formats,
+GradScaler state machine, optimizers, checkpoints, model key names."""
+import math
+import os
+
+import pytest
+import torch
+import torch.distributed as dist
+
+
+def test_cli_reference_flags_and_defaults():
+    from dpt_b200.cli import parse_args
+    a = parse_args([])
+    # reference train_ddp.py:22-43
+    assert (a.data_dir, a.epochs, a.batch_size, a.workers) == ("./data", 10, 128, 4)
+    assert (a.lr, a.momentum, a.weight_decay) == (0.1, 0.9, 5e-4)
+    assert a.amp is False and a.print_freq == 50 and a.output_dir == "./experiments" and a.seed == 42
+    b = parse_args(["--amp", "--batch-size", "64", "--backend", "gloo", "--amp-dtype", "fp16",
+                    "--synthetic", "--arch", "resnet50"])
+    assert b.amp and b.batch_size == 64 and b.backend == "gloo" and b.arch == "resnet50"
+
+
+@pytest.mark.parametrize("n,world,drop_last", [(50000, 1, False), (50000, 8, False), (10, 4, False),
+                                               (101, 3, True), (7, 8, False), (1000, 2, True)])
+def test_sampler_matches_torch(n, world, drop_last):
+    from dpt_b200.data import DistributedSampler
+    ds = list(range(n))
+    for rank in range(world):
+        for epoch in (0, 1, 5):
+            for shuffle in (True, False):
+                a = DistributedSampler(ds, world, rank, shuffle=shuffle, drop_last=drop_last)
+                b = torch.utils.data.DistributedSampler(ds, world, rank, shuffle=shuffle,
+                                                        drop_last=drop_last)
+                a.set_epoch(epoch)
+                b.set_epoch(epoch)
+                assert list(a) == list(b)
+                assert len(a) == len(b)
+
+
+def test_steps_per_epoch_match_survey():
+    from dpt_b200.data import DistributedSampler
+    for world, steps in [(1, 391), (2, 196), (4, 98), (8, 49)]:
+        s = DistributedSampler(list(range(50000)), world, 0)
+        assert math.ceil(len(s) / 128) == steps
+
+
+def _param_list(arch):
+    import torchvision
+    m = getattr(torchvision.models, arch)(num_classes=10 if arch == "resnet18" else 1000)
+    return [p for p in m.parameters()]
+
+
+@pytest.mark.parametrize("arch", ["resnet18", "resnet50"])
+def test_bucket_planner_matches_torch(arch):
+    from dpt_b200.parallel.bucket import compute_bucket_assignment_by_size
+    params = _param_list(arch)
+    for order in (params, list(reversed(params))):
+        for limits in ([1024 * 1024, 25 * 1024 * 1024], [2 ** 62], [4096, 65536, 10 ** 6]):
+            ours, lim_o = compute_bucket_assignment_by_size(order, limits)
+            ref, lim_r = dist._compute_bucket_assignment_by_size(order, limits)
+            assert ours == ref
+            assert lim_o == lim_r
+
+
+def test_bucket_sizes_resnet18_reverse_order():
+    """Reversed registration order with the 1 MiB / 25 MiB caps gives 3 buckets covering all
+    44,726,568 gradient bytes (3 steady-state buckets)."""
+    from dpt_b200.parallel.bucket import compute_bucket_assignment_by_size
+    params = list(reversed(_param_list("resnet18")))
+    b, _ = compute_bucket_assignment_by_size(params, [1024 * 1024, 25 * 1024 * 1024])
+    sizes = [sum(params[i].numel() * 4 for i in bk) for bk in b]
+    assert len(sizes) == 3 and sum(sizes) == 44726568
+
+
+def test_metrics_golden_strings(tmp_path):
+    from dpt_b200 import metrics as M
+    assert M.banner("cuda:0", 8, True) == "Using device: cuda:0, world_size=8, amp=True"
+    assert M.step_line(0, 50, 391, 2.30259, 10.5, 12345.678) == \
+        "Epoch [1] Step [50/391] Loss: 2.3026  Acc: 10.50%  Throughput: 12345.68 samples/s (global)"
+    assert M.epoch_line(1, 10, 1.5, 45.123, 1.25, 50.0, 12.3456) == \
+        "[Epoch 2/10] Train: loss=1.5000, acc=45.12% | Val: loss=1.2500, acc=50.00% | Epoch time: 12.35s"
+    assert M.csv_row(0, 1.5, 45.123, 1.25, 50.0, 12.3456) == "1,1.5000,45.12,1.2500,50.00,12.3456\n"
+    c = M.MetricsCSV(str(tmp_path))
+    c.append(0, 1.0, 2.0, 3.0, 4.0, 5.0)
+    c2 = M.MetricsCSV(str(tmp_path))  # re-run appends, header written once (train_ddp.py:350-355)
+    c2.append(1, 1.0, 2.0, 3.0, 4.0, 5.0)
+    lines = (tmp_path / "metrics_rank0.csv").read_text().splitlines()
+    assert lines[0] == "epoch,train_loss,train_acc,val_loss,val_acc,epoch_time_seconds"
+    assert len(lines) == 3
+
+
+def test_grad_scaler_state_machine_matches_torch():
+    from dpt_b200.amp import GradScaler
+    ours = GradScaler(device="cpu", init_scale=1024.0, growth_interval=3, enabled=True)
+    ref = torch.amp.GradScaler("cpu", init_scale=1024.0, growth_interval=3, enabled=True)
+    p_o = torch.nn.Parameter(torch.ones(4))
+    p_r = torch.nn.Parameter(torch.ones(4))
+    from dpt_b200.optim import SGD
+    opt_o = SGD([p_o], lr=0.1)
+    opt_r = torch.optim.SGD([p_r], lr=0.1)
+    pattern = [False, False, True, False, False, False, False, True, True, False]
+    for bad in pattern:
+        for p, sc, opt in ((p_o, ours, opt_o), (p_r, ref, opt_r)):
+            opt.zero_grad()
+            loss = (p * 2.0).sum()
+            sc.scale(loss).backward()
+            if bad:
+                p.grad[1] = float("inf")
+            sc.step(opt)
+            sc.update()
+        assert ours.get_scale() == ref.get_scale()
+        assert torch.allclose(p_o, p_r)
+    assert set(ours.state_dict().keys()) == set(ref.state_dict().keys()) == {
+        "scale", "growth_factor", "backoff_factor", "growth_interval", "_growth_tracker"}
+    assert ours.state_dict()["_growth_tracker"] == ref.state_dict()["_growth_tracker"]
+    with pytest.raises(RuntimeError):
+        ours.unscale_(opt_o)
+        ours.unscale_(opt_o)
+    disabled = GradScaler(device="cpu", enabled=False)
+    x = torch.tensor(3.0)
+    assert disabled.scale(x) is x and disabled.state_dict() == {}
+
+
+def test_sgd_and_adam_match_torch_on_cpu():
+    from dpt_b200.optim import SGD, Adam, AdamW
+    torch.manual_seed(0)
+    shapes = [(8, 3, 3, 3), (8,), (4, 8)]
+    def make():
+        torch.manual_seed(1)
+        return [torch.nn.Parameter(torch.randn(s)) for s in shapes]
+    cases = [
+        (lambda ps: SGD(ps, lr=0.1, momentum=0.9, weight_decay=5e-4),
+         lambda ps: torch.optim.SGD(ps, lr=0.1, momentum=0.9, weight_decay=5e-4)),
+        (lambda ps: SGD(ps, lr=0.05, momentum=0.8, nesterov=True),
+         lambda ps: torch.optim.SGD(ps, lr=0.05, momentum=0.8, nesterov=True)),
+        (lambda ps: Adam(ps, lr=1e-2, weight_decay=1e-2), lambda ps: torch.optim.Adam(ps, lr=1e-2, weight_decay=1e-2)),
+        (lambda ps: AdamW(ps, lr=1e-2), lambda ps: torch.optim.AdamW(ps, lr=1e-2)),
+    ]
+    for mk_o, mk_r in cases:
+        po, pr = make(), make()
+        oo, orr = mk_o(po), mk_r(pr)
+        for it in range(5):
+            g = torch.Generator().manual_seed(it)
+            for a, b in zip(po, pr):
+                gr = torch.randn(a.shape, generator=g)
+                a.grad = gr.clone()
+                b.grad = gr.clone()
+            oo.step()
+            orr.step()
+        for a, b in zip(po, pr):
+            assert torch.allclose(a, b, atol=1e-6, rtol=1e-5)
+    # state_dict layout parity for SGD
+    po, pr = make(), make()
+    oo = SGD(po, lr=0.1, momentum=0.9, weight_decay=5e-4)
+    orr = torch.optim.SGD(pr, lr=0.1, momentum=0.9, weight_decay=5e-4)
+    for a, b in zip(po, pr):
+        a.grad = torch.ones_like(a)
+        b.grad = torch.ones_like(b)
+    oo.step()
+    orr.step()
+    so, sr = oo.state_dict(), orr.state_dict()
+    assert set(so["param_groups"][0].keys()) == set(sr["param_groups"][0].keys())
+    assert so["param_groups"][0]["params"] == sr["param_groups"][0]["params"]
+    assert set(so["state"].keys()) == set(sr["state"].keys())
+    for k in sr["state"]:
+        assert torch.allclose(so["state"][k]["momentum_buffer"], sr["state"][k]["momentum_buffer"])
+
+
+@pytest.mark.parametrize("arch", ["resnet18", "resnet34", "resnet50"])
+def test_state_dict_keys_match_torchvision(arch):
+    import torchvision
+    from dpt_b200.models import resnet as R
+    ours = getattr(R, arch)(num_classes=10)
+    ref = getattr(torchvision.models, arch)(num_classes=10)
+    so, sr = ours.state_dict(), ref.state_dict()
+    assert list(so.keys()) == list(sr.keys())
+    for k in so:
+        assert so[k].shape == sr[k].shape and so[k].dtype == sr[k].dtype, k
+    assert [n for n, _ in ours.named_parameters()] == [n for n, _ in ref.named_parameters()]
+    ref.load_state_dict(so)      # ours -> torchvision
+    ours.load_state_dict(sr)     # torchvision -> ours
+    x = torch.randn(2, 3, 32, 32)
+    ours.eval(); ref.eval()
+    assert torch.allclose(ours(x), ref(x), atol=1e-4)
+
+
+def test_resnet18_workload_constants():
+    from dpt_b200.models.resnet import resnet18
+    m = resnet18(10)
+    ps = list(m.parameters())
+    assert len(ps) == 62 and sum(p.numel() for p in ps) == 11181642
+    bufs = list(m.buffers())
+    assert len(bufs) == 60 and sum(b.numel() for b in bufs if b.dtype == torch.float32) == 9600
+
+
+def test_checkpoint_roundtrip_with_stock_torch_objects(tmp_path):
+    import torchvision
+    from dpt_b200.amp import GradScaler
+    from dpt_b200.checkpoint import load_checkpoint, save_checkpoint
+    from dpt_b200.models.resnet import resnet18
+    from dpt_b200.optim import SGD
+    torch.manual_seed(0)
+    m = resnet18(10)
+    opt = SGD(m.parameters(), lr=0.1, momentum=0.9, weight_decay=5e-4)
+    x = torch.randn(4, 3, 32, 32)
+    m(x).sum().backward()
+    opt.step()
+    sc = GradScaler(device="cpu", enabled=True)
+    sc._lazy_init()
+    path = str(tmp_path / "ck.pt")
+    save_checkpoint(path, m, opt, sc, epoch=3)
+    payload = torch.load(path, weights_only=False)
+    assert payload["epoch"] == 3 and set(payload) >= {"model", "optimizer", "scaler", "epoch", "args"}
+    # stock objects consume it
+    tv = torchvision.models.resnet18(num_classes=10)
+    tv.load_state_dict(payload["model"])
+    tv_opt = torch.optim.SGD(tv.parameters(), lr=0.1, momentum=0.9, weight_decay=5e-4)
+    tv_opt.load_state_dict(payload["optimizer"])
+    torch.amp.GradScaler("cpu").load_state_dict(payload["scaler"])
+    # and a DDP-style ("module."-prefixed) checkpoint loads back into ours
+    torch.save({"model": {"module." + k: v for k, v in tv.state_dict().items()},
+                "optimizer": tv_opt.state_dict(), "scaler": None, "epoch": 7}, path)
+    m2 = resnet18(10)
+    opt2 = SGD(m2.parameters(), lr=0.1, momentum=0.9, weight_decay=5e-4)
+    out = load_checkpoint(path, m2, opt2)
+    assert out["epoch"] == 7
+    for a, b in zip(m.state_dict().values(), m2.state_dict().values()):
+        assert torch.equal(a, b)
+    mb = opt2.state_dict()["state"][0]["momentum_buffer"]
+    assert torch.allclose(mb, opt.state_dict()["state"][0]["momentum_buffer"])
+
+
+def test_synthetic_dataset_shapes():
+    from dpt_b200.data import SyntheticImages
+    ds = SyntheticImages(100, 32, 10)
+    x, y = ds[5]
+    assert x.shape == (3, 32, 32) and x.dtype == torch.float32 and y.dtype == torch.int64
+    assert len(ds) == 100
+
+
+def test_c_header_declares_every_bound_symbol():
+    from dpt_b200.ops import _lib
+    hdr = open(os.path.join(os.path.dirname(__file__), "..", "include", "dptb200.h")).read()
+    for name in list(_lib._SIGS) + ["dpt_comm_flag_bytes", "dpt_comm_error"]:
+        assert name + "(" in hdr, name
+    if _lib.available():
+        lib = _lib.lib()
+        for name in _lib._SIGS:
+            assert hasattr(lib, name)
