@@ -329,7 +329,7 @@ class ResNetEngine:
                                       x_shape, False)
         if self.training:
             b["dx"] = torch.empty(x_shape, **bf)               # grad wrt block input (main path)
-            fused = b["ds"] is not None and b["units"][0].conv.stride == b["ds"].conv.stride
+            fused = self._can_fuse_dgrad(b["units"][0], b["ds"])
             b["dx_ds"] = torch.empty(x_shape, **bf) if (b["ds"] is not None and not fused) else None
             b["d_mid"] = [torch.empty(u.y_shape, **bf) for u in b["units"][:-1]]
         self.blocks.append(b)
@@ -467,6 +467,13 @@ class ResNetEngine:
                                dy2=u2.d_raw, w2=self._w(u2.conv), pad2=u2.conv.padding)
         return out
 
+    @staticmethod
+    def _can_fuse_dgrad(u1, ds) -> bool:
+        """The fused dgrad kernel accumulates two convs that read the same input in one TMEM
+        tile; it needs the same stride and the same number of output channels (BasicBlock)."""
+        return (ds is not None and u1.conv.stride == ds.conv.stride
+                and u1.conv.out_channels == ds.conv.out_channels)
+
     def _bwd_block(self, b, dy, dy2):
         units, ds = b["units"], b["ds"]
         k = len(units)
@@ -484,7 +491,7 @@ class ResNetEngine:
             self._wgrad(u1, b["x"])
             return b["dx"], g_skip
         self._bn_bwd(ds, g_skip)
-        if u1.conv.stride == ds.conv.stride:
+        if self._can_fuse_dgrad(u1, ds):
             # conv1 and the 1x1 downsample read the same block input: one fused dgrad kernel
             self._dgrad(u1, b["x_shape"], b["dx"], ds)
             pair = (b["dx"], None)
