@@ -21,6 +21,7 @@ extern "C" {
 #define DPT_ERR_TMAP (-3)   /* cuTensorMapEncodeTiled rejected the descriptor */
 #define DPT_ERR_ARG (-4)    /* invalid argument */
 #define DPT_ERR_TIMEOUT (-5)
+#define DPT_ERR_TOO_LARGE (-6) /* size beyond a built-in fixed-capacity buffer */
 
 /* ---- tcgen05 / TMA implicit-GEMM convolution (csrc/ops/igemm_tcgen05.cu) ----------------
  * Stand in for the cuDNN convolution forward / backward-data / backward-filter calls that
@@ -60,6 +61,21 @@ int dpt_bn_bwd_reduce(const void* dy1, const void* dy2, const void* y, const voi
 int dpt_bn_bwd_apply(const void* g, const void* x, const float* save_mean, const float* save_invstd,
                      const float* gamma, const float* dgamma, const float* dbeta, void* dx,
                      long long M, int C, void* stream);
+/* BatchNorm training forward for callers that may not allocate (fixed start-up memory plans,
+ * loops that cannot take cudaMalloc's device-wide sync, plugins handed only pointers + a stream).
+ * This entry point has no counterpart in the reference; it exists for those callers only.
+ * Same result as dpt_bn_stats followed by dpt_bn_fwd_train, but the sum / sum-of-squares scratch
+ * is a 32 KiB device array built into the library (held by every GPU that loads it until exit),
+ * so nothing is allocated.  Limits: C <= DPT_BN_NOALLOC_MAX_CHANNELS, otherwise
+ * DPT_ERR_TOO_LARGE.  The first call on a device resolves the array's address for that device
+ * (make it before any stream capture there).  Calls on one device share the array: it is
+ * cleared at the start of each call, and calls that overlap on the GPU race — serialise them. */
+#define DPT_BN_NOALLOC_MAX_CHANNELS 4096
+int dpt_bn_fwd_train_noalloc(const void* x, const float* gamma, const float* beta,
+                             const void* residual, void* y, float* save_mean, float* save_invstd,
+                             float* running_mean, float* running_var,
+                             long long* num_batches_tracked, long long M, int C, float momentum,
+                             float eps, int relu, void* stream);
 int dpt_maxpool3x3s2_fwd(const void* x, void* y, void* idx, int N, int H, int W, int C, void* stream);
 int dpt_maxpool3x3s2_bwd(const void* dy, const void* dy2, const void* idx, void* dx, int N, int H,
                          int W, int C, void* stream);
