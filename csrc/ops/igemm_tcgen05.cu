@@ -123,6 +123,7 @@ igemm_kernel(const __grid_constant__ IgemmMaps maps, const __grid_constant__ Ige
     __shared__ __align__(8) uint64_t empty_bar[NSTAGES];
     __shared__ __align__(8) uint64_t tmem_full_bar;
     __shared__ uint32_t tmem_base_smem;
+    __shared__ __align__(16) float s_stat[2][4][BLOCK_N];  // per-epilogue-warp column partials
 
     const uint32_t warp = threadIdx.x >> 5;
     const uint32_t lane = threadIdx.x & 31;
@@ -368,9 +369,37 @@ igemm_kernel(const __grid_constant__ IgemmMaps maps, const __grid_constant__ Ige
                 const float t2 = warp_colsum16(s2, lane);
                 const int colsel = ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 +
                                    ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
-                if ((lane & 1) == 0 && cbase + colsel < prm.n_total) {
-                    atomicAdd(prm.stat_sum + cbase + colsel, t1);
-                    atomicAdd(prm.stat_sq + cbase + colsel, t2);
+                if ((lane & 1) == 0) {
+                    s_stat[0][sub][c * 16 + colsel] = t1;
+                    s_stat[1][sub][c * 16 + colsel] = t2;
+                }
+            }
+        }
+        if (MODE == MODE_FPROP && prm.stat_sum != nullptr) {
+            // combine the 4 epilogue warps in shared memory, then 16-byte vector RED: the
+            // 2*Cout statistics live on a few cache lines and L2 serialises atomics per line
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            if (sub == 0) {
+                for (int j = lane * 4; j < BLOCK_N; j += 128) {
+                    const int cg = col0 + j;
+                    if (cg >= prm.n_total) break;
+                    float a[4], b[4];
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        a[e] = s_stat[0][0][j + e] + s_stat[0][1][j + e] + s_stat[0][2][j + e] +
+                               s_stat[0][3][j + e];
+                        b[e] = s_stat[1][0][j + e] + s_stat[1][1][j + e] + s_stat[1][2][j + e] +
+                               s_stat[1][3][j + e];
+                    }
+                    if (cg + 4 <= prm.n_total) {
+                        red_add_f32x4(prm.stat_sum + cg, a[0], a[1], a[2], a[3]);
+                        red_add_f32x4(prm.stat_sq + cg, b[0], b[1], b[2], b[3]);
+                    } else {
+                        for (int e = 0; e < 4 && cg + e < prm.n_total; ++e) {
+                            atomicAdd(prm.stat_sum + cg + e, a[e]);
+                            atomicAdd(prm.stat_sq + cg + e, b[e]);
+                        }
+                    }
                 }
             }
         }

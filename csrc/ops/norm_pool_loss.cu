@@ -97,6 +97,19 @@ __device__ __forceinline__ void block_reduce_cg(float (&s1)[8], float (&s2)[8], 
     }
 }
 
+// Per-channel reductions finish with atomics on a handful of cache lines (2*C floats), which the
+// L2 serialises per line: keep the CTA count at one per SM and use 16-byte vector RED.
+static inline int reduce_grid(long long nvec) {
+    long long blocks = (nvec + kEwThreads - 1) / kEwThreads;
+    if (blocks > 148) blocks = 148;
+    if (blocks < 1) blocks = 1;
+    return static_cast<int>(blocks);
+}
+__device__ __forceinline__ void red_add8(float* dst, const float (&v)[8]) {
+    red_add_f32x4(dst, v[0], v[1], v[2], v[3]);
+    red_add_f32x4(dst + 4, v[4], v[5], v[6], v[7]);
+}
+
 // ------------------------------------------------------------------------------------ BN stats
 // sum[c] += sum_m x[m,c]; sq[c] += sum_m x[m,c]^2   (buffers zeroed by the caller)
 __global__ void __launch_bounds__(kEwThreads) bn_stats_kernel(const bf16x8* __restrict__ x,
@@ -119,11 +132,8 @@ __global__ void __launch_bounds__(kEwThreads) bn_stats_kernel(const bf16x8* __re
     block_reduce_cg(s1, s2, cvec, sh);
     if (threadIdx.x < cvec) {
         const int cg = threadIdx.x;
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            atomicAdd(sum + cg * 8 + k, s1[k]);
-            atomicAdd(sq + cg * 8 + k, s2[k]);
-        }
+        red_add8(sum + cg * 8, s1);
+        red_add8(sq + cg * 8, s2);
     }
 }
 
@@ -265,11 +275,8 @@ bn_bwd_reduce_kernel(const bf16x8* __restrict__ dy1, const bf16x8* __restrict__ 
     }
     block_reduce_cg(s1, s2, cvec, sh);
     if (threadIdx.x < cvec) {
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            atomicAdd(dbeta + cg * 8 + k, s1[k]);
-            atomicAdd(dgamma + cg * 8 + k, s2[k]);
-        }
+        red_add8(dbeta + cg * 8, s1);
+        red_add8(dgamma + cg * 8, s2);
     }
 }
 
@@ -618,7 +625,7 @@ static inline bool cvec_ok(int C) { return C % 8 == 0 && (kEwThreads % (C / 8)) 
 extern "C" int dpt_bn_stats(const void* x, float* sum, float* sq, long long M, int C, void* stream) {
     if (!cvec_ok(C)) return DPT_ERR_SHAPE;
     const long long nvec = M * (C / 8);
-    bn_stats_kernel<<<ew_grid(nvec, C / 8), kEwThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+    bn_stats_kernel<<<reduce_grid(nvec), kEwThreads, 0, static_cast<cudaStream_t>(stream)>>>(
         static_cast<const bf16x8*>(x), sum, sq, nvec, C / 8);
     DPT_CHECK_LAUNCH();
 }
@@ -655,7 +662,7 @@ extern "C" int dpt_bn_bwd_reduce(const void* dy1, const void* dy2, const void* y
                                  float* dgamma, float* dbeta, long long M, int C, void* stream) {
     if (!cvec_ok(C)) return DPT_ERR_SHAPE;
     const long long nvec = M * (C / 8);
-    bn_bwd_reduce_kernel<<<ew_grid(nvec, C / 8), kEwThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+    bn_bwd_reduce_kernel<<<reduce_grid(nvec), kEwThreads, 0, static_cast<cudaStream_t>(stream)>>>(
         static_cast<const bf16x8*>(dy1), static_cast<const bf16x8*>(dy2),
         static_cast<const bf16x8*>(y), static_cast<const bf16x8*>(x), save_mean, save_invstd,
         static_cast<bf16x8*>(g_out), dgamma, dbeta, nvec, C / 8);
@@ -826,7 +833,7 @@ extern "C" int dpt_bn_fwd_train_noalloc(const void* x, const float* gamma, const
     cudaError_t e = cudaMemsetAsync(scratch, 0, sizeof(float) * 2 * C, st);
     if (e != cudaSuccess) return static_cast<int>(e);
     const long long nvec = M * (C / 8);
-    bn_stats_kernel<<<ew_grid(nvec, C / 8), kEwThreads, 0, st>>>(static_cast<const bf16x8*>(x), sum,
+    bn_stats_kernel<<<reduce_grid(nvec), kEwThreads, 0, st>>>(static_cast<const bf16x8*>(x), sum,
                                                                  sq, nvec, C / 8);
     const float unbias = M > 1 ? static_cast<float>(M) / static_cast<float>(M - 1) : 1.f;
     bn_fwd_kernel<<<ew_grid(nvec, C / 8), kEwThreads, 0, st>>>(
