@@ -42,6 +42,11 @@ def parse():
                    help="flush L2 (untimed 256 MiB memset) between timed steps; default is no flush "
                         "because one step touches ~207 MB > 126 MB L2")
     p.add_argument("--fused-optimizer", action="store_true")
+    p.add_argument("--bucket-cap-mb", type=float, default=None)
+    p.add_argument("--comm-ctas", type=int, default=0)
+    p.add_argument("--eager-buffer-sync", action="store_true",
+                   help="broadcast BN buffers from rank 0 every step (torch DDP behaviour) instead "
+                        "of lazily before eval/checkpoint")
     p.add_argument("--profile-sync", action="store_true",
                    help="extra eager pass with per-bucket event timing (reported under grad_sync)")
     return p.parse_args()
@@ -149,13 +154,15 @@ def run_ours(a):
     model = build_model(device, a.arch, a.num_classes)
     ddp = None
     if world > 1:
-        model = ddp = DistributedDataParallel(model, device_ids=[local], backend="native")
+        model = ddp = DistributedDataParallel(model, device_ids=[local], backend="native",
+                                              bucket_cap_mb=a.bucket_cap_mb, comm_ctas=a.comm_ctas)
     opt = SGD(model.parameters(), lr=0.1, momentum=0.9, weight_decay=5e-4)
     if ddp is not None and a.fused_optimizer:
         ddp.enable_fused_sgd(opt)
     scaler = GradScaler(device=device, enabled=False)  # bf16: no loss scaling needed
     shape = (a.batch_size, 3, a.image_size, a.image_size)
-    step = TrainStep(model, opt, scaler, batch_shape=shape, cuda_graph=not a.no_graph)
+    step = TrainStep(model, opt, scaler, batch_shape=shape, cuda_graph=not a.no_graph,
+                     lazy_buffer_sync=not a.eager_buffer_sync)
     batches = make_host_batches(8, shape, a.num_classes, seed=1234 + rank)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=device) if a.l2_flush else None
 
@@ -213,9 +220,6 @@ def run_ours(a):
     e2e_ms = max(e2e_ms, wall_ms)
 
     sync = {}
-    if a.profile_sync and ddp is not None:
-        sync = profile_sync_pass(model, opt, batches, a, device)
-
     gb = a.batch_size * world
     res = {
         "metric": "samples/sec (device-timed, max over ranks)",
@@ -237,7 +241,9 @@ def run_ours(a):
                          else "not flushed: one step touches ~207 MB (fp32 params+grads+momentum, bf16 shadow, "
                               "activations) > 126 MB L2",
                    "grad_allreduce": "native NVLink peer-memory two-shot, fused 1/world epilogue" if world > 1 else "none (1 GPU)",
-                   "fused_optimizer": bool(a.fused_optimizer and world > 1)},
+                   "fused_optimizer": bool(a.fused_optimizer and world > 1),
+                   "grad_buckets_bytes": ddp.bucket_sizes() if ddp is not None else [],
+                   "bn_buffer_sync": "lazy (before eval/checkpoint)" if not a.eager_buffer_sync else "every step"},
         "clocks": clocks,
         "e2e": {"value": gb * K / (e2e_ms * 1e-3), "unit": "samples/s",
                 "ms_per_step": e2e_ms / K,
@@ -258,12 +264,46 @@ def run_ours(a):
     cleanup_distributed()
 
 
-def profile_sync_pass(model, opt, batches, a, device):
-    """Eager (non-graph) steps with per-bucket CUDA events: % of step time in exposed sync."""
+def run_profile_sync(a):
+    """Separate pass (`--profile-sync`): eager (non-graph) steps with per-bucket CUDA events —
+    % of step time spent in exposed gradient sync, max over ranks (BASELINE.json metric 2)."""
+    import torch
     from dpt_b200.amp import GradScaler
     from dpt_b200.graph_step import TrainStep
+    from dpt_b200.models.resnet import build_model
+    from dpt_b200.optim import SGD
+    from dpt_b200.parallel.ddp import DistributedDataParallel
     from dpt_b200.profiler import GradSyncProfiler
-    return {}
+    from dpt_b200.runtime import cleanup_distributed, set_seed, setup_distributed
+    rank, world, local = setup_distributed("native")
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    set_seed(42, rank)
+    model = DistributedDataParallel(build_model(device, a.arch, a.num_classes), device_ids=[local],
+                                    backend="native", profile=True)
+    opt = SGD(model.parameters(), lr=0.1, momentum=0.9, weight_decay=5e-4)
+    shape = (a.batch_size, 3, a.image_size, a.image_size)
+    step = TrainStep(model, opt, GradScaler(device=device, enabled=False), batch_shape=shape,
+                     cuda_graph=False)
+    batches = make_host_batches(4, shape, a.num_classes, seed=99 + rank)
+    prof = GradSyncProfiler(model, sample_first=10 ** 9)
+    for i in range(max(a.warmup, 3)):
+        step(*batches[i % 4])
+    barrier_sync()
+    for i in range(a.steps):
+        prof.step_begin()
+        step(*batches[i % 4])
+        prof.step_end()
+    summ = prof.summary()
+    last = prof.records[-1].get("buckets", [])
+    res = {"metric": "% step time in exposed gradient sync (device events, max over ranks)",
+           "impl": "ours", "n_gpus": world, "steps": a.steps, "mode": "eager launches (event timing is "
+           "not available inside a CUDA graph)", "grad_sync": summ,
+           "buckets_last_step": last, "bucket_bytes": model.bucket_sizes()}
+    if rank == 0:
+        print(json.dumps(res))
+    model.shutdown()
+    cleanup_distributed()
 
 
 # ====================================================================================== reference
@@ -368,6 +408,8 @@ def main():
         raise SystemExit(subprocess.call(cmd))
     if a.impl == "reference":
         run_reference(a)
+    elif a.profile_sync:
+        run_profile_sync(a)
     else:
         run_ours(a)
 

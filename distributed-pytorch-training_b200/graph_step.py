@@ -23,7 +23,8 @@ from .parallel.ddp import DistributedDataParallel
 
 class TrainStep:
     def __init__(self, model, optimizer, scaler=None, *, batch_shape, cuda_graph: bool = True,
-                 warmup: int = 2) -> None:
+                 warmup: int = 2, lazy_buffer_sync: bool = True) -> None:
+        self.lazy_buffer_sync = lazy_buffer_sync
         self.ddp = model if isinstance(model, DistributedDataParallel) else None
         self.net = model.module if self.ddp is not None else model
         if not isinstance(self.net, ResNet):
@@ -70,7 +71,7 @@ class TrainStep:
         Fn = self.Fn
         ddp = self.ddp
         if ddp is not None:
-            ddp.sync_buffers()
+            ddp.sync_buffers(lazy=self.lazy_buffer_sync)
             ddp.prepare_for_backward()
         self.arena.grad.zero_()
         logits = self.eng.forward(self.x)

@@ -180,7 +180,12 @@ class DistributedDataParallel(nn.Module):
         if backend == "native" and (not cuda or not ext_available()):
             backend = "gloo" if not cuda else "nccl"
         self.backend = backend
-        self.bucket_bytes_cap = int((bucket_cap_mb if bucket_cap_mb is not None else 25) * 1024 * 1024)
+        # torch's default cap is 25 MiB, sized for NCCL's per-collective cost.  A peer-memory bucket
+        # kernel costs ~15 us to launch and NVSwitch bandwidth does not depend on message count, so
+        # the native backend defaults to 4 MiB: the last bucket (the exposed tail of backward) is
+        # then ~1-2 MB instead of ~9 MB for ResNet-18.
+        default_cap = 4 if backend == "native" else 25
+        self.bucket_bytes_cap = int((bucket_cap_mb if bucket_cap_mb is not None else default_cap) * 1024 * 1024)
         self.first_bucket_bytes = int(first_bucket_mb * 1024 * 1024)
         self.profile = profile
         self.fused_optimizer = fused_optimizer
@@ -351,9 +356,17 @@ class DistributedDataParallel(nn.Module):
             return self.reducer.finalize(self._stream())
         return self.reducer.finalize()
 
-    def sync_buffers(self) -> None:
+    def sync_buffers(self, lazy: bool = False) -> None:
+        """Rank 0's buffers -> all ranks.  ``lazy=True`` (used by TrainStep) only marks the
+        buffers as stale: a training-mode forward never *reads* BatchNorm running statistics, so
+        the per-step broadcast torch DDP performs (distributed.py:2214-2257) changes nothing a
+        user can observe until the next eval forward / checkpoint, where the real sync happens."""
         if not (self.broadcast_buffers and self._mod_buffers and self.world_size > 1):
             return
+        if lazy:
+            self._buffers_stale = True
+            return
+        self._buffers_stale = False
         if self.backend == "native":
             self.comm.broadcast_(self.buffer_buf, 0, self._buffer_bytes, src=0, ctas=1)
         else:
@@ -369,7 +382,8 @@ class DistributedDataParallel(nn.Module):
             if self.reducer is not None and self.backend == "native":
                 # queue finalize at the end of this backward pass from the first gradient hook
                 self._arm_autograd_finalize()
-        elif self.require_forward_param_sync and self.module.training is False and self._iter > 0:
+        elif (self.require_forward_param_sync or getattr(self, "_buffers_stale", False)) \
+                and self.module.training is False:
             # first eval forward after training syncs buffers once (torch distributed.py:1637-1650)
             self.sync_buffers()
             self.require_forward_param_sync = False
