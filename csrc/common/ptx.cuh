@@ -167,6 +167,16 @@ __host__ __device__ constexpr uint32_t make_idesc_bf16(int M, int N, int a_mn_ma
            | (uint32_t(N >> 3) << 17) | (uint32_t(M >> 4) << 24);
 }
 
+// ----------------------------------------------------------------------------- PDL
+// Programmatic dependent launch: a kernel launched with the programmatic-stream-serialization
+// attribute may start while its predecessor is still running; it must call pdl_wait() before
+// touching anything the predecessor wrote.  pdl_launch_dependents() lets the *next* kernel
+// start its prologue early.  Both are no-ops for ordinary launches.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+
 // ----------------------------------------------------------------------------- memory ops
 __device__ __forceinline__ void red_add_f32x4(float* p, float a, float b, float c, float d) {
     asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c),
@@ -208,4 +218,34 @@ __device__ __forceinline__ void st_peer_f32x4(float4* p, float4 v) {
                  : "memory");
 }
 
+}  // namespace dpt
+
+// ----------------------------------------------------------------------------- host launch
+#include <cstdlib>
+#include <utility>
+namespace dpt {
+inline bool pdl_enabled() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = std::getenv("DPT_PDL");
+        v = (e == nullptr || e[0] != '0') ? 1 : 0;
+    }
+    return v == 1;
+}
+// Launch with the programmatic-stream-serialization attribute (unless DPT_PDL=0).
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                              cudaStream_t st, Args&&... args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(std::forward<Args>(args))...);
+}
 }  // namespace dpt

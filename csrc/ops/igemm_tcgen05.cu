@@ -182,6 +182,10 @@ igemm_kernel(const __grid_constant__ IgemmMaps maps, const __grid_constant__ Ige
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = tmem_base_smem;
+    // everything above (barrier init, TMEM allocation, descriptor prefetch) overlapped the tail
+    // of the previous kernel; from here on we read what it produced
+    pdl_launch_dependents();
+    pdl_wait();
 
     if (warp == 0) {
         // ============================================================ TMA producer
@@ -492,7 +496,8 @@ static int launch_cfg(const IgemmMaps& maps, const IgemmParams& prm, dim3 grid, 
         if (e != cudaSuccess) return int(e);
         attr_done = true;
     }
-    kern<<<grid, kNumThreads, smem, st>>>(maps, prm);
+    cudaError_t le = launch_pdl(kern, grid, dim3(kNumThreads), static_cast<size_t>(smem), st, maps, prm);
+    if (le != cudaSuccess) return int(le);
     return int(cudaGetLastError());
 }
 

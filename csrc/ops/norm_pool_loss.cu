@@ -116,6 +116,8 @@ __global__ void __launch_bounds__(kEwThreads) bn_stats_kernel(const bf16x8* __re
                                                               float* __restrict__ sum,
                                                               float* __restrict__ sq, long long nvec,
                                                               int cvec) {
+    pdl_launch_dependents();
+    pdl_wait();
     __shared__ float sh[2][kEwThreads / 32][32][8 + 1];
     const long long stride = static_cast<long long>(gridDim.x) * kEwThreads;
     long long i = static_cast<long long>(blockIdx.x) * kEwThreads + threadIdx.x;
@@ -149,6 +151,8 @@ bn_fwd_kernel(const bf16x8* __restrict__ x, const float* __restrict__ sum,
               float* __restrict__ running_var, long long* __restrict__ num_batches_tracked,
               long long nvec, int cvec, float inv_m, float unbias, float momentum, float eps,
               int relu) {
+    pdl_launch_dependents();
+    pdl_wait();
     const long long stride = static_cast<long long>(gridDim.x) * kEwThreads;
     long long i = static_cast<long long>(blockIdx.x) * kEwThreads + threadIdx.x;
     const int cg = static_cast<int>(i % cvec);
@@ -197,6 +201,8 @@ bn_eval_kernel(const bf16x8* __restrict__ x, const float* __restrict__ gamma,
                const float* __restrict__ beta, const float* __restrict__ running_mean,
                const float* __restrict__ running_var, const bf16x8* __restrict__ residual,
                bf16x8* __restrict__ y, long long nvec, int cvec, float eps, int relu) {
+    pdl_launch_dependents();
+    pdl_wait();
     const long long stride = static_cast<long long>(gridDim.x) * kEwThreads;
     long long i = static_cast<long long>(blockIdx.x) * kEwThreads + threadIdx.x;
     const int cg = static_cast<int>(i % cvec);
@@ -235,6 +241,8 @@ bn_bwd_reduce_kernel(const bf16x8* __restrict__ dy1, const bf16x8* __restrict__ 
                      const float* __restrict__ save_mean, const float* __restrict__ save_invstd,
                      bf16x8* __restrict__ g_out, float* __restrict__ dgamma,
                      float* __restrict__ dbeta, long long nvec, int cvec) {
+    pdl_launch_dependents();
+    pdl_wait();
     __shared__ float sh[2][kEwThreads / 32][32][8 + 1];
     const long long stride = static_cast<long long>(gridDim.x) * kEwThreads;
     long long i = static_cast<long long>(blockIdx.x) * kEwThreads + threadIdx.x;
@@ -287,6 +295,8 @@ bn_bwd_apply_kernel(const bf16x8* __restrict__ g, const bf16x8* __restrict__ x,
                     const float* __restrict__ gamma, const float* __restrict__ dgamma,
                     const float* __restrict__ dbeta, bf16x8* __restrict__ dx, long long nvec,
                     int cvec, float inv_m, float grad_unscale) {
+    pdl_launch_dependents();
+    pdl_wait();
     const long long stride = static_cast<long long>(gridDim.x) * kEwThreads;
     long long i = static_cast<long long>(blockIdx.x) * kEwThreads + threadIdx.x;
     const int cg = static_cast<int>(i % cvec);
@@ -318,6 +328,8 @@ bn_bwd_apply_kernel(const bf16x8* __restrict__ g, const bf16x8* __restrict__ x,
 __global__ void __launch_bounds__(kEwThreads)
 maxpool_fwd_kernel(const bf16x8* __restrict__ x, bf16x8* __restrict__ y, uint8_t* __restrict__ idx,
                    int N, int H, int W, int cvec, int P, int Q) {
+    pdl_launch_dependents();
+    pdl_wait();
     const long long total = static_cast<long long>(N) * P * Q * cvec;
     for (long long i = static_cast<long long>(blockIdx.x) * kEwThreads + threadIdx.x; i < total;
          i += static_cast<long long>(gridDim.x) * kEwThreads) {
@@ -364,6 +376,8 @@ __global__ void __launch_bounds__(kEwThreads)
 maxpool_bwd_kernel(const bf16x8* __restrict__ dy, const bf16x8* __restrict__ dy2,
                    const uint8_t* __restrict__ idx,
                    bf16x8* __restrict__ dx, int N, int H, int W, int cvec, int P, int Q) {
+    pdl_launch_dependents();
+    pdl_wait();
     const long long total = static_cast<long long>(N) * H * W * cvec;
     for (long long i = static_cast<long long>(blockIdx.x) * kEwThreads + threadIdx.x; i < total;
          i += static_cast<long long>(gridDim.x) * kEwThreads) {
@@ -412,6 +426,8 @@ __global__ void __launch_bounds__(256)
 head_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w,
                 const float* __restrict__ b, float* __restrict__ pooled,
                 float* __restrict__ logits, int HW, int C, int K) {
+    pdl_launch_dependents();
+    pdl_wait();
     extern __shared__ float sp[];
     const int n = blockIdx.x;
     const float inv = 1.f / HW;
@@ -437,6 +453,8 @@ head_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w
 __global__ void __launch_bounds__(256)
 head_bwd_dx_kernel(const float* __restrict__ dlogits, const float* __restrict__ w,
                    __nv_bfloat16* __restrict__ dx, int HW, int C, int K) {
+    pdl_launch_dependents();
+    pdl_wait();
     extern __shared__ float sd[];
     const int n = blockIdx.x;
     for (int k = threadIdx.x; k < K; k += blockDim.x) sd[k] = dlogits[static_cast<long long>(n) * K + k];
@@ -455,6 +473,8 @@ __global__ void __launch_bounds__(64)
 head_bwd_dw_kernel(const float* __restrict__ dlogits, const float* __restrict__ pooled,
                    float* __restrict__ dw, float* __restrict__ db, int B, int C, int K,
                    float unscale) {
+    pdl_launch_dependents();
+    pdl_wait();
     const int k = blockIdx.y;
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c < C) {
@@ -480,6 +500,8 @@ __global__ void __launch_bounds__(1024)
 ce_fwd_bwd_kernel(const float* __restrict__ logits, const long long* __restrict__ target,
                   float* __restrict__ loss_out, float* __restrict__ dlogits,
                   const float* __restrict__ loss_scale, double* __restrict__ metrics, int B, int K) {
+    pdl_launch_dependents();
+    pdl_wait();
     __shared__ float s_loss[32];
     __shared__ int s_corr[32];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
@@ -554,6 +576,8 @@ ce_fwd_bwd_kernel(const float* __restrict__ logits, const long long* __restrict_
 __global__ void __launch_bounds__(kEwThreads)
 im2col_nchw_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ out, int N, int C,
                    int H, int W, int R, int S, int stride, int pad, int P, int Q, int ldk) {
+    pdl_launch_dependents();
+    pdl_wait();
     // one thread = 8 consecutive columns of one row (ldk % 8 == 0): a single 16-byte store
     const int cv = ldk / 8;
     const long long total = static_cast<long long>(N) * P * Q * cv;
@@ -590,6 +614,8 @@ im2col_nchw_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ out,
 __global__ void __launch_bounds__(kEwThreads)
 pad_rows_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int rows, int cols,
                 int ld) {
+    pdl_launch_dependents();
+    pdl_wait();
     const int total = rows * ld;
     for (int i = blockIdx.x * kEwThreads + threadIdx.x; i < total; i += gridDim.x * kEwThreads) {
         const int c = i % ld, r = i / ld;
@@ -601,6 +627,8 @@ pad_rows_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, 
 __global__ void __launch_bounds__(kEwThreads)
 nchw_to_nhwc_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y, int N, int C, int H,
                     int W) {
+    pdl_launch_dependents();
+    pdl_wait();
     const long long total = static_cast<long long>(N) * C * H * W;
     for (long long i = static_cast<long long>(blockIdx.x) * kEwThreads + threadIdx.x; i < total;
          i += static_cast<long long>(gridDim.x) * kEwThreads) {
@@ -625,7 +653,7 @@ static inline bool cvec_ok(int C) { return C % 8 == 0 && (kEwThreads % (C / 8)) 
 extern "C" int dpt_bn_stats(const void* x, float* sum, float* sq, long long M, int C, void* stream) {
     if (!cvec_ok(C)) return DPT_ERR_SHAPE;
     const long long nvec = M * (C / 8);
-    bn_stats_kernel<<<reduce_grid(nvec), kEwThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+    launch_pdl(bn_stats_kernel, dim3(reduce_grid(nvec)), dim3(kEwThreads), 0, static_cast<cudaStream_t>(stream), 
         static_cast<const bf16x8*>(x), sum, sq, nvec, C / 8);
     DPT_CHECK_LAUNCH();
 }
@@ -638,7 +666,7 @@ extern "C" int dpt_bn_fwd_train(const void* x, const float* sum, const float* sq
     if (!cvec_ok(C)) return DPT_ERR_SHAPE;
     const long long nvec = M * (C / 8);
     const float unbias = M > 1 ? static_cast<float>(M) / static_cast<float>(M - 1) : 1.f;
-    bn_fwd_kernel<<<ew_grid(nvec, C / 8), kEwThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+    launch_pdl(bn_fwd_kernel, dim3(ew_grid(nvec, C / 8)), dim3(kEwThreads), 0, static_cast<cudaStream_t>(stream), 
         static_cast<const bf16x8*>(x), sum, sq, gamma, beta, static_cast<const bf16x8*>(residual),
         static_cast<bf16x8*>(y), save_mean, save_invstd, running_mean, running_var,
         num_batches_tracked, nvec, C / 8, 1.f / static_cast<float>(M), unbias, momentum, eps, relu);
@@ -651,7 +679,7 @@ extern "C" int dpt_bn_fwd_eval(const void* x, const float* gamma, const float* b
                                int relu, void* stream) {
     if (!cvec_ok(C)) return DPT_ERR_SHAPE;
     const long long nvec = M * (C / 8);
-    bn_eval_kernel<<<ew_grid(nvec, C / 8), kEwThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+    launch_pdl(bn_eval_kernel, dim3(ew_grid(nvec, C / 8)), dim3(kEwThreads), 0, static_cast<cudaStream_t>(stream), 
         static_cast<const bf16x8*>(x), gamma, beta, running_mean, running_var,
         static_cast<const bf16x8*>(residual), static_cast<bf16x8*>(y), nvec, C / 8, eps, relu);
     DPT_CHECK_LAUNCH();
@@ -662,7 +690,7 @@ extern "C" int dpt_bn_bwd_reduce(const void* dy1, const void* dy2, const void* y
                                  float* dgamma, float* dbeta, long long M, int C, void* stream) {
     if (!cvec_ok(C)) return DPT_ERR_SHAPE;
     const long long nvec = M * (C / 8);
-    bn_bwd_reduce_kernel<<<reduce_grid(nvec), kEwThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+    launch_pdl(bn_bwd_reduce_kernel, dim3(reduce_grid(nvec)), dim3(kEwThreads), 0, static_cast<cudaStream_t>(stream), 
         static_cast<const bf16x8*>(dy1), static_cast<const bf16x8*>(dy2),
         static_cast<const bf16x8*>(y), static_cast<const bf16x8*>(x), save_mean, save_invstd,
         static_cast<bf16x8*>(g_out), dgamma, dbeta, nvec, C / 8);
@@ -674,7 +702,7 @@ extern "C" int dpt_bn_bwd_apply(const void* g, const void* x, const float* save_
                                 const float* dbeta, void* dx, long long M, int C, void* stream) {
     if (!cvec_ok(C)) return DPT_ERR_SHAPE;
     const long long nvec = M * (C / 8);
-    bn_bwd_apply_kernel<<<ew_grid(nvec, C / 8), kEwThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+    launch_pdl(bn_bwd_apply_kernel, dim3(ew_grid(nvec, C / 8)), dim3(kEwThreads), 0, static_cast<cudaStream_t>(stream), 
         static_cast<const bf16x8*>(g), static_cast<const bf16x8*>(x), save_mean, save_invstd, gamma,
         dgamma, dbeta, static_cast<bf16x8*>(dx), nvec, C / 8, 1.f / static_cast<float>(M), 1.f);
     DPT_CHECK_LAUNCH();
@@ -685,7 +713,7 @@ extern "C" int dpt_maxpool3x3s2_fwd(const void* x, void* y, void* idx, int N, in
     if (C % 8 != 0) return DPT_ERR_SHAPE;
     const int P = (H + 2 - 3) / 2 + 1, Q = (W + 2 - 3) / 2 + 1;
     const long long total = static_cast<long long>(N) * P * Q * (C / 8);
-    maxpool_fwd_kernel<<<ew_grid(total, 1), kEwThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+    launch_pdl(maxpool_fwd_kernel, dim3(ew_grid(total, 1)), dim3(kEwThreads), 0, static_cast<cudaStream_t>(stream), 
         static_cast<const bf16x8*>(x), static_cast<bf16x8*>(y), static_cast<uint8_t*>(idx), N, H, W,
         C / 8, P, Q);
     DPT_CHECK_LAUNCH();
@@ -696,7 +724,7 @@ extern "C" int dpt_maxpool3x3s2_bwd(const void* dy, const void* dy2, const void*
     if (C % 8 != 0) return DPT_ERR_SHAPE;
     const int P = (H + 2 - 3) / 2 + 1, Q = (W + 2 - 3) / 2 + 1;
     const long long total = static_cast<long long>(N) * H * W * (C / 8);
-    maxpool_bwd_kernel<<<ew_grid(total, 1), kEwThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+    launch_pdl(maxpool_bwd_kernel, dim3(ew_grid(total, 1)), dim3(kEwThreads), 0, static_cast<cudaStream_t>(stream), 
         static_cast<const bf16x8*>(dy), static_cast<const bf16x8*>(dy2),
         static_cast<const uint8_t*>(idx), static_cast<bf16x8*>(dx), N, H, W, C / 8, P, Q);
     DPT_CHECK_LAUNCH();
@@ -704,7 +732,7 @@ extern "C" int dpt_maxpool3x3s2_bwd(const void* dy, const void* dy2, const void*
 
 extern "C" int dpt_head_fwd(const void* x, const float* w, const float* b, float* pooled,
                             float* logits, int B, int HW, int C, int K, void* stream) {
-    head_fwd_kernel<<<B, 256, C * sizeof(float), static_cast<cudaStream_t>(stream)>>>(
+    launch_pdl(head_fwd_kernel, dim3(B), dim3(256), C * sizeof(float), static_cast<cudaStream_t>(stream), 
         static_cast<const __nv_bfloat16*>(x), w, b, pooled, logits, HW, C, K);
     DPT_CHECK_LAUNCH();
 }
@@ -713,10 +741,10 @@ extern "C" int dpt_head_bwd(const float* dlogits, const float* w, const float* p
                             float* dw, float* db, int B, int HW, int C, int K, void* stream) {
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (dx != nullptr)
-        head_bwd_dx_kernel<<<B, 256, K * sizeof(float), st>>>(
+        launch_pdl(head_bwd_dx_kernel, dim3(B), dim3(256), K * sizeof(float), st, 
             dlogits, w, static_cast<__nv_bfloat16*>(dx), HW, C, K);
     dim3 grid((C + 63) / 64, K);
-    head_bwd_dw_kernel<<<grid, 64, 0, st>>>(dlogits, pooled, dw, db, B, C, K, 1.f);
+    launch_pdl(head_bwd_dw_kernel, dim3(grid), dim3(64), 0, st, dlogits, pooled, dw, db, B, C, K, 1.f);
     DPT_CHECK_LAUNCH();
 }
 
@@ -726,7 +754,7 @@ extern "C" int dpt_cross_entropy(const float* logits, const long long* target, f
     int threads = B * 32;
     if (threads > 1024) threads = 1024;
     if (threads < 32) threads = 32;
-    ce_fwd_bwd_kernel<<<1, threads, 0, static_cast<cudaStream_t>(stream)>>>(
+    launch_pdl(ce_fwd_bwd_kernel, dim3(1), dim3(threads), 0, static_cast<cudaStream_t>(stream), 
         logits, target, loss, dlogits, loss_scale, metrics, B, K);
     DPT_CHECK_LAUNCH();
 }
@@ -736,15 +764,14 @@ extern "C" int dpt_im2col_nchw_f32(const float* x, void* out, int N, int C, int 
     const int P = (H + 2 * pad - R) / stride + 1, Q = (W + 2 * pad - S) / stride + 1;
     if (ldk % 8 != 0) return DPT_ERR_SHAPE;
     const long long total = static_cast<long long>(N) * P * Q * (ldk / 8);
-    im2col_nchw_kernel<<<ew_grid(total, 1), kEwThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+    launch_pdl(im2col_nchw_kernel, dim3(ew_grid(total, 1)), dim3(kEwThreads), 0, static_cast<cudaStream_t>(stream), 
         x, static_cast<__nv_bfloat16*>(out), N, C, H, W, R, S, stride, pad, P, Q, ldk);
     DPT_CHECK_LAUNCH();
 }
 
 extern "C" int dpt_pad_rows_f32_to_bf16(const float* src, void* dst, int rows, int cols, int ld,
                                         void* stream) {
-    pad_rows_kernel<<<ew_grid(static_cast<long long>(rows) * ld, 1), kEwThreads, 0,
-                      static_cast<cudaStream_t>(stream)>>>(src, static_cast<__nv_bfloat16*>(dst),
+    launch_pdl(pad_rows_kernel, dim3(ew_grid(static_cast<long long>(rows) * ld, 1)), dim3(kEwThreads), 0, static_cast<cudaStream_t>(stream), src, static_cast<__nv_bfloat16*>(dst),
                                                            rows, cols, ld);
     DPT_CHECK_LAUNCH();
 }
@@ -752,7 +779,7 @@ extern "C" int dpt_pad_rows_f32_to_bf16(const float* src, void* dst, int rows, i
 extern "C" int dpt_nchw_f32_to_nhwc_bf16(const float* x, void* y, int N, int C, int H, int W,
                                          void* stream) {
     const long long total = static_cast<long long>(N) * C * H * W;
-    nchw_to_nhwc_kernel<<<ew_grid(total, 1), kEwThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+    launch_pdl(nchw_to_nhwc_kernel, dim3(ew_grid(total, 1)), dim3(kEwThreads), 0, static_cast<cudaStream_t>(stream), 
         x, static_cast<__nv_bfloat16*>(y), N, C, H, W);
     DPT_CHECK_LAUNCH();
 }
@@ -833,10 +860,10 @@ extern "C" int dpt_bn_fwd_train_noalloc(const void* x, const float* gamma, const
     cudaError_t e = cudaMemsetAsync(scratch, 0, sizeof(float) * 2 * C, st);
     if (e != cudaSuccess) return static_cast<int>(e);
     const long long nvec = M * (C / 8);
-    bn_stats_kernel<<<reduce_grid(nvec), kEwThreads, 0, st>>>(static_cast<const bf16x8*>(x), sum,
+    launch_pdl(bn_stats_kernel, dim3(reduce_grid(nvec)), dim3(kEwThreads), 0, st, static_cast<const bf16x8*>(x), sum,
                                                                  sq, nvec, C / 8);
     const float unbias = M > 1 ? static_cast<float>(M) / static_cast<float>(M - 1) : 1.f;
-    bn_fwd_kernel<<<ew_grid(nvec, C / 8), kEwThreads, 0, st>>>(
+    launch_pdl(bn_fwd_kernel, dim3(ew_grid(nvec, C / 8)), dim3(kEwThreads), 0, st, 
         static_cast<const bf16x8*>(x), sum, sq, gamma, beta, static_cast<const bf16x8*>(residual),
         static_cast<bf16x8*>(y), save_mean, save_invstd, running_mean, running_var,
         num_batches_tracked, nvec, C / 8, 1.f / static_cast<float>(M), unbias, momentum, eps, relu);

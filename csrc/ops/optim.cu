@@ -12,6 +12,7 @@
 #include <cstdint>
 
 #include "../../include/dptb200.h"
+#include "../common/ptx.cuh"
 
 namespace dpt {
 
@@ -23,6 +24,8 @@ __device__ __forceinline__ bool finite4(float4 v) {
 __global__ void __launch_bounds__(256)
 amp_unscale_kernel(float* __restrict__ g, long long n, const float* __restrict__ inv_scale,
                    float* __restrict__ found_inf) {
+    pdl_launch_dependents();
+    pdl_wait();
     const float s = inv_scale ? *inv_scale : 1.f;
     bool bad = false;
     const long long n4 = n / 4;
@@ -47,6 +50,8 @@ amp_unscale_kernel(float* __restrict__ g, long long n, const float* __restrict__
 __global__ void amp_update_scale_kernel(float* scale, int* growth_tracker, float* found_inf,
                                         float* inv_scale_out, float growth_factor,
                                         float backoff_factor, int growth_interval) {
+    pdl_launch_dependents();
+    pdl_wait();
     if (threadIdx.x == 0 && blockIdx.x == 0) {
         if (*found_inf > 0.f) {
             *scale = *scale * backoff_factor;
@@ -75,6 +80,8 @@ sgd_flat_kernel(float* __restrict__ p, const float* __restrict__ g, float* __res
                 __nv_bfloat16* __restrict__ shadow, long long n, float lr, float momentum,
                 float dampening, float wd, int nesterov, const float* __restrict__ grad_scale,
                 const float* __restrict__ found_inf) {
+    pdl_launch_dependents();
+    pdl_wait();
     if (found_inf != nullptr && *found_inf > 0.f) return;
     const float gs = grad_scale ? *grad_scale : 1.f;
     const long long n4 = n / 4;
@@ -126,6 +133,8 @@ adam_flat_kernel(float* __restrict__ p, const float* __restrict__ g, float* __re
                  float beta1, float beta2, float eps, float wd, int decoupled,
                  const int* __restrict__ step_count, const float* __restrict__ grad_scale,
                  const float* __restrict__ found_inf) {
+    pdl_launch_dependents();
+    pdl_wait();
     if (found_inf != nullptr && *found_inf > 0.f) return;
     const float gs = grad_scale ? *grad_scale : 1.f;
     const float t = static_cast<float>(*step_count + 1);
@@ -152,12 +161,16 @@ adam_flat_kernel(float* __restrict__ p, const float* __restrict__ g, float* __re
 }
 
 __global__ void step_inc_kernel(int* step_count, const float* found_inf) {
+    pdl_launch_dependents();
+    pdl_wait();
     if (found_inf != nullptr && *found_inf > 0.f) return;
     *step_count += 1;
 }
 
 __global__ void __launch_bounds__(256)
 cast_f32_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, long long n) {
+    pdl_launch_dependents();
+    pdl_wait();
     for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
          i += static_cast<long long>(gridDim.x) * blockDim.x)
         dst[i] = __float2bfloat16_rn(src[i]);
@@ -176,7 +189,7 @@ using namespace dpt;
 
 extern "C" int dpt_amp_unscale(float* g, long long n, const float* inv_scale, float* found_inf,
                                void* stream) {
-    amp_unscale_kernel<<<flat_grid(n), 256, 0, static_cast<cudaStream_t>(stream)>>>(g, n, inv_scale,
+    launch_pdl(amp_unscale_kernel, dim3(flat_grid(n)), dim3(256), 0, static_cast<cudaStream_t>(stream), g, n, inv_scale,
                                                                                    found_inf);
     return static_cast<int>(cudaGetLastError());
 }
@@ -184,7 +197,7 @@ extern "C" int dpt_amp_unscale(float* g, long long n, const float* inv_scale, fl
 extern "C" int dpt_amp_update_scale(float* scale, int* growth_tracker, float* found_inf,
                                     float* inv_scale_out, float growth_factor, float backoff_factor,
                                     int growth_interval, void* stream) {
-    amp_update_scale_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(
+    launch_pdl(amp_update_scale_kernel, dim3(1), dim3(32), 0, static_cast<cudaStream_t>(stream), 
         scale, growth_tracker, found_inf, inv_scale_out, growth_factor, backoff_factor,
         growth_interval);
     return static_cast<int>(cudaGetLastError());
@@ -193,7 +206,7 @@ extern "C" int dpt_amp_update_scale(float* scale, int* growth_tracker, float* fo
 extern "C" int dpt_sgd_flat(float* p, const float* g, float* m, void* shadow, long long n, float lr,
                             float momentum, float dampening, float wd, int nesterov,
                             const float* grad_scale, const float* found_inf, void* stream) {
-    sgd_flat_kernel<<<flat_grid(n), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+    launch_pdl(sgd_flat_kernel, dim3(flat_grid(n)), dim3(256), 0, static_cast<cudaStream_t>(stream), 
         p, g, m, static_cast<__nv_bfloat16*>(shadow), n, lr, momentum, dampening, wd, nesterov,
         grad_scale, found_inf);
     return static_cast<int>(cudaGetLastError());
@@ -204,15 +217,15 @@ extern "C" int dpt_adam_flat(float* p, const float* g, float* m, float* v, void*
                              int* step_count, const float* grad_scale, const float* found_inf,
                              void* stream) {
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    adam_flat_kernel<<<flat_grid(n), 256, 0, st>>>(p, g, m, v, static_cast<__nv_bfloat16*>(shadow),
+    launch_pdl(adam_flat_kernel, dim3(flat_grid(n)), dim3(256), 0, st, p, g, m, v, static_cast<__nv_bfloat16*>(shadow),
                                                    n, lr, beta1, beta2, eps, wd, decoupled,
                                                    step_count, grad_scale, found_inf);
-    step_inc_kernel<<<1, 1, 0, st>>>(step_count, found_inf);
+    launch_pdl(step_inc_kernel, dim3(1), dim3(1), 0, st, step_count, found_inf);
     return static_cast<int>(cudaGetLastError());
 }
 
 extern "C" int dpt_cast_f32_to_bf16(const float* src, void* dst, long long n, void* stream) {
-    cast_f32_bf16_kernel<<<flat_grid(n * 4), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+    launch_pdl(cast_f32_bf16_kernel, dim3(flat_grid(n * 4)), dim3(256), 0, static_cast<cudaStream_t>(stream), 
         src, static_cast<__nv_bfloat16*>(dst), n);
     return static_cast<int>(cudaGetLastError());
 }
