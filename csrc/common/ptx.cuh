@@ -224,6 +224,14 @@ __device__ __forceinline__ void st_peer_f32x4(float4* p, float4 v) {
 #include <cstdlib>
 #include <utility>
 namespace dpt {
+// The programmatic attribute only orders a kernel after the previous *kernel of its stream*;
+// a dependency that entered the stream through cudaStreamWaitEvent (another stream's work) is
+// NOT covered by griddepcontrol.wait.  The first kernel launched after such a wait must
+// therefore be an ordinary launch: callers announce it with dpt_pdl_skip_next().
+inline int& pdl_skip_flag() {
+    static int f = 0;
+    return f;
+}
 inline bool pdl_enabled() {
     static int v = -1;
     if (v < 0) {
@@ -245,7 +253,12 @@ inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, siz
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
-    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    bool use = pdl_enabled();
+    if (pdl_skip_flag()) {
+        use = false;
+        pdl_skip_flag() = 0;
+    }
+    cfg.numAttrs = use ? 1 : 0;
     return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(std::forward<Args>(args))...);
 }
 }  // namespace dpt

@@ -130,7 +130,7 @@ igemm_kernel(const __grid_constant__ IgemmMaps maps, const __grid_constant__ Ige
 
     // ---------------------------------------------------------------- tile coordinates
     int cls = 0, split = blockIdx.z;
-    if (MODE != MODE_WGRAD && prm.nclasses > 1) {
+    if (MODE != MODE_WGRAD) {
         cls = blockIdx.z / prm.splits;
         split = blockIdx.z % prm.splits;
     }
@@ -409,6 +409,9 @@ igemm_kernel(const __grid_constant__ IgemmMaps maps, const __grid_constant__ Ige
         }
     }
 
+    // Reductions (split-K accumulators, BN statistics) are fire-and-forget: make sure they have
+    // been performed before this CTA counts as complete for a programmatically dependent kernel.
+    if (warp >= 2 && (prm.out_mode == OUT_F32_ATOMIC || prm.stat_sum != nullptr)) __threadfence();
     tc_fence_before();
     __syncthreads();
     if (warp == 1) tmem_dealloc(tmem_base, kTmemCols);
@@ -495,6 +498,14 @@ static int launch_cfg(const IgemmMaps& maps, const IgemmParams& prm, dim3 grid, 
             cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return int(e);
         attr_done = true;
+    }
+    {
+        static int igemm_pdl = -1;
+        if (igemm_pdl < 0) {
+            const char* e = std::getenv("DPT_PDL_IGEMM");
+            igemm_pdl = (e == nullptr || e[0] != '0') ? 1 : 0;
+        }
+        if (!igemm_pdl) pdl_skip_flag() = 1;
     }
     cudaError_t le = launch_pdl(kern, grid, dim3(kNumThreads), static_cast<size_t>(smem), st, maps, prm);
     if (le != cudaSuccess) return int(le);
@@ -638,9 +649,24 @@ extern "C" int dpt_conv_fprop(const void* x, const void* w, void* y, int N, int 
 }
 
 // dX = conv_dgrad(dY, W) [+ conv_dgrad(dY2, W2) for a second conv reading the same input].
+extern "C" int dpt_conv_dgrad_ex(const void* dy, const void* w, void* dx, int N, int H, int W,
+                                 int Cin, int Cout, int R, int S, int stride, int pad,
+                                 const void* dy2, const void* w2, int R2, int S2, int pad2,
+                                 int out_f32_atomic, int splits, void* stream);
+
 extern "C" int dpt_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin,
                               int Cout, int R, int S, int stride, int pad, const void* dy2,
                               const void* w2, int R2, int S2, int pad2, void* stream) {
+    return dpt_conv_dgrad_ex(dy, w, dx, N, H, W, Cin, Cout, R, S, stride, pad, dy2, w2, R2, S2, pad2,
+                             0, 1, stream);
+}
+
+// out_f32_atomic = 1: dx is fp32 (pre-zeroed) and the k loop is split over `splits` CTAs per
+// tile, reduced with vector RED (fills the machine when the tile grid is tiny).
+extern "C" int dpt_conv_dgrad_ex(const void* dy, const void* w, void* dx, int N, int H, int W,
+                                 int Cin, int Cout, int R, int S, int stride, int pad,
+                                 const void* dy2, const void* w2, int R2, int S2, int pad2,
+                                 int out_f32_atomic, int splits, void* stream) {
     if (Cin % 8 != 0 || Cout % 8 != 0 || (stride != 1 && stride != 2)) return DPT_ERR_SHAPE;
     const int P = (H + 2 * pad - R) / stride + 1, Q = (W + 2 * pad - S) / stride + 1;
     IgemmMaps maps;
@@ -715,18 +741,19 @@ extern "C" int dpt_conv_dgrad(const void* dy, const void* w, void* dx, int N, in
     prm.NB = N;
     // (odd H/W with stride 2: classes hp=1 have one row fewer; mask through OH/OW below)
     prm.chunks = (Cout + 63) / 64;
-    prm.splits = 1;
+    if (!out_f32_atomic || splits < 1) splits = 1;
+    prm.splits = splits;
     prm.nclasses = ncls;
     prm.n_total = Cin;
     prm.out = dx;
-    prm.out_mode = OUT_BF16;
+    prm.out_mode = out_f32_atomic ? OUT_F32_ATOMIC : OUT_BF16;
     prm.ldo = Cin;
     prm.OH = H;
     prm.OW = W;
     prm.osh = stride;
     prm.osw = stride;
     if (stride == 2 && ((H & 1) || (W & 1))) return DPT_ERR_SHAPE;  // TODO: odd sizes
-    dim3 grid(prm.tiles_q * prm.tiles_p * prm.tiles_n, (Cin + block_n - 1) / block_n, ncls);
+    dim3 grid(prm.tiles_q * prm.tiles_p * prm.tiles_n, (Cin + block_n - 1) / block_n, ncls * splits);
     return launch<MODE_DGRAD>(maps, prm, grid, block_n, static_cast<cudaStream_t>(stream));
 }
 

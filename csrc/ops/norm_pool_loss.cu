@@ -232,11 +232,104 @@ bn_eval_kernel(const bf16x8* __restrict__ x, const float* __restrict__ gamma,
     }
 }
 
+// Column-strip BatchNorm training forward for small tensors whose producer is a split-K conv with
+// fp32 atomic output: one CTA owns 8 channels for ALL rows, so statistics and normalisation
+// happen in a single launch.  Writes y (bf16) and a bf16 copy of x for the backward pass.
+__global__ void __launch_bounds__(kEwThreads)
+bn_fwd_small_f32_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
+                        const float* __restrict__ beta, const bf16x8* __restrict__ residual,
+                        bf16x8* __restrict__ y, bf16x8* __restrict__ x_bf16,
+                        float* __restrict__ save_mean, float* __restrict__ save_invstd,
+                        float* __restrict__ running_mean, float* __restrict__ running_var,
+                        long long* __restrict__ num_batches_tracked, int M, int cvec, float inv_m,
+                        float unbias, float momentum, float eps, int relu) {
+    __shared__ float sh[2][kEwThreads / 32][8];
+    __shared__ float s_scale[8], s_shift[8];
+    const int cg = blockIdx.x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float s1[8] = {0, 0, 0, 0, 0, 0, 0, 0}, s2[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int m = threadIdx.x; m < M; m += kEwThreads) {
+        const float4* p4 = reinterpret_cast<const float4*>(x + (static_cast<long long>(m) * cvec + cg) * 8);
+        const float4 a = p4[0], b = p4[1];
+        const float f[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            s1[k] += f[k];
+            s2[k] += f[k] * f[k];
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            s1[k] += __shfl_xor_sync(0xffffffffu, s1[k], o);
+            s2[k] += __shfl_xor_sync(0xffffffffu, s2[k], o);
+        }
+    }
+    if (lane == 0) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            sh[0][warp][k] = s1[k];
+            sh[1][warp][k] = s2[k];
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x < 8) {
+        const int k = threadIdx.x, c = cg * 8 + k;
+        float t1 = 0.f, t2 = 0.f;
+        for (int w = 0; w < kEwThreads / 32; ++w) {
+            t1 += sh[0][w][k];
+            t2 += sh[1][w][k];
+        }
+        const float mean = t1 * inv_m;
+        const float var = fmaxf(t2 * inv_m - mean * mean, 0.f);
+        const float invstd = rsqrtf(var + eps);
+        const float sc = gamma[c] * invstd;
+        s_scale[k] = sc;
+        s_shift[k] = beta[c] - mean * sc;
+        save_mean[c] = mean;
+        save_invstd[c] = invstd;
+        if (running_mean != nullptr) {
+            running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+            running_var[c] = (1.f - momentum) * running_var[c] + momentum * var * unbias;
+        }
+        if (cg == 0 && k == 0 && num_batches_tracked != nullptr) *num_batches_tracked += 1;
+    }
+    __syncthreads();
+    float sc[8], sf[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        sc[k] = s_scale[k];
+        sf[k] = s_shift[k];
+    }
+    for (int m = threadIdx.x; m < M; m += kEwThreads) {
+        const long long v = static_cast<long long>(m) * cvec + cg;
+        const float4* p4 = reinterpret_cast<const float4*>(x + v * 8);
+        const float4 a = p4[0], b = p4[1];
+        float f[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+        x_bf16[v] = pack8(f);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) f[k] = fmaf(f[k], sc[k], sf[k]);
+        if (residual != nullptr) {
+            float r[8];
+            unpack8(residual[v], r);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) f[k] += r[k];
+        }
+        if (relu) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) f[k] = fmaxf(f[k], 0.f);
+        }
+        y[v] = pack8(f);
+    }
+}
+
 // ------------------------------------------------------------------------------------ BN bwd
 // Pass 1: g = (dy1 + dy2) * [y > 0];  dbeta[c] += sum g;  dgamma[c] += sum g * xhat.
 // Writes g (bf16) for pass 2 and for the residual branch.
+template <bool DY_F32>
 __global__ void __launch_bounds__(kEwThreads)
-bn_bwd_reduce_kernel(const bf16x8* __restrict__ dy1, const bf16x8* __restrict__ dy2,
+bn_bwd_reduce_kernel(const void* __restrict__ dy1_raw, const bf16x8* __restrict__ dy2,
                      const bf16x8* __restrict__ y, const bf16x8* __restrict__ x,
                      const float* __restrict__ save_mean, const float* __restrict__ save_invstd,
                      bf16x8* __restrict__ g_out, float* __restrict__ dgamma,
@@ -256,7 +349,14 @@ bn_bwd_reduce_kernel(const bf16x8* __restrict__ dy1, const bf16x8* __restrict__ 
     float s1[8] = {0, 0, 0, 0, 0, 0, 0, 0}, s2[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     for (; i < nvec; i += stride) {
         float g[8], xv[8];
-        unpack8(dy1[i], g);
+        if (DY_F32) {
+            const float4* p4 = reinterpret_cast<const float4*>(dy1_raw) + 2 * i;
+            const float4 a = p4[0], b = p4[1];
+            g[0] = a.x; g[1] = a.y; g[2] = a.z; g[3] = a.w;
+            g[4] = b.x; g[5] = b.y; g[6] = b.z; g[7] = b.w;
+        } else {
+            unpack8(reinterpret_cast<const bf16x8*>(dy1_raw)[i], g);
+        }
         if (dy2 != nullptr) {
             float t[8];
             unpack8(dy2[i], t);
@@ -648,11 +748,21 @@ using namespace dpt;
 
 #define DPT_CHECK_LAUNCH() return static_cast<int>(cudaGetLastError())
 
+// debugging knob: DPT_PDL_EW=0 launches the kernels of this file without PDL
+static inline void ew_pdl_gate() {
+    static int on = -1;
+    if (on < 0) {
+        const char* e = std::getenv("DPT_PDL_EW");
+        on = (e == nullptr || e[0] != '0') ? 1 : 0;
+    }
+    if (!on) pdl_skip_flag() = 1;
+}
 static inline bool cvec_ok(int C) { return C % 8 == 0 && (kEwThreads % (C / 8)) == 0; }
 
 extern "C" int dpt_bn_stats(const void* x, float* sum, float* sq, long long M, int C, void* stream) {
     if (!cvec_ok(C)) return DPT_ERR_SHAPE;
     const long long nvec = M * (C / 8);
+    ew_pdl_gate();
     launch_pdl(bn_stats_kernel, dim3(reduce_grid(nvec)), dim3(kEwThreads), 0, static_cast<cudaStream_t>(stream), 
         static_cast<const bf16x8*>(x), sum, sq, nvec, C / 8);
     DPT_CHECK_LAUNCH();
@@ -666,10 +776,33 @@ extern "C" int dpt_bn_fwd_train(const void* x, const float* sum, const float* sq
     if (!cvec_ok(C)) return DPT_ERR_SHAPE;
     const long long nvec = M * (C / 8);
     const float unbias = M > 1 ? static_cast<float>(M) / static_cast<float>(M - 1) : 1.f;
+    ew_pdl_gate();
     launch_pdl(bn_fwd_kernel, dim3(ew_grid(nvec, C / 8)), dim3(kEwThreads), 0, static_cast<cudaStream_t>(stream), 
         static_cast<const bf16x8*>(x), sum, sq, gamma, beta, static_cast<const bf16x8*>(residual),
         static_cast<bf16x8*>(y), save_mean, save_invstd, running_mean, running_var,
         num_batches_tracked, nvec, C / 8, 1.f / static_cast<float>(M), unbias, momentum, eps, relu);
+    DPT_CHECK_LAUNCH();
+}
+
+extern "C" int dpt_bn_fwd_train_small_f32(const float* x, const float* gamma, const float* beta,
+                                          const void* residual, void* y, void* x_bf16,
+                                          float* save_mean, float* save_invstd,
+                                          float* running_mean, float* running_var,
+                                          long long* num_batches_tracked, long long M, int C,
+                                          float momentum, float eps, int relu, void* stream) {
+    if (C % 8 != 0 || M <= 0 || M > (1 << 24)) return DPT_ERR_SHAPE;
+    const float unbias = M > 1 ? static_cast<float>(M) / static_cast<float>(M - 1) : 1.f;
+    ew_pdl_gate();
+    // Measured on B200: launched with the programmatic attribute right behind a split-K conv,
+    // this kernel observed the accumulator before the conv's reductions had landed (CUDA-graph
+    // replay only).  Consumers of RED-accumulated fp32 data are therefore ordinary launches.
+    pdl_skip_flag() = 1;
+    launch_pdl(bn_fwd_small_f32_kernel, dim3(C / 8), dim3(kEwThreads), 0,
+               static_cast<cudaStream_t>(stream), x, gamma, beta,
+               static_cast<const bf16x8*>(residual), static_cast<bf16x8*>(y),
+               static_cast<bf16x8*>(x_bf16), save_mean, save_invstd, running_mean, running_var,
+               num_batches_tracked, static_cast<int>(M), C / 8, 1.f / static_cast<float>(M), unbias,
+               momentum, eps, relu);
     DPT_CHECK_LAUNCH();
 }
 
@@ -679,19 +812,38 @@ extern "C" int dpt_bn_fwd_eval(const void* x, const float* gamma, const float* b
                                int relu, void* stream) {
     if (!cvec_ok(C)) return DPT_ERR_SHAPE;
     const long long nvec = M * (C / 8);
+    ew_pdl_gate();
     launch_pdl(bn_eval_kernel, dim3(ew_grid(nvec, C / 8)), dim3(kEwThreads), 0, static_cast<cudaStream_t>(stream), 
         static_cast<const bf16x8*>(x), gamma, beta, running_mean, running_var,
         static_cast<const bf16x8*>(residual), static_cast<bf16x8*>(y), nvec, C / 8, eps, relu);
     DPT_CHECK_LAUNCH();
 }
 
+extern "C" int dpt_bn_bwd_reduce_ex(const void* dy1, int dy1_is_f32, const void* dy2, const void* y,
+                                    const void* x, const float* save_mean,
+                                    const float* save_invstd, void* g_out, float* dgamma,
+                                    float* dbeta, long long M, int C, void* stream);
+
 extern "C" int dpt_bn_bwd_reduce(const void* dy1, const void* dy2, const void* y, const void* x,
                                  const float* save_mean, const float* save_invstd, void* g_out,
                                  float* dgamma, float* dbeta, long long M, int C, void* stream) {
+    return dpt_bn_bwd_reduce_ex(dy1, 0, dy2, y, x, save_mean, save_invstd, g_out, dgamma, dbeta, M,
+                                C, stream);
+}
+
+// dy1 may be fp32 (output of a split-K dgrad); g_out is then mandatory (pass 2 reads bf16 g).
+extern "C" int dpt_bn_bwd_reduce_ex(const void* dy1, int dy1_is_f32, const void* dy2, const void* y,
+                                    const void* x, const float* save_mean,
+                                    const float* save_invstd, void* g_out, float* dgamma,
+                                    float* dbeta, long long M, int C, void* stream) {
     if (!cvec_ok(C)) return DPT_ERR_SHAPE;
+    if (dy1_is_f32 && g_out == nullptr) return DPT_ERR_ARG;
     const long long nvec = M * (C / 8);
-    launch_pdl(bn_bwd_reduce_kernel, dim3(reduce_grid(nvec)), dim3(kEwThreads), 0, static_cast<cudaStream_t>(stream), 
-        static_cast<const bf16x8*>(dy1), static_cast<const bf16x8*>(dy2),
+    auto kern = dy1_is_f32 ? bn_bwd_reduce_kernel<true> : bn_bwd_reduce_kernel<false>;
+    ew_pdl_gate();
+    if (dy1_is_f32) pdl_skip_flag() = 1;  // dy1 was accumulated with REDs by a split-K dgrad
+    launch_pdl(kern, dim3(reduce_grid(nvec)), dim3(kEwThreads), 0, static_cast<cudaStream_t>(stream), 
+        dy1, static_cast<const bf16x8*>(dy2),
         static_cast<const bf16x8*>(y), static_cast<const bf16x8*>(x), save_mean, save_invstd,
         static_cast<bf16x8*>(g_out), dgamma, dbeta, nvec, C / 8);
     DPT_CHECK_LAUNCH();
@@ -702,6 +854,7 @@ extern "C" int dpt_bn_bwd_apply(const void* g, const void* x, const float* save_
                                 const float* dbeta, void* dx, long long M, int C, void* stream) {
     if (!cvec_ok(C)) return DPT_ERR_SHAPE;
     const long long nvec = M * (C / 8);
+    ew_pdl_gate();
     launch_pdl(bn_bwd_apply_kernel, dim3(ew_grid(nvec, C / 8)), dim3(kEwThreads), 0, static_cast<cudaStream_t>(stream), 
         static_cast<const bf16x8*>(g), static_cast<const bf16x8*>(x), save_mean, save_invstd, gamma,
         dgamma, dbeta, static_cast<bf16x8*>(dx), nvec, C / 8, 1.f / static_cast<float>(M), 1.f);
@@ -713,6 +866,7 @@ extern "C" int dpt_maxpool3x3s2_fwd(const void* x, void* y, void* idx, int N, in
     if (C % 8 != 0) return DPT_ERR_SHAPE;
     const int P = (H + 2 - 3) / 2 + 1, Q = (W + 2 - 3) / 2 + 1;
     const long long total = static_cast<long long>(N) * P * Q * (C / 8);
+    ew_pdl_gate();
     launch_pdl(maxpool_fwd_kernel, dim3(ew_grid(total, 1)), dim3(kEwThreads), 0, static_cast<cudaStream_t>(stream), 
         static_cast<const bf16x8*>(x), static_cast<bf16x8*>(y), static_cast<uint8_t*>(idx), N, H, W,
         C / 8, P, Q);
@@ -724,6 +878,7 @@ extern "C" int dpt_maxpool3x3s2_bwd(const void* dy, const void* dy2, const void*
     if (C % 8 != 0) return DPT_ERR_SHAPE;
     const int P = (H + 2 - 3) / 2 + 1, Q = (W + 2 - 3) / 2 + 1;
     const long long total = static_cast<long long>(N) * H * W * (C / 8);
+    ew_pdl_gate();
     launch_pdl(maxpool_bwd_kernel, dim3(ew_grid(total, 1)), dim3(kEwThreads), 0, static_cast<cudaStream_t>(stream), 
         static_cast<const bf16x8*>(dy), static_cast<const bf16x8*>(dy2),
         static_cast<const uint8_t*>(idx), static_cast<bf16x8*>(dx), N, H, W, C / 8, P, Q);
@@ -732,6 +887,7 @@ extern "C" int dpt_maxpool3x3s2_bwd(const void* dy, const void* dy2, const void*
 
 extern "C" int dpt_head_fwd(const void* x, const float* w, const float* b, float* pooled,
                             float* logits, int B, int HW, int C, int K, void* stream) {
+    ew_pdl_gate();
     launch_pdl(head_fwd_kernel, dim3(B), dim3(256), C * sizeof(float), static_cast<cudaStream_t>(stream), 
         static_cast<const __nv_bfloat16*>(x), w, b, pooled, logits, HW, C, K);
     DPT_CHECK_LAUNCH();
@@ -741,9 +897,11 @@ extern "C" int dpt_head_bwd(const float* dlogits, const float* w, const float* p
                             float* dw, float* db, int B, int HW, int C, int K, void* stream) {
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (dx != nullptr)
-        launch_pdl(head_bwd_dx_kernel, dim3(B), dim3(256), K * sizeof(float), st, 
+        ew_pdl_gate();
+    launch_pdl(head_bwd_dx_kernel, dim3(B), dim3(256), K * sizeof(float), st, 
             dlogits, w, static_cast<__nv_bfloat16*>(dx), HW, C, K);
     dim3 grid((C + 63) / 64, K);
+    ew_pdl_gate();
     launch_pdl(head_bwd_dw_kernel, dim3(grid), dim3(64), 0, st, dlogits, pooled, dw, db, B, C, K, 1.f);
     DPT_CHECK_LAUNCH();
 }
@@ -754,6 +912,7 @@ extern "C" int dpt_cross_entropy(const float* logits, const long long* target, f
     int threads = B * 32;
     if (threads > 1024) threads = 1024;
     if (threads < 32) threads = 32;
+    ew_pdl_gate();
     launch_pdl(ce_fwd_bwd_kernel, dim3(1), dim3(threads), 0, static_cast<cudaStream_t>(stream), 
         logits, target, loss, dlogits, loss_scale, metrics, B, K);
     DPT_CHECK_LAUNCH();
@@ -764,6 +923,7 @@ extern "C" int dpt_im2col_nchw_f32(const float* x, void* out, int N, int C, int 
     const int P = (H + 2 * pad - R) / stride + 1, Q = (W + 2 * pad - S) / stride + 1;
     if (ldk % 8 != 0) return DPT_ERR_SHAPE;
     const long long total = static_cast<long long>(N) * P * Q * (ldk / 8);
+    ew_pdl_gate();
     launch_pdl(im2col_nchw_kernel, dim3(ew_grid(total, 1)), dim3(kEwThreads), 0, static_cast<cudaStream_t>(stream), 
         x, static_cast<__nv_bfloat16*>(out), N, C, H, W, R, S, stride, pad, P, Q, ldk);
     DPT_CHECK_LAUNCH();
@@ -771,6 +931,7 @@ extern "C" int dpt_im2col_nchw_f32(const float* x, void* out, int N, int C, int 
 
 extern "C" int dpt_pad_rows_f32_to_bf16(const float* src, void* dst, int rows, int cols, int ld,
                                         void* stream) {
+    ew_pdl_gate();
     launch_pdl(pad_rows_kernel, dim3(ew_grid(static_cast<long long>(rows) * ld, 1)), dim3(kEwThreads), 0, static_cast<cudaStream_t>(stream), src, static_cast<__nv_bfloat16*>(dst),
                                                            rows, cols, ld);
     DPT_CHECK_LAUNCH();
@@ -779,6 +940,7 @@ extern "C" int dpt_pad_rows_f32_to_bf16(const float* src, void* dst, int rows, i
 extern "C" int dpt_nchw_f32_to_nhwc_bf16(const float* x, void* y, int N, int C, int H, int W,
                                          void* stream) {
     const long long total = static_cast<long long>(N) * C * H * W;
+    ew_pdl_gate();
     launch_pdl(nchw_to_nhwc_kernel, dim3(ew_grid(total, 1)), dim3(kEwThreads), 0, static_cast<cudaStream_t>(stream), 
         x, static_cast<__nv_bfloat16*>(y), N, C, H, W);
     DPT_CHECK_LAUNCH();
@@ -860,9 +1022,11 @@ extern "C" int dpt_bn_fwd_train_noalloc(const void* x, const float* gamma, const
     cudaError_t e = cudaMemsetAsync(scratch, 0, sizeof(float) * 2 * C, st);
     if (e != cudaSuccess) return static_cast<int>(e);
     const long long nvec = M * (C / 8);
+    ew_pdl_gate();
     launch_pdl(bn_stats_kernel, dim3(reduce_grid(nvec)), dim3(kEwThreads), 0, st, static_cast<const bf16x8*>(x), sum,
                                                                  sq, nvec, C / 8);
     const float unbias = M > 1 ? static_cast<float>(M) / static_cast<float>(M - 1) : 1.f;
+    ew_pdl_gate();
     launch_pdl(bn_fwd_kernel, dim3(ew_grid(nvec, C / 8)), dim3(kEwThreads), 0, st, 
         static_cast<const bf16x8*>(x), sum, sq, gamma, beta, static_cast<const bf16x8*>(residual),
         static_cast<bf16x8*>(y), save_mean, save_invstd, running_mean, running_var,

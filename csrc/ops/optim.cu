@@ -229,3 +229,10 @@ extern "C" int dpt_cast_f32_to_bf16(const float* src, void* dst, long long n, vo
         src, static_cast<__nv_bfloat16*>(dst), n);
     return static_cast<int>(cudaGetLastError());
 }
+
+// The next kernel launched through this library follows a cross-stream event wait: launch it
+// without the programmatic-dependent-launch attribute (see csrc/common/ptx.cuh).
+extern "C" int dpt_pdl_skip_next() {
+    dpt::pdl_skip_flag() = 1;
+    return 0;
+}

@@ -81,6 +81,8 @@ class TrainStep:
         self.eng.backward(self.dlogits)
         if ddp is not None:
             ddp.finalize_backward()
+        from .ops import _lib
+        _lib.pdl_skip_next()          # the optimizer kernel follows cross-stream joins
         sc = self.scaler
         if sc is None:
             self.optimizer.step()

@@ -232,15 +232,41 @@ class _EngineFn(torch.autograd.Function):
 class _Unit:
     """conv -> BN (-> +residual) (-> ReLU) with its buffers."""
     __slots__ = ("conv", "bn", "x_shape", "y_shape", "raw", "y", "sum", "sq", "mean", "invstd",
-                 "d_raw", "g", "relu", "name")
+                 "d_raw", "g", "relu", "name", "fsplit", "raw32", "dsplit")
+
+
+def _live_taps(H, W, P, Q, k, stride, pad):
+    """Filter taps that touch at least one real (non-padding) pixel."""
+    n = 0
+    for r in range(k):
+        for s_ in range(k):
+            hmin, hmax = r - pad, (P - 1) * stride + r - pad
+            wmin, wmax = s_ - pad, (Q - 1) * stride + s_ - pad
+            if hmax < 0 or hmin >= H or wmax < 0 or wmin >= W:
+                continue
+            n += 1
+    return n
+
+
+def _pick_splits(tiles: int, ksteps: int, sm_target: int = 120) -> int:
+    """Split the k loop over CTAs when the tile grid alone would leave most SMs idle: a single
+    CTA can only pull ~50 GB/s of operands through TMA, so small-M layers are spread out."""
+    import os
+    if tiles > 32 or ksteps < 4 or os.environ.get("DPT_NO_SPLITK", "0") == "1":
+        return 1
+    s = min(ksteps, max(1, sm_target // tiles))
+    per = -(-ksteps // s)
+    return max(1, -(-ksteps // per))
 
 
 class ResNetEngine:
     STEM_LDK = 152  # 7*7*3 = 147 padded so that rows are 16-byte aligned for TMA
 
     def __init__(self, model: ResNet, in_shape, training: bool) -> None:
+        from ..ops import _lib
         from ..ops import functional as Fn
         self.Fn = Fn
+        self._lib = _lib
         self.m = model
         self.training = training
         self.dev = model.fc.weight.device
@@ -251,6 +277,8 @@ class ResNetEngine:
         bf = dict(device=self.dev, dtype=torch.bfloat16)
         f32 = dict(device=self.dev, dtype=torch.float32)
         self.units: list[_Unit] = []
+        self._zero32_plan: list = []
+        self._zero32_n = 0
         bns = [mod for mod in model.modules() if isinstance(mod, BatchNorm2d)]
         total_c = sum(b.num_features for b in bns)
         # one arena for all batch statistics so a single memset clears them every step
@@ -281,11 +309,27 @@ class ResNetEngine:
         self.logits = torch.empty((N, K), **f32)
         self.d_feat = torch.empty(shape, **bf) if training else None
         self._last_input = None
+        # materialise the fp32 split-K accumulators
+        self.zero32 = torch.zeros(max(self._zero32_n, 1), **f32) if training else None
+
+        def z32(handle):
+            off, n, shp = self._zero32_plan[handle]
+            return self.zero32[off:off + n].view(shp)
+        if training:
+            for u in self.units:
+                if u.raw32 is not None:
+                    u.raw32 = z32(u.raw32)
+            for b in self.blocks:
+                if isinstance(b.get("dx"), int):
+                    b["dx"] = z32(b["dx"])
+                b["d_mid"] = [z32(t) if isinstance(t, int) else t for t in b.get("d_mid", [])]
         # weight-gradient kernels are off the critical path (nothing in backward consumes
         # them): they run on a second stream, concurrently with the dgrad / BN-backward chain
         self.side = torch.cuda.Stream(device=self.dev) if training else None
         self._ev_pool = [torch.cuda.Event() for _ in range(64)] if training else []
         self._ev_i = 0
+        self._z32_ev = torch.cuda.Event() if training else None
+        self._z32_pending = False
 
     # ------------------------------------------------------------------ planning
     def _unit(self, name, conv, bn, x_shape, y_shape, relu) -> _Unit:
@@ -301,8 +345,35 @@ class ResNetEngine:
         self._stat_off += 2 * C
         u.d_raw = torch.empty(y_shape, **bf) if self.training else None
         u.g = torch.empty(y_shape, **bf) if self.training else None
+        u.fsplit, u.raw32, u.dsplit = 1, None, 1
+        if self.training and conv.in_channels % 8 == 0:
+            N, H, W, Cin = x_shape
+            _, P, Q, Cout = y_shape
+            k, st, pd = conv.kernel_size, conv.stride, conv.padding
+            bn_ = 128 if Cout >= 128 else 64
+            tiles = -(-(N * P * Q) // 128) * -(-Cout // bn_)
+            ksteps = _live_taps(H, W, P, Q, k, st, pd) * -(-Cin // 64)
+            u.fsplit = _pick_splits(tiles, ksteps)
+            if u.fsplit > 1:
+                u.raw32 = self._zero32_alloc(y_shape)
+            # dgrad: rows are input pixels of one stride-parity class, k runs over (taps, Cout)
+            bn_d = 128 if Cin >= 128 else 64
+            rows = N * -(-H // st) * -(-W // st)
+            dtiles = -(-rows // 128) * -(-Cin // bn_d) * (st * st)
+            dk = max(1, _live_taps(H, W, P, Q, k, st, pd) // (st * st)) * -(-Cout // 64)
+            u.dsplit = _pick_splits(dtiles, dk)
         self.units.append(u)
         return u
+
+    def _zero32_alloc(self, shape):
+        """fp32 scratch that must be zero at the start of every step (split-K accumulators):
+        carved from one flat buffer so a single memset clears all of it."""
+        n = 1
+        for d in shape:
+            n *= d
+        self._zero32_plan.append((self._zero32_n, n, tuple(shape)))
+        self._zero32_n += (n + 63) // 64 * 64
+        return len(self._zero32_plan) - 1
 
     def _conv_unit(self, name, conv, bn, x_shape, relu) -> _Unit:
         N, H, W, _ = x_shape
@@ -328,10 +399,24 @@ class ResNetEngine:
             b["ds"] = self._conv_unit(f"{name}.downsample", blk.downsample[0], blk.downsample[1],
                                       x_shape, False)
         if self.training:
-            b["dx"] = torch.empty(x_shape, **bf)               # grad wrt block input (main path)
-            fused = self._can_fuse_dgrad(b["units"][0], b["ds"])
+            u1 = b["units"][0]
+            first_block = len(self.blocks) == 0     # its dx feeds max-pool backward (bf16 only)
+            if u1.dsplit > 1 and not first_block:
+                b["dx"] = self._zero32_alloc(x_shape)           # fp32 split-K accumulator
+            else:
+                u1.dsplit = 1
+                b["dx"] = torch.empty(x_shape, **bf)           # grad wrt block input (main path)
+            fused = self._can_fuse_dgrad(u1, b["ds"])
             b["dx_ds"] = torch.empty(x_shape, **bf) if (b["ds"] is not None and not fused) else None
-            b["d_mid"] = [torch.empty(u.y_shape, **bf) for u in b["units"][:-1]]
+            if b["ds"] is not None:
+                b["ds"].dsplit = 1
+            b["d_mid"] = []
+            for i, u in enumerate(b["units"][:-1]):
+                nxt = b["units"][i + 1]                         # its dgrad produces grad wrt u.y
+                if nxt.dsplit > 1:
+                    b["d_mid"].append(self._zero32_alloc(u.y_shape))
+                else:
+                    b["d_mid"].append(torch.empty(u.y_shape, **bf))
         self.blocks.append(b)
         return last.y_shape
 
@@ -369,7 +454,16 @@ class ResNetEngine:
     def _fwd_unit(self, u: _Unit, x, residual=None):
         Fn = self.Fn
         conv, bn = u.conv, u.bn
-        if self.training:
+        if self.training and u.fsplit > 1:
+            # tiny tile grid: split-K over CTAs into an fp32 accumulator, then one column-strip
+            # kernel does statistics + normalisation (+residual, +ReLU)
+            Fn.conv_fprop(x, self._w(conv), conv.stride, conv.padding, out=u.raw32, splits=u.fsplit)
+            Fn.bn_fwd_train_small_f32(u.raw32, bn.weight, bn.bias, residual=residual, relu=u.relu,
+                                      out=u.y, x_bf16=u.raw, save_mean=u.mean, save_invstd=u.invstd,
+                                      running_mean=bn.running_mean, running_var=bn.running_var,
+                                      num_batches_tracked=bn.num_batches_tracked,
+                                      momentum=bn.momentum, eps=bn.eps)
+        elif self.training:
             Fn.conv_fprop(x, self._w(conv), conv.stride, conv.padding, out=u.raw,
                           stats=(u.sum, u.sq))
             Fn.bn_fwd_train(u.raw, u.sum, u.sq, bn.weight, bn.bias, residual=residual, relu=u.relu,
@@ -392,6 +486,11 @@ class ResNetEngine:
         self._last_input = x_nchw
         if self.training:
             self.stats.zero_()
+            if self._zero32_n:
+                with self._fork_side():      # off the critical path: first used in layer2
+                    self.zero32.zero_()
+                self._z32_ev.record(self.side)
+                self._z32_pending = True
         # ---- stem: im2col + GEMM (+BN statistics in the epilogue) ----------------------
         st = self.stem
         N, P, Q, _ = st.y_shape
@@ -417,6 +516,10 @@ class ResNetEngine:
         # ---- residual stages ------------------------------------------------------------
         for b in self.blocks:
             b["x"] = x
+            if self.training and self._z32_pending and any(u.fsplit > 1 for u in b["units"] + ([b["ds"]] if b["ds"] else [])):
+                torch.cuda.current_stream().wait_event(self._z32_ev)
+                self._lib.pdl_skip_next()
+                self._z32_pending = False
             idn = x if b["ds"] is None else self._fwd_unit(b["ds"], x)
             h = x
             for u in b["units"][:-1]:
@@ -448,6 +551,7 @@ class ResNetEngine:
         self._ev_i += 1
         ev.record(torch.cuda.current_stream())
         self.side.wait_event(ev)
+        self._lib.pdl_skip_next()     # first kernel on the side stream follows an event wait
         return torch.cuda.stream(self.side)
 
     def _wgrad(self, u: _Unit, x_in):
@@ -460,11 +564,14 @@ class ResNetEngine:
 
     def _dgrad(self, u: _Unit, x_shape, out, u2: Optional[_Unit] = None):
         conv = u.conv
+        splits = u.dsplit if out.dtype == torch.float32 else 1
         if u2 is None:
-            self.Fn.conv_dgrad(u.d_raw, self._w(conv), x_shape, conv.stride, conv.padding, out=out)
+            self.Fn.conv_dgrad(u.d_raw, self._w(conv), x_shape, conv.stride, conv.padding, out=out,
+                               splits=splits)
         else:
             self.Fn.conv_dgrad(u.d_raw, self._w(conv), x_shape, conv.stride, conv.padding, out=out,
-                               dy2=u2.d_raw, w2=self._w(u2.conv), pad2=u2.conv.padding)
+                               dy2=u2.d_raw, w2=self._w(u2.conv), pad2=u2.conv.padding,
+                               splits=splits)
         return out
 
     @staticmethod
@@ -507,6 +614,10 @@ class ResNetEngine:
         Fn = self.Fn
         m = self.m
         dlogits = dlogits.contiguous()
+        if self._z32_pending:
+            torch.cuda.current_stream().wait_event(self._z32_ev)
+            self._lib.pdl_skip_next()
+            self._z32_pending = False
         Fn.head_bwd(dlogits, m.fc.weight, self.pooled, self.feat_shape, self._gw(m.fc.weight),
                     self._gw(m.fc.bias), dx=self.d_feat)
         with self._fork_side():
@@ -525,3 +636,4 @@ class ResNetEngine:
                     147, out_mode=2, splits=max(1, min(64, M // 512)))
             self._ready(m.conv1.weight, m.bn1.weight, m.bn1.bias)
         torch.cuda.current_stream().wait_stream(self.side)   # join
+        self._lib.pdl_skip_next()

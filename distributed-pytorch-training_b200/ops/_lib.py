@@ -24,6 +24,10 @@ vp, i32, i64, f32, f64 = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_doubl
 _SIGS = {
     "dpt_conv_fprop": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp, vp, i32, i32, vp],
     "dpt_conv_dgrad": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp, vp, i32, i32, i32, vp],
+    "dpt_conv_dgrad_ex": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp, vp, i32, i32, i32,
+                          i32, i32, vp],
+    "dpt_bn_fwd_train_small_f32": [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, f32, f32, i32, vp],
+    "dpt_bn_bwd_reduce_ex": [vp, i32, vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, vp],
     "dpt_conv_wgrad": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp],
     "dpt_gemm_bf16": [i32, vp, vp, vp, i32, i32, i32, i64, i64, i64, i32, vp, vp, vp, i32, vp],
     "dpt_bn_stats": [vp, vp, vp, i64, i32, vp],
@@ -44,6 +48,7 @@ _SIGS = {
     "dpt_sgd_flat": [vp, vp, vp, vp, i64, f32, f32, f32, f32, i32, vp, vp, vp],
     "dpt_adam_flat": [vp, vp, vp, vp, vp, i64, f32, f32, f32, f32, f32, i32, vp, vp, vp, vp],
     "dpt_cast_f32_to_bf16": [vp, vp, i64, vp],
+    "dpt_pdl_skip_next": [],
     "dpt_symm_alloc": [C.c_size_t, C.POINTER(vp), vp],
     "dpt_symm_open": [vp, C.POINTER(vp)],
     "dpt_symm_close": [vp],
@@ -102,6 +107,11 @@ def check(code: int, what: str) -> None:
 
 def call(name: str, *args) -> None:
     check(getattr(lib(), name)(*args), name)
+
+
+def pdl_skip_next() -> None:
+    """Call after a cross-stream event wait: the next kernel launch is fully ordered."""
+    lib().dpt_pdl_skip_next()
 
 
 LAUNCHES = 0  # kernels launched through this binding (bench.py reports it)

@@ -37,15 +37,18 @@ def conv_fprop(x, w, stride=1, pad=0, *, out=None, stats=None, splits=1):
     return out
 
 
-def conv_dgrad(dy, w, x_shape, stride=1, pad=0, *, out=None, dy2=None, w2=None, pad2=0):
-    """dx = conv_backward_data(dy, w) [+ conv_backward_data(dy2, w2)] for convs sharing x."""
+def conv_dgrad(dy, w, x_shape, stride=1, pad=0, *, out=None, dy2=None, w2=None, pad2=0, splits=1):
+    """dx = conv_backward_data(dy, w) [+ conv_backward_data(dy2, w2)] for convs sharing x.
+    ``splits > 1``: ``out`` is a pre-zeroed fp32 tensor accumulated with split-K atomics."""
     N, H, W, Cin = x_shape
     Cout, R, S, _ = w.shape
+    atomic = splits > 1
     if out is None:
-        out = torch.empty((N, H, W, Cin), device=dy.device, dtype=BF16)
+        out = (torch.zeros if atomic else torch.empty)(
+            (N, H, W, Cin), device=dy.device, dtype=torch.float32 if atomic else BF16)
     R2, S2 = (w2.shape[1], w2.shape[2]) if w2 is not None else (0, 0)
-    call("dpt_conv_dgrad", ptr(dy), ptr(w), ptr(out), N, H, W, Cin, Cout, R, S, stride, pad,
-         ptr(dy2), ptr(w2), R2, S2, pad2, stream())
+    call("dpt_conv_dgrad_ex", ptr(dy), ptr(w), ptr(out), N, H, W, Cin, Cout, R, S, stride, pad,
+         ptr(dy2), ptr(w2), R2, S2, pad2, int(atomic), splits, stream())
     count()
     return out
 
@@ -94,6 +97,19 @@ def bn_fwd_train(x, sum_, sq, gamma, beta, *, residual=None, relu=False, out=Non
     return out, save_mean, save_invstd
 
 
+def bn_fwd_train_small_f32(x32, gamma, beta, *, residual=None, relu=False, out, x_bf16, save_mean,
+                           save_invstd, running_mean=None, running_var=None,
+                           num_batches_tracked=None, momentum=0.1, eps=1e-5):
+    """Statistics + normalisation in one launch for a small fp32 tensor (split-K conv output)."""
+    C_ = x32.shape[-1]
+    M = x32.numel() // C_
+    call("dpt_bn_fwd_train_small_f32", ptr(x32), ptr(gamma), ptr(beta), ptr(residual), ptr(out),
+         ptr(x_bf16), ptr(save_mean), ptr(save_invstd), ptr(running_mean), ptr(running_var),
+         ptr(num_batches_tracked), M, C_, momentum, eps, int(relu), stream())
+    count()
+    return out
+
+
 def bn_fwd_eval(x, gamma, beta, running_mean, running_var, *, residual=None, relu=False, out=None,
                 eps=1e-5):
     C_ = x.shape[-1]
@@ -115,8 +131,12 @@ def bn_bwd(dy, x, save_mean, save_invstd, gamma, dgamma, dbeta, *, dy2=None, y=N
     need_g = (dy2 is not None) or (y is not None)
     if need_g and g_out is None:
         g_out = torch.empty_like(x)
-    call("dpt_bn_bwd_reduce", ptr(dy), ptr(dy2), ptr(y), ptr(x), ptr(save_mean), ptr(save_invstd),
-         ptr(g_out), ptr(dgamma), ptr(dbeta), M, C_, stream())
+    f32 = dy.dtype == torch.float32
+    need_g = need_g or f32
+    if need_g and g_out is None:
+        g_out = torch.empty_like(x)
+    call("dpt_bn_bwd_reduce_ex", ptr(dy), int(f32), ptr(dy2), ptr(y), ptr(x), ptr(save_mean),
+         ptr(save_invstd), ptr(g_out), ptr(dgamma), ptr(dbeta), M, C_, stream())
     g = g_out if need_g else dy
     if dx is None:
         dx = torch.empty_like(x)

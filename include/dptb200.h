@@ -32,6 +32,10 @@ int dpt_conv_fprop(const void* x, const void* w, void* y, int N, int H, int W, i
 int dpt_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout,
                    int R, int S, int stride, int pad, const void* dy2, const void* w2, int R2,
                    int S2, int pad2, void* stream);
+/* split-K variant: out_f32_atomic = 1 accumulates into a pre-zeroed fp32 dx with `splits` CTAs per tile */
+int dpt_conv_dgrad_ex(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin,
+                      int Cout, int R, int S, int stride, int pad, const void* dy2, const void* w2,
+                      int R2, int S2, int pad2, int out_f32_atomic, int splits, void* stream);
 int dpt_conv_wgrad(const void* dy, const void* x, float* dw, int N, int H, int W, int Cin, int Cout,
                    int R, int S, int stride, int pad, int splits, void* stream);
 /* op: 0 = A[M,K]*B[N,K]^T, 1 = A[M,K]*B[K,N], 2 = A[K,M]^T*B[K,N]; out_mode 0 bf16, 1 fp32,
@@ -52,12 +56,21 @@ int dpt_bn_fwd_train(const void* x, const float* sum, const float* sq, const flo
                      float* save_invstd, float* running_mean, float* running_var,
                      long long* num_batches_tracked, long long M, int C, float momentum, float eps,
                      int relu, void* stream);
+/* single-launch statistics + normalisation for small tensors produced by a split-K conv (fp32 x) */
+int dpt_bn_fwd_train_small_f32(const float* x, const float* gamma, const float* beta,
+                               const void* residual, void* y, void* x_bf16, float* save_mean,
+                               float* save_invstd, float* running_mean, float* running_var,
+                               long long* num_batches_tracked, long long M, int C, float momentum,
+                               float eps, int relu, void* stream);
 int dpt_bn_fwd_eval(const void* x, const float* gamma, const float* beta, const float* running_mean,
                     const float* running_var, const void* residual, void* y, long long M, int C,
                     float eps, int relu, void* stream);
 int dpt_bn_bwd_reduce(const void* dy1, const void* dy2, const void* y, const void* x,
                       const float* save_mean, const float* save_invstd, void* g_out, float* dgamma,
                       float* dbeta, long long M, int C, void* stream);
+int dpt_bn_bwd_reduce_ex(const void* dy1, int dy1_is_f32, const void* dy2, const void* y,
+                         const void* x, const float* save_mean, const float* save_invstd,
+                         void* g_out, float* dgamma, float* dbeta, long long M, int C, void* stream);
 int dpt_bn_bwd_apply(const void* g, const void* x, const float* save_mean, const float* save_invstd,
                      const float* gamma, const float* dgamma, const float* dbeta, void* dx,
                      long long M, int C, void* stream);
@@ -106,6 +119,10 @@ int dpt_adam_flat(float* p, const float* g, float* m, float* v, void* shadow_bf1
                   float lr, float beta1, float beta2, float eps, float wd, int decoupled,
                   int* step_count, const float* grad_scale, const float* found_inf, void* stream);
 int dpt_cast_f32_to_bf16(const float* src, void* dst, long long n, void* stream);
+/* Kernels here are launched with programmatic dependent launch (they overlap their prologue with
+ * the previous kernel of the same stream).  Call this right after making a stream wait on another
+ * stream's event: the next launch is then an ordinary, fully ordered one. */
+int dpt_pdl_skip_next(void);
 
 /* ---- NVLink peer-memory collectives (csrc/comm/p2p_collectives.cu) ---------------------------
  * Stand in for ProcessGroupNCCL allreduce / broadcast / barrier as driven by torch DDP on the

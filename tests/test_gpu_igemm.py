@@ -140,3 +140,18 @@ def test_gemm_ops(mnk):
     Fn.gemm(2, A2, B1, C2, M, N, K, ld(M), ld(N), N, out_mode=2, splits=3)
     torch.cuda.synchronize()
     _close(C2, A2[:, :M].float().t() @ B1[:, :N].float(), 2e-3, "gemm TN split")
+
+
+@pytest.mark.parametrize("case", CONV_CASES[:6])
+def test_conv_dgrad_splitk(case):
+    Fn = _F()
+    N, H, W, Cin, Cout, k, s, p = case
+    P, Q = Fn.conv_out_hw(H, W, k, k, s, p)
+    dy = _mk((N, P, Q, Cout), 1.0, 21)
+    w = _mk((Cout, k, k, Cin), 0.05, 22)
+    dx = Fn.conv_dgrad(dy, w, (N, H, W, Cin), s, p, splits=3)
+    torch.cuda.synchronize()
+    assert dx.dtype == torch.float32
+    ref = torch.nn.grad.conv2d_input((N, Cin, H, W), w.float().permute(0, 3, 1, 2),
+                                     dy.float().permute(0, 3, 1, 2), stride=s, padding=p)
+    _close(dx.permute(0, 3, 1, 2), ref, 2e-3, "dgrad split-k")

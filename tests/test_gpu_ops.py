@@ -254,3 +254,46 @@ def test_amp_scale_state_machine():
     torch.cuda.synchronize()
     assert found.item() == 1.0
     assert abs(g[0].item() - 4.0 / 65536.0) < 1e-9
+
+
+@pytest.mark.parametrize("shape", [(128, 4, 4, 128), (128, 1, 1, 512), (16, 2, 2, 256)])
+@pytest.mark.parametrize("relu,res", [(True, False), (True, True), (False, False)])
+def test_bn_small_f32_fused_and_f32_dy_backward(shape, relu, res):
+    """Split-K path: fp32 conv accumulator -> single-launch BN; fp32 incoming gradient."""
+    Fn = _F()
+    N, H, W, C = shape
+    x32 = torch.randn(shape, device="cuda") * 2 + 0.3
+    gamma = torch.rand(C, device="cuda") + 0.5
+    beta = torch.randn(C, device="cuda")
+    residual = _rand(shape, 4) if res else None
+    rm, rv = torch.zeros(C, device="cuda"), torch.ones(C, device="cuda")
+    nbt = torch.zeros((), device="cuda", dtype=torch.int64)
+    y = torch.empty(shape, device="cuda", dtype=torch.bfloat16)
+    xb = torch.empty(shape, device="cuda", dtype=torch.bfloat16)
+    mean, invstd = torch.empty(C, device="cuda"), torch.empty(C, device="cuda")
+    Fn.bn_fwd_train_small_f32(x32, gamma, beta, residual=residual, relu=relu, out=y, x_bf16=xb,
+                              save_mean=mean, save_invstd=invstd, running_mean=rm, running_var=rv,
+                              num_batches_tracked=nbt)
+    xr = x32.permute(0, 3, 1, 2).clone().requires_grad_(True)
+    gr = gamma.clone().requires_grad_(True)
+    br = beta.clone().requires_grad_(True)
+    rm_r, rv_r = torch.zeros(C, device="cuda"), torch.ones(C, device="cuda")
+    yr = F.batch_norm(xr, rm_r, rv_r, gr, br, training=True, momentum=0.1, eps=1e-5)
+    if res:
+        yr = yr + residual.float().permute(0, 3, 1, 2)
+    if relu:
+        yr = F.relu(yr)
+    torch.cuda.synchronize()
+    _close(y.permute(0, 3, 1, 2), yr, 1.5e-2, "y")
+    _close(xb, x32, 1e-2, "bf16 copy of x")
+    _close(rm, rm_r, 1e-3, "running_mean")
+    _close(rv, rv_r, 1e-3, "running_var")
+    assert int(nbt) == 1
+    dy32 = torch.randn(shape, device="cuda")
+    dgamma, dbeta = torch.zeros(C, device="cuda"), torch.zeros(C, device="cuda")
+    dx, g = Fn.bn_bwd(dy32, xb, mean, invstd, gamma, dgamma, dbeta, y=y if relu else None)
+    yr.backward(dy32.permute(0, 3, 1, 2))
+    torch.cuda.synchronize()
+    _close(dx.permute(0, 3, 1, 2), xr.grad, 4e-2, "dx")
+    _close(dgamma, gr.grad, 3e-2, "dgamma")
+    _close(dbeta, br.grad, 2e-2, "dbeta")
