@@ -41,9 +41,12 @@ def parse():
     p.add_argument("--l2-flush", action="store_true",
                    help="flush L2 (untimed 256 MiB memset) between timed steps; default is no flush "
                         "because one step touches ~207 MB > 126 MB L2")
-    p.add_argument("--fused-optimizer", action="store_true")
+    p.add_argument("--fused-optimizer", action="store_true", default=None,
+                   help="apply SGD inside the all-reduce kernel (default: on when N > 1)")
+    p.add_argument("--no-fused-optimizer", dest="fused_optimizer", action="store_false")
     p.add_argument("--bucket-cap-mb", type=float, default=None)
-    p.add_argument("--comm-ctas", type=int, default=0)
+    p.add_argument("--comm-ctas", type=int, default=16,
+                   help="CTAs of each bucket all-reduce kernel (fewer = less SM contention with backward)")
     p.add_argument("--eager-buffer-sync", action="store_true",
                    help="broadcast BN buffers from rank 0 every step (torch DDP behaviour) instead "
                         "of lazily before eval/checkpoint")
@@ -157,8 +160,10 @@ def run_ours(a):
         model = ddp = DistributedDataParallel(model, device_ids=[local], backend="native",
                                               bucket_cap_mb=a.bucket_cap_mb, comm_ctas=a.comm_ctas)
     opt = SGD(model.parameters(), lr=0.1, momentum=0.9, weight_decay=5e-4)
+    if a.fused_optimizer is None:
+        a.fused_optimizer = world > 1
     if ddp is not None and a.fused_optimizer:
-        ddp.enable_fused_sgd(opt)
+        a.fused_optimizer = bool(ddp.enable_fused_sgd(opt))
     scaler = GradScaler(device=device, enabled=False)  # bf16: no loss scaling needed
     shape = (a.batch_size, 3, a.image_size, a.image_size)
     step = TrainStep(model, opt, scaler, batch_shape=shape, cuda_graph=not a.no_graph,
@@ -240,7 +245,9 @@ def run_ours(a):
                    "l2": "flushed between timed steps (untimed 256 MiB memset)" if flush is not None
                          else "not flushed: one step touches ~207 MB (fp32 params+grads+momentum, bf16 shadow, "
                               "activations) > 126 MB L2",
-                   "grad_allreduce": "native NVLink peer-memory two-shot, fused 1/world epilogue" if world > 1 else "none (1 GPU)",
+                   "grad_allreduce": (f"native NVLink peer-memory two-shot, {a.comm_ctas} CTAs/bucket, fused "
+                                      "1/world" + (" + SGD update" if a.fused_optimizer else "") + " epilogue")
+                                     if world > 1 else "none (1 GPU)",
                    "fused_optimizer": bool(a.fused_optimizer and world > 1),
                    "grad_buckets_bytes": ddp.bucket_sizes() if ddp is not None else [],
                    "bn_buffer_sync": "lazy (before eval/checkpoint)" if not a.eager_buffer_sync else "every step"},

@@ -248,14 +248,31 @@ bn_fwd_small_f32_kernel(const float* __restrict__ x, const float* __restrict__ g
     const int cg = blockIdx.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     float s1[8] = {0, 0, 0, 0, 0, 0, 0, 0}, s2[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    for (int m = threadIdx.x; m < M; m += kEwThreads) {
-        const float4* p4 = reinterpret_cast<const float4*>(x + (static_cast<long long>(m) * cvec + cg) * 8);
-        const float4 a = p4[0], b = p4[1];
-        const float f[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+    // rows are independent: issue 4 rows' loads before consuming them (latency, not bandwidth,
+    // bounds this kernel)
+    constexpr int kRows = 4;
+    for (int m0 = threadIdx.x; m0 < M; m0 += kEwThreads * kRows) {
+        float4 a[kRows], b[kRows];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            s1[k] += f[k];
-            s2[k] += f[k] * f[k];
+        for (int j = 0; j < kRows; ++j) {
+            const int m = m0 + j * kEwThreads;
+            if (m < M) {
+                const float4* p4 = reinterpret_cast<const float4*>(
+                    x + (static_cast<long long>(m) * cvec + cg) * 8);
+                a[j] = p4[0];
+                b[j] = p4[1];
+            } else {
+                a[j] = b[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < kRows; ++j) {
+            const float f[8] = {a[j].x, a[j].y, a[j].z, a[j].w, b[j].x, b[j].y, b[j].z, b[j].w};
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                s1[k] += f[k];
+                s2[k] += f[k] * f[k];
+            }
         }
     }
 #pragma unroll
@@ -302,25 +319,41 @@ bn_fwd_small_f32_kernel(const float* __restrict__ x, const float* __restrict__ g
         sc[k] = s_scale[k];
         sf[k] = s_shift[k];
     }
-    for (int m = threadIdx.x; m < M; m += kEwThreads) {
-        const long long v = static_cast<long long>(m) * cvec + cg;
-        const float4* p4 = reinterpret_cast<const float4*>(x + v * 8);
-        const float4 a = p4[0], b = p4[1];
-        float f[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
-        x_bf16[v] = pack8(f);
+    for (int m0 = threadIdx.x; m0 < M; m0 += kEwThreads * kRows) {
+        float4 a[kRows], b[kRows];
+        bf16x8 rres[kRows];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) f[k] = fmaf(f[k], sc[k], sf[k]);
-        if (residual != nullptr) {
-            float r[8];
-            unpack8(residual[v], r);
-#pragma unroll
-            for (int k = 0; k < 8; ++k) f[k] += r[k];
+        for (int j = 0; j < kRows; ++j) {
+            const int m = m0 + j * kEwThreads;
+            if (m < M) {
+                const long long v = static_cast<long long>(m) * cvec + cg;
+                const float4* p4 = reinterpret_cast<const float4*>(x + v * 8);
+                a[j] = p4[0];
+                b[j] = p4[1];
+                if (residual != nullptr) rres[j] = residual[v];
+            }
         }
-        if (relu) {
 #pragma unroll
-            for (int k = 0; k < 8; ++k) f[k] = fmaxf(f[k], 0.f);
+        for (int j = 0; j < kRows; ++j) {
+            const int m = m0 + j * kEwThreads;
+            if (m >= M) continue;
+            const long long v = static_cast<long long>(m) * cvec + cg;
+            float f[8] = {a[j].x, a[j].y, a[j].z, a[j].w, b[j].x, b[j].y, b[j].z, b[j].w};
+            x_bf16[v] = pack8(f);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) f[k] = fmaf(f[k], sc[k], sf[k]);
+            if (residual != nullptr) {
+                float r[8];
+                unpack8(rres[j], r);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) f[k] += r[k];
+            }
+            if (relu) {
+#pragma unroll
+                for (int k = 0; k < 8; ++k) f[k] = fmaxf(f[k], 0.f);
+            }
+            y[v] = pack8(f);
         }
-        y[v] = pack8(f);
     }
 }
 
@@ -413,6 +446,109 @@ bn_bwd_apply_kernel(const bf16x8* __restrict__ g, const bf16x8* __restrict__ x,
     for (; i < nvec; i += stride) {
         float gv[8], xv[8], o[8];
         unpack8(g[i], gv);
+        unpack8(x[i], xv);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const float xh = (xv[k] - mean[k]) * istd[k];
+            o[k] = a[k] * (gv[k] - b[k] - xh * c2[k]);
+        }
+        dx[i] = pack8(o);
+    }
+}
+
+// Single-launch BatchNorm backward: pass 1 (masked-gradient sums) and pass 2 (dx) in one kernel
+// separated by a grid-wide barrier.  The grid is at most one CTA per SM, so every CTA is
+// resident and the spin barrier cannot deadlock.  `scratch` = 2*C floats + `counter` must be zero
+// on entry (the engine clears them with the per-step statistics memset); the per-channel sums
+// are added into dgamma / dbeta (gradient accumulation semantics) by CTA 0.
+template <bool DY_F32>
+__global__ void __launch_bounds__(kEwThreads)
+bn_bwd_fused_kernel(const void* __restrict__ dy1_raw, const bf16x8* __restrict__ dy2,
+                    const bf16x8* __restrict__ y, const bf16x8* __restrict__ x,
+                    const float* __restrict__ save_mean, const float* __restrict__ save_invstd,
+                    const float* __restrict__ gamma, bf16x8* __restrict__ g_out,
+                    float* __restrict__ dgamma, float* __restrict__ dbeta,
+                    float* __restrict__ scratch, unsigned int* __restrict__ counter,
+                    bf16x8* __restrict__ dx, long long nvec, int cvec, float inv_m) {
+    pdl_launch_dependents();
+    pdl_wait();
+    __shared__ float sh[2][kEwThreads / 32][32][8 + 1];
+    const long long stride = static_cast<long long>(gridDim.x) * kEwThreads;
+    const long long i0 = static_cast<long long>(blockIdx.x) * kEwThreads + threadIdx.x;
+    const int cg = static_cast<int>(i0 % cvec);
+    const int C = cvec * 8;
+    float mean[8], istd[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        mean[k] = save_mean[cg * 8 + k];
+        istd[k] = save_invstd[cg * 8 + k];
+    }
+    float s1[8] = {0, 0, 0, 0, 0, 0, 0, 0}, s2[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (long long i = i0; i < nvec; i += stride) {
+        float g[8], xv[8];
+        if (DY_F32) {
+            const float4* p4 = reinterpret_cast<const float4*>(dy1_raw) + 2 * i;
+            const float4 a = p4[0], b = p4[1];
+            g[0] = a.x; g[1] = a.y; g[2] = a.z; g[3] = a.w;
+            g[4] = b.x; g[5] = b.y; g[6] = b.z; g[7] = b.w;
+        } else {
+            unpack8(reinterpret_cast<const bf16x8*>(dy1_raw)[i], g);
+        }
+        if (dy2 != nullptr) {
+            float t[8];
+            unpack8(dy2[i], t);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) g[k] += t[k];
+        }
+        if (y != nullptr) {
+            float yv[8];
+            unpack8(y[i], yv);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) g[k] = yv[k] > 0.f ? g[k] : 0.f;
+        }
+        const bf16x8 gb = pack8(g);
+        g_out[i] = gb;
+        unpack8(gb, g);
+        unpack8(x[i], xv);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            s1[k] += g[k];
+            s2[k] += g[k] * (xv[k] - mean[k]) * istd[k];
+        }
+    }
+    block_reduce_cg(s1, s2, cvec, sh);
+    if (threadIdx.x < cvec) {
+        red_add8(scratch + cg * 8, s1);          // sum g
+        red_add8(scratch + C + cg * 8, s2);      // sum g * xhat
+    }
+    // ---- grid barrier ----------------------------------------------------------------------
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        atomicAdd(counter, 1u);
+        unsigned int seen;
+        do {
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(counter) : "memory");
+        } while (seen < gridDim.x);
+    }
+    __syncthreads();
+    // ---- pass 2 ----------------------------------------------------------------------------
+    float a[8], b[8], c2[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const int c = cg * 8 + k;
+        const float sg = __ldcg(scratch + c), sgx = __ldcg(scratch + C + c);
+        a[k] = gamma[c] * istd[k];
+        b[k] = sg * inv_m;
+        c2[k] = sgx * inv_m;
+        if (blockIdx.x == 0 && threadIdx.x < cvec) {
+            dbeta[c] += sg;
+            dgamma[c] += sgx;
+        }
+    }
+    for (long long i = i0; i < nvec; i += stride) {
+        float gv[8], xv[8], o[8];
+        unpack8(g_out[i], gv);
         unpack8(x[i], xv);
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
@@ -846,6 +982,26 @@ extern "C" int dpt_bn_bwd_reduce_ex(const void* dy1, int dy1_is_f32, const void*
         dy1, static_cast<const bf16x8*>(dy2),
         static_cast<const bf16x8*>(y), static_cast<const bf16x8*>(x), save_mean, save_invstd,
         static_cast<bf16x8*>(g_out), dgamma, dbeta, nvec, C / 8);
+    DPT_CHECK_LAUNCH();
+}
+
+// One-launch BatchNorm backward (see bn_bwd_fused_kernel).  scratch: 2*C zeroed floats; counter:
+// one zeroed uint32; g_out is mandatory (pass 2 re-reads the masked gradient from it).
+extern "C" int dpt_bn_bwd_fused(const void* dy1, int dy1_is_f32, const void* dy2, const void* y,
+                                const void* x, const float* save_mean, const float* save_invstd,
+                                const float* gamma, void* g_out, float* dgamma, float* dbeta,
+                                float* scratch, unsigned int* counter, void* dx, long long M, int C,
+                                void* stream) {
+    if (!cvec_ok(C) || g_out == nullptr) return DPT_ERR_SHAPE;
+    const long long nvec = M * (C / 8);
+    auto kern = dy1_is_f32 ? bn_bwd_fused_kernel<true> : bn_bwd_fused_kernel<false>;
+    ew_pdl_gate();
+    if (dy1_is_f32) pdl_skip_flag() = 1;  // dy1 was accumulated with REDs by a split-K dgrad
+    launch_pdl(kern, dim3(reduce_grid(nvec)), dim3(kEwThreads), 0, static_cast<cudaStream_t>(stream),
+               dy1, static_cast<const bf16x8*>(dy2), static_cast<const bf16x8*>(y),
+               static_cast<const bf16x8*>(x), save_mean, save_invstd, gamma,
+               static_cast<bf16x8*>(g_out), dgamma, dbeta, scratch, counter,
+               static_cast<bf16x8*>(dx), nvec, C / 8, 1.f / static_cast<float>(M));
     DPT_CHECK_LAUNCH();
 }
 

@@ -232,7 +232,7 @@ class _EngineFn(torch.autograd.Function):
 class _Unit:
     """conv -> BN (-> +residual) (-> ReLU) with its buffers."""
     __slots__ = ("conv", "bn", "x_shape", "y_shape", "raw", "y", "sum", "sq", "mean", "invstd",
-                 "d_raw", "g", "relu", "name", "fsplit", "raw32", "dsplit")
+                 "d_raw", "g", "relu", "name", "fsplit", "raw32", "dsplit", "bscratch", "bcounter")
 
 
 def _live_taps(H, W, P, Q, k, stride, pad):
@@ -248,10 +248,12 @@ def _live_taps(H, W, P, Q, k, stride, pad):
     return n
 
 
-def _pick_splits(tiles: int, ksteps: int, sm_target: int = 120) -> int:
+def _pick_splits(tiles: int, ksteps: int, sm_target: int = 0) -> int:
     """Split the k loop over CTAs when the tile grid alone would leave most SMs idle: a single
     CTA can only pull ~50 GB/s of operands through TMA, so small-M layers are spread out."""
     import os
+    if sm_target <= 0:
+        sm_target = int(os.environ.get("DPT_SPLITK_TARGET", "64"))
     if tiles > 32 or ksteps < 4 or os.environ.get("DPT_NO_SPLITK", "0") == "1":
         return 1
     s = min(ksteps, max(1, sm_target // tiles))
@@ -281,8 +283,11 @@ class ResNetEngine:
         self._zero32_n = 0
         bns = [mod for mod in model.modules() if isinstance(mod, BatchNorm2d)]
         total_c = sum(b.num_features for b in bns)
-        # one arena for all batch statistics so a single memset clears them every step
-        self.stats = torch.zeros(2 * total_c, **f32)
+        # one arena for everything that must be zero at the start of a step (forward batch
+        # statistics, backward per-channel sums, grid-barrier counters): a single memset
+        self.stats = torch.zeros(4 * total_c + len(bns) + 8, **f32)
+        self._bwd_off = 2 * total_c
+        self._cnt_off = 4 * total_c
         self.saved = torch.zeros(2 * total_c, **f32)
         self._stat_off = 0
 
@@ -328,6 +333,8 @@ class ResNetEngine:
         self.side = torch.cuda.Stream(device=self.dev) if training else None
         self._ev_pool = [torch.cuda.Event() for _ in range(64)] if training else []
         self._ev_i = 0
+        import os
+        self._fuse_bn_bwd = os.environ.get("DPT_FUSE_BN_BWD", "0") == "1"
         self._z32_ev = torch.cuda.Event() if training else None
         self._z32_pending = False
 
@@ -346,6 +353,10 @@ class ResNetEngine:
         u.d_raw = torch.empty(y_shape, **bf) if self.training else None
         u.g = torch.empty(y_shape, **bf) if self.training else None
         u.fsplit, u.raw32, u.dsplit = 1, None, 1
+        bo = self._bwd_off + o
+        u.bscratch = self.stats[bo:bo + 2 * C]
+        ci = self._cnt_off + len(self.units)
+        u.bcounter = self.stats[ci:ci + 1].view(torch.int32)
         if self.training and conv.in_channels % 8 == 0:
             N, H, W, Cin = x_shape
             _, P, Q, Cout = y_shape
@@ -539,6 +550,13 @@ class ResNetEngine:
         """Fused (gradient-pair sum + ReLU mask +) BatchNorm backward of unit ``u``.
         Leaves grad wrt the conv output in ``u.d_raw`` and the masked gradient in ``u.g``."""
         bn = u.bn
+        nvec = u.raw.numel() // 8
+        if self._fuse_bn_bwd and nvec <= 148 * 256:
+            # small tensor: one launch (grid barrier between the reduction and the dx pass)
+            self.Fn.bn_bwd_fused(dy, u.raw, u.mean, u.invstd, bn.weight, self._gw(bn.weight),
+                                 self._gw(bn.bias), u.bscratch, u.bcounter, dy2=dy2,
+                                 y=u.y if u.relu else None, g_out=u.g, dx=u.d_raw)
+            return u.d_raw
         masked = u.relu or dy2 is not None
         self.Fn.bn_bwd(dy, u.raw, u.mean, u.invstd, bn.weight, self._gw(bn.weight),
                        self._gw(bn.bias), dy2=dy2, y=u.y if u.relu else None,

@@ -34,6 +34,7 @@ _SIGS = {
     "dpt_bn_fwd_train": [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, f32, f32, i32, vp],
     "dpt_bn_fwd_eval": [vp, vp, vp, vp, vp, vp, vp, i64, i32, f32, i32, vp],
     "dpt_bn_bwd_reduce": [vp, vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, vp],
+    "dpt_bn_bwd_fused": [vp, i32, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, vp],
     "dpt_bn_bwd_apply": [vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, vp],
     "dpt_maxpool3x3s2_fwd": [vp, vp, vp, i32, i32, i32, i32, vp],
     "dpt_maxpool3x3s2_bwd": [vp, vp, vp, vp, i32, i32, i32, i32, vp],

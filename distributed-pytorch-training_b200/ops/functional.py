@@ -146,6 +146,19 @@ def bn_bwd(dy, x, save_mean, save_invstd, gamma, dgamma, dbeta, *, dy2=None, y=N
     return dx, g
 
 
+def bn_bwd_fused(dy, x, save_mean, save_invstd, gamma, dgamma, dbeta, scratch, counter, *, dy2=None,
+                 y=None, g_out, dx):
+    """Single-launch BatchNorm backward.  ``scratch`` (2*C fp32) and ``counter`` (int32 scalar)
+    must be zero on entry; dgamma / dbeta are accumulated into."""
+    C_ = x.shape[-1]
+    M = x.numel() // C_
+    call("dpt_bn_bwd_fused", ptr(dy), int(dy.dtype == torch.float32), ptr(dy2), ptr(y), ptr(x),
+         ptr(save_mean), ptr(save_invstd), ptr(gamma), ptr(g_out), ptr(dgamma), ptr(dbeta),
+         ptr(scratch), ptr(counter), ptr(dx), M, C_, stream())
+    count()
+    return dx, g_out
+
+
 def maxpool_fwd(x, *, out=None, idx=None):
     N, H, W, C_ = x.shape
     P, Q = conv_out_hw(H, W, 3, 3, 2, 1)

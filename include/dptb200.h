@@ -71,6 +71,11 @@ int dpt_bn_bwd_reduce(const void* dy1, const void* dy2, const void* y, const voi
 int dpt_bn_bwd_reduce_ex(const void* dy1, int dy1_is_f32, const void* dy2, const void* y,
                          const void* x, const float* save_mean, const float* save_invstd,
                          void* g_out, float* dgamma, float* dbeta, long long M, int C, void* stream);
+/* both passes in one launch (grid barrier); scratch = 2*C zeroed floats, counter = zeroed u32 */
+int dpt_bn_bwd_fused(const void* dy1, int dy1_is_f32, const void* dy2, const void* y, const void* x,
+                     const float* save_mean, const float* save_invstd, const float* gamma,
+                     void* g_out, float* dgamma, float* dbeta, float* scratch,
+                     unsigned int* counter, void* dx, long long M, int C, void* stream);
 int dpt_bn_bwd_apply(const void* g, const void* x, const float* save_mean, const float* save_invstd,
                      const float* gamma, const float* dgamma, const float* dbeta, void* dx,
                      long long M, int C, void* stream);

@@ -297,3 +297,32 @@ def test_bn_small_f32_fused_and_f32_dy_backward(shape, relu, res):
     _close(dx.permute(0, 3, 1, 2), xr.grad, 4e-2, "dx")
     _close(dgamma, gr.grad, 3e-2, "dgamma")
     _close(dbeta, br.grad, 2e-2, "dbeta")
+
+
+@pytest.mark.parametrize("shape", [(128, 16, 16, 64), (128, 4, 4, 128), (128, 1, 1, 512), (5, 3, 3, 32)])
+@pytest.mark.parametrize("relu,two", [(True, True), (True, False), (False, False)])
+def test_bn_bwd_fused_single_launch(shape, relu, two):
+    """One-launch BN backward (grid barrier) equals the two-kernel version, incl. accumulation."""
+    Fn = _F()
+    C = shape[-1]
+    x = (_rand(shape, 1).float() * 2 + 0.5).to(torch.bfloat16)
+    gamma = torch.rand(C, device="cuda") + 0.5
+    beta = torch.randn(C, device="cuda")
+    ssum, ssq = torch.zeros(C, device="cuda"), torch.zeros(C, device="cuda")
+    Fn.bn_stats(x, ssum, ssq)
+    y, mean, invstd = Fn.bn_fwd_train(x, ssum, ssq, gamma, beta, relu=relu)
+    dy = _rand(shape, 5)
+    dy2 = _rand(shape, 6) if two else None
+    ref_dg, ref_db = torch.ones(C, device="cuda"), torch.ones(C, device="cuda")   # pre-existing grads
+    ref_dx, ref_g = Fn.bn_bwd(dy, x, mean, invstd, gamma, ref_dg, ref_db, dy2=dy2, y=y if relu else None)
+    dg, db = torch.ones(C, device="cuda"), torch.ones(C, device="cuda")
+    scratch = torch.zeros(2 * C, device="cuda")
+    counter = torch.zeros(1, device="cuda", dtype=torch.int32)
+    g = torch.empty_like(x)
+    dx = torch.empty_like(x)
+    Fn.bn_bwd_fused(dy, x, mean, invstd, gamma, dg, db, scratch, counter, dy2=dy2,
+                    y=y if relu else None, g_out=g, dx=dx)
+    torch.cuda.synchronize()
+    _close(dx, ref_dx, 4e-2, "dx")   # bf16 output, sums reduced in a different order
+    _close(dg, ref_dg, 5e-3, "dgamma")
+    _close(db, ref_db, 5e-3, "dbeta")
