@@ -163,7 +163,72 @@ class Communicator:
             raise RuntimeError(f"[rank {self.rank}] peer-memory collective timed out waiting for "
                                f"rank {peer} (epoch {code & 0xFFFFFF}); a rank died or stalled")
 
+    # ------------------------------------------------------------------ watchdog / heartbeat
+    def start_watchdog(self, interval_s: float = 1.0, abort: bool = False, heartbeat: bool = True):
+        """Host thread that (a) polls the device-written error word, so a peer that died or
+        stalled is reported with (rank, peer, epoch) instead of hanging the job — the stand-in
+        for ProcessGroupNCCL's watchdog / heartbeat monitor (ProcessGroupNCCL.hpp:610,690) — and
+        (b) publishes a per-rank heartbeat key in the torch store."""
+        import os
+        import sys
+        import threading
+        import time
+        if getattr(self, "_wd_thread", None) is not None:
+            return
+        self._wd_stop = threading.Event()
+        self.fault = None
+        store = None
+        if heartbeat and dist.is_available() and dist.is_initialized():
+            try:
+                store = dist.distributed_c10d._get_default_store()
+            except Exception:  # noqa: BLE001
+                store = None
+
+        def run():
+            while not self._wd_stop.wait(interval_s):
+                try:
+                    if store is not None:
+                        store.set(f"dpt_b200/heartbeat/{self.rank}", str(time.time()))
+                    code = int(self.lib.dpt_comm_error(self.handle)) if self.handle else 0
+                except Exception:  # noqa: BLE001
+                    return
+                if code:
+                    peer = (code >> 24) & 0x7F
+                    self.fault = (self.rank, peer, code & 0xFFFFFF)
+                    sys.stderr.write(f"[dpt_b200 watchdog] rank {self.rank}: collective timed out "
+                                     f"waiting for rank {peer} (epoch {code & 0xFFFFFF})\n")
+                    sys.stderr.flush()
+                    if abort:
+                        os._exit(70)
+                    return
+
+        self._wd_thread = threading.Thread(target=run, name="dpt-watchdog", daemon=True)
+        self._wd_thread.start()
+
+    def peer_heartbeats(self) -> dict:
+        """Age in seconds of every rank's last heartbeat (needs start_watchdog on all ranks)."""
+        import time
+        out = {}
+        try:
+            store = dist.distributed_c10d._get_default_store()
+        except Exception:  # noqa: BLE001
+            return out
+        now = time.time()
+        for r in range(self.world):
+            try:
+                out[r] = now - float(store.get(f"dpt_b200/heartbeat/{r}").decode())
+            except Exception:  # noqa: BLE001
+                out[r] = float("inf")
+        return out
+
+    def stop_watchdog(self) -> None:
+        if getattr(self, "_wd_thread", None) is not None:
+            self._wd_stop.set()
+            self._wd_thread.join(timeout=2.0)
+            self._wd_thread = None
+
     def close(self) -> None:
+        self.stop_watchdog()
         if getattr(self, "handle", None) is None:
             return
         torch.cuda.synchronize()

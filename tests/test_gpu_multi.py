@@ -288,3 +288,45 @@ def _trainstep_worker(rank, world):
 @needs2
 def test_trainstep_under_native_ddp_graph_and_fused_optimizer():
     _run(_trainstep_worker)
+
+
+# --------------------------------------------------------------------------------- fault path
+def _stalled_rank_worker(rank, world):
+    """A rank that never enters the collective must produce a diagnostic on the others within
+    the timeout instead of a hang; DPT_FAULT_STALL_RANK injects the fault."""
+    import time
+    import torch.distributed as dist
+    from dpt_b200.parallel.comm import Communicator
+    comm = Communicator(timeout_s=1.5)
+    comm.start_watchdog(interval_s=0.2)
+    dev = torch.device("cuda", rank)
+    buf = comm.alloc(1 << 20)
+    stalled = int(os.environ.get("DPT_FAULT_STALL_RANK", world - 1))
+    torch.cuda.synchronize()
+    dist.barrier()
+    t0 = time.time()
+    if rank != stalled:
+        comm.allreduce_(buf, 0, 1 << 18)
+        torch.cuda.synchronize()               # returns once the device-side wait timed out
+        elapsed = time.time() - t0
+        assert elapsed < 20.0, f"collective hung for {elapsed:.1f}s"
+        raised = False
+        try:
+            comm.check_health()
+        except RuntimeError as e:
+            raised = True
+            assert f"rank {stalled}" in str(e) or "timed out" in str(e), str(e)
+        assert raised, "a missing peer must surface as an error"
+        time.sleep(0.5)
+        assert comm.fault is not None and comm.fault[0] == rank, "watchdog thread did not report"
+    else:
+        time.sleep(4.0)                         # the "dead" rank
+    hb = comm.peer_heartbeats()
+    assert all(v < 30 for v in hb.values()), hb
+    dist.barrier()
+    comm.stop_watchdog()
+
+
+@needs2
+def test_stalled_rank_times_out_with_diagnostic():
+    _run(_stalled_rank_worker, world=2)
