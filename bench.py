@@ -45,6 +45,7 @@ def parse():
                    help="apply SGD inside the all-reduce kernel (default: on when N > 1)")
     p.add_argument("--no-fused-optimizer", dest="fused_optimizer", action="store_false")
     p.add_argument("--bucket-cap-mb", type=float, default=None)
+    p.add_argument("--allreduce-algo", default="auto", choices=["auto", "twoshot", "nvls"])
     p.add_argument("--comm-ctas", type=int, default=16,
                    help="CTAs of each bucket all-reduce kernel (fewer = less SM contention with backward)")
     p.add_argument("--eager-buffer-sync", action="store_true",
@@ -158,7 +159,8 @@ def run_ours(a):
     ddp = None
     if world > 1:
         model = ddp = DistributedDataParallel(model, device_ids=[local], backend="native",
-                                              bucket_cap_mb=a.bucket_cap_mb, comm_ctas=a.comm_ctas)
+                                              bucket_cap_mb=a.bucket_cap_mb, comm_ctas=a.comm_ctas,
+                                              allreduce_algo=a.allreduce_algo)
     opt = SGD(model.parameters(), lr=0.1, momentum=0.9, weight_decay=5e-4)
     if a.fused_optimizer is None:
         a.fused_optimizer = world > 1
@@ -249,6 +251,7 @@ def run_ours(a):
                                       "1/world" + (" + SGD update" if a.fused_optimizer else "") + " epilogue")
                                      if world > 1 else "none (1 GPU)",
                    "fused_optimizer": bool(a.fused_optimizer and world > 1),
+                   "nvls": bool(getattr(ddp, "nvls", False)) if ddp is not None else False,
                    "grad_buckets_bytes": ddp.bucket_sizes() if ddp is not None else [],
                    "bn_buffer_sync": "lazy (before eval/checkpoint)" if not a.eager_buffer_sync else "every step"},
         "clocks": clocks,

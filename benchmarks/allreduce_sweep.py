@@ -56,7 +56,8 @@ def main():
         s *= 4
     extra = [9461800 // 16 * 16, 26494976, 8769792, 44726568 // 16 * 16]  # ResNet-18 DDP buckets
     sizes = sorted(set(sizes + [e for e in extra if e <= a.max_mb * 1024 * 1024]))
-    buf = comm.alloc(max(sizes))
+    buf = comm.alloc_multicast(max(sizes)) or comm.alloc(max(sizes))
+    has_nvls = hasattr(buf, "mc_ptr")
     out = torch.empty(min(max(sizes), 4 << 20) // 4, device="cuda")
     rows = []
     for nbytes in sizes:
@@ -69,15 +70,18 @@ def main():
         if nbytes <= (4 << 20):
             o = out[:n]
             t_one = timeit(lambda: comm.allreduce_oneshot(buf, 0, o), iters)
+        t_nvls = timeit(lambda: comm.allreduce_nvls_(buf, 0, n, ctas=a.ctas), iters) if has_nvls else None
         f = 2 * (world - 1) / world
         row = {"bytes": nbytes, "nccl_us": t_nccl, "twoshot_us": t_two, "oneshot_us": t_one,
                "nccl_busbw_gbs": nbytes / t_nccl * f / 1e3, "twoshot_busbw_gbs": nbytes / t_two * f / 1e3,
-               "twoshot_vs_nccl": t_nccl / t_two,
+               "nvls_us": t_nvls, "nvls_busbw_gbs": (nbytes / t_nvls * f / 1e3) if t_nvls else None,
+               "twoshot_vs_nccl": t_nccl / t_two, "nvls_vs_nccl": (t_nccl / t_nvls) if t_nvls else None,
                "twoshot_frac_of_770": nbytes / t_two * f / 1e3 / 770.0}
         rows.append(row)
         if rank == 0:
             one = f"{t_one:9.1f}" if t_one is not None else "        -"
-            print(f"{nbytes:>12d} B  nccl {t_nccl:9.1f} us  two-shot {t_two:9.1f} us  one-shot {one} us  "
+            nv = f"{t_nvls:9.1f}" if t_nvls is not None else "        -"
+            print(f"{nbytes:>12d} B  nccl {t_nccl:9.1f} us  two-shot {t_two:9.1f} us  nvls {nv} us  one-shot {one} us  "
                   f"busBW nccl {row['nccl_busbw_gbs']:7.1f}  ours {row['twoshot_busbw_gbs']:7.1f} GB/s  "
                   f"speedup {row['twoshot_vs_nccl']:5.2f}x", flush=True)
     comm.check_health()

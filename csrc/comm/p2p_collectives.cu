@@ -250,6 +250,64 @@ broadcast_kernel(CommCtx c, Peers bufs, long long n16, int src) {
     if (threadIdx.x == 0) c.epoch[blockIdx.x] = e0 + 2;
 }
 
+// NVLS: multimem.ld_reduce returns the in-switch sum of every rank's copy, multimem.st writes
+// every copy.  Rank r still owns slice r (so each element is reduced and broadcast exactly
+// once); link traffic per GPU is ~S instead of 2(N-1)/N*S and the reduction costs no SM adds.
+__device__ __forceinline__ float4 multimem_ld_reduce_f32x4(const float4* mc) {
+    float4 r;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+                 : "l"(mc)
+                 : "memory");
+    return r;
+}
+__device__ __forceinline__ void multimem_st_f32x4(float4* mc, float4 v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(v.x),
+                 "f"(v.y), "f"(v.z), "f"(v.w)
+                 : "memory");
+}
+
+__global__ void __launch_bounds__(kCommThreads, 1)
+allreduce_nvls_kernel(CommCtx c, float* __restrict__ mc, long long n4, Epilogue ep) {
+    __shared__ uint32_t s_epoch;
+    if (threadIdx.x == 0) s_epoch = c.epoch[blockIdx.x];
+    __syncthreads();
+    const uint32_t e0 = s_epoch;
+    xgpu_barrier(c, e0 + 1);
+    const long long per = (n4 + c.world - 1) / c.world;
+    const long long lo = per * c.rank;
+    const long long hi = min(n4, lo + per);
+    const float gs = ep.scale * (ep.inv_scale ? *ep.inv_scale : 1.f);
+    bool bad = false;
+    float4* mc4 = reinterpret_cast<float4*>(mc);
+    const long long step = static_cast<long long>(gridDim.x) * kCommThreads;
+    constexpr int kU = 4;
+    for (long long i0 = lo + static_cast<long long>(blockIdx.x) * kCommThreads + threadIdx.x;
+         i0 < hi; i0 += step * kU) {
+        float4 v[kU];
+#pragma unroll
+        for (int u = 0; u < kU; ++u)
+            if (i0 + u * step < hi) v[u] = multimem_ld_reduce_f32x4(mc4 + i0 + u * step);
+#pragma unroll
+        for (int u = 0; u < kU; ++u) {
+            const long long i = i0 + u * step;
+            if (i >= hi) continue;
+            float4 s = v[u];
+            bad |= !(isfinite(s.x) && isfinite(s.y) && isfinite(s.z) && isfinite(s.w));
+            s.x *= gs;
+            s.y *= gs;
+            s.z *= gs;
+            s.w *= gs;
+            multimem_st_f32x4(mc4 + i, s);
+        }
+    }
+    if (ep.found_inf[0] != nullptr && __any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) {
+        for (int p = 0; p < c.world; ++p) *ep.found_inf[p] = 1.f;
+    }
+    xgpu_barrier(c, e0 + 2);
+    if (threadIdx.x == 0) c.epoch[blockIdx.x] = e0 + 2;
+}
+
 __global__ void barrier_kernel(CommCtx c) {
     __shared__ uint32_t s_epoch;
     if (threadIdx.x == 0) s_epoch = c.epoch[blockIdx.x];
@@ -459,6 +517,24 @@ extern "C" int dpt_allreduce_oneshot(dpt_comm* c, void* const* in, float* out, l
         case 8: launch_oneshot<8>(c, g, out, n4, ep, ctas, st); break;
         default: return DPT_ERR_ARG;
     }
+    return static_cast<int>(cudaGetLastError());
+}
+
+// NVLS in-place fused all-reduce: `mc` is this rank's mapping of the multicast object covering
+// every rank's buffer (plus the same element offset on every rank).
+extern "C" int dpt_allreduce_nvls(dpt_comm* c, void* mc, long long n, float scale,
+                                  const float* inv_scale, void* const* found_inf, int ctas,
+                                  void* stream) {
+    if (n % 4 != 0) return DPT_ERR_SHAPE;
+    const int world = c->ctx.world;
+    if (world < 2) return DPT_ERR_ARG;
+    const long long n4 = n / 4;
+    Epilogue ep;
+    fill_epilogue(&ep, world, scale, inv_scale, found_inf);
+    if (ctas <= 0) ctas = 16;
+    ctas = clamp_ctas(ctas, n4, world);
+    allreduce_nvls_kernel<<<ctas, kCommThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+        c->ctx, static_cast<float*>(mc), n4, ep);
     return static_cast<int>(cudaGetLastError());
 }
 

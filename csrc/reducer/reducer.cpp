@@ -144,6 +144,17 @@ void Reducer::launch_bucket(int b, cudaStream_t compute) {
         }
     }
     const bool fuse = fusion_.enabled && world_ > 1;
+    if (nvls_mc_ != 0 && !fuse && world_ > 1 && bk.numel * 4 >= nvls_min_bytes_) {
+        int rc2 = dpt_allreduce_nvls(
+            comm_, reinterpret_cast<void*>(nvls_mc_ + bk.offset * 4), bk.numel,
+            1.0f / static_cast<float>(world_), reinterpret_cast<const float*>(inv_scale_),
+            (check_finite_ && !found_inf_ptrs_.empty()) ? finf : nullptr, ctas_, comm_stream_);
+        if (rc2 != 0)
+            throw std::runtime_error("dpt_allreduce_nvls failed with code " + std::to_string(rc2));
+        DPTR_CUDA(cudaEventRecord(ev_done_[b], comm_stream_));
+        ++launches_;
+        return;
+    }
     int rc = dpt_allreduce_fused(
         comm_, bufs, bk.numel, 1.0f / static_cast<float>(world_),
         reinterpret_cast<const float*>(inv_scale_),

@@ -65,6 +65,12 @@ class Reducer {
         check_finite_ = check_finite;
     }
     void set_enabled(bool on) { enabled_ = on; }  // no_sync()
+    // NVLS: base of this rank's multicast mapping of the gradient arena; buckets of at least
+    // `min_bytes` use the multimem kernel (unless the fused-SGD epilogue is active).
+    void set_nvls(uintptr_t mc_grad_base, int64_t min_bytes) {
+        nvls_mc_ = mc_grad_base;
+        nvls_min_bytes_ = min_bytes;
+    }
 
     void prepare_for_backward(uintptr_t compute_stream);
     void mark_ready(int param_index, uintptr_t compute_stream);
@@ -101,6 +107,8 @@ class Reducer {
     std::vector<cudaEvent_t> ev_ready_, ev_start_, ev_done_;
     cudaEvent_t ev_bwd_start_ = nullptr, ev_bwd_end_ = nullptr;
     int64_t launches_ = 0;
+    uintptr_t nvls_mc_ = 0;
+    int64_t nvls_min_bytes_ = 0;
 };
 
 }  // namespace dptr

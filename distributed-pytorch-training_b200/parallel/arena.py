@@ -41,7 +41,7 @@ def _dense_strides(p: torch.Tensor) -> tuple:
 
 
 class ParamArena:
-    def __init__(self, named_params, device, comm=None, with_shadow=True) -> None:
+    def __init__(self, named_params, device, comm=None, with_shadow=True, multicast=False) -> None:
         named_params = [(n, p) for n, p in named_params if p.requires_grad]
         self.device = torch.device(device)
         self.comm = comm
@@ -58,7 +58,9 @@ class ParamArena:
         self.symmetric = comm is not None and self.device.type == "cuda"
         if self.symmetric:
             self.param_buf = comm.alloc(self.numel * 4)
-            self.grad_buf = comm.alloc(self.numel * 4)
+            # gradients may additionally be bound to an NVSwitch multicast object (NVLS)
+            self.grad_buf = (comm.alloc_multicast(self.numel * 4) if multicast else None) \
+                or comm.alloc(self.numel * 4)
             self.shadow_buf = comm.alloc(self.numel * 2) if with_shadow else None
             self.param = self.param_buf.view(torch.float32, 0, self.numel)
             self.grad = self.grad_buf.view(torch.float32, 0, self.numel)

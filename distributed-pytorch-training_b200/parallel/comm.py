@@ -65,6 +65,7 @@ class Communicator:
         self.lib = _lib.lib()
         self.device = torch.device("cuda", torch.cuda.current_device())
         self._buffers: list[SymmBuffer] = []
+        self._mc_buffers: list = []
         self.flags = self.alloc(int(self.lib.dpt_comm_flag_bytes()))
         handle = C.c_void_p()
         _lib.check(self.lib.dpt_comm_create(self.rank, self.world, self.flags.ptrs(), float(timeout_s),
@@ -102,6 +103,40 @@ class Communicator:
         sb = SymmBuffer(nbytes, local, peer_ptrs, opened)
         self._buffers.append(sb)
         return sb
+
+    def alloc_multicast(self, nbytes: int):
+        """Symmetric buffer that is additionally bound to an NVSwitch multicast object (NVLS).
+        Returns None when multicast is not exposed here (callers fall back to ``alloc``)."""
+        from . import nvls
+        if self.world < 2 or not nvls.multicast_supported(self.device.index):
+            return None
+        ok = torch.tensor([1], device=self.device)
+        try:
+            buf = nvls.MulticastBuffer(self, nbytes)
+        except Exception as e:  # noqa: BLE001
+            import sys
+            sys.stderr.write(f"[dpt_b200] rank {self.rank}: NVLS setup failed ({e}); using P2P kernels\n")
+            buf = None
+            ok.zero_()
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)
+        if int(ok.item()) == 0:
+            return None
+        self._mc_buffers.append(buf)
+        return buf
+
+    def allreduce_nvls_(self, buf, byte_offset: int, numel: int, *, scale: float | None = None,
+                        inv_scale: torch.Tensor | None = None, check_finite: bool = False,
+                        ctas: int = 0, stream: int | None = None) -> None:
+        """In-place fused all-reduce through the multicast mapping of ``buf``."""
+        if scale is None:
+            scale = 1.0 / self.world
+        st = _lib.stream() if stream is None else stream
+        fi = self.scalars.ptrs(0) if check_finite else None
+        _lib.check(self.lib.dpt_allreduce_nvls(self.handle, buf.mc_ptr + byte_offset, numel, scale,
+                                               _lib.ptr(inv_scale), fi, ctas, st),
+                   "dpt_allreduce_nvls")
+        self.launches += 1
+        _lib.count()
 
     def host_barrier(self) -> None:
         if self.world > 1:
@@ -240,5 +275,8 @@ class Communicator:
         for sb in self._buffers:
             self.lib.dpt_symm_free(sb.peer_ptrs[self.rank])
         self._buffers.clear()
+        for mb in self._mc_buffers:
+            mb.release()
+        self._mc_buffers.clear()
         self.lib.dpt_comm_destroy(self.handle)
         self.handle = None

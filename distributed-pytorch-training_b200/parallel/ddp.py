@@ -151,7 +151,8 @@ class DistributedDataParallel(nn.Module):
                  find_unused_parameters=False, check_reduction=False,
                  gradient_as_bucket_view=True, static_graph=True, *, backend: str = "native",
                  comm=None, fused_optimizer=False, profile=False, comm_ctas: int = 0,
-                 comm_timeout: float = 30.0, first_bucket_mb: float = 1.0):
+                 comm_timeout: float = 30.0, first_bucket_mb: float = 1.0,
+                 allreduce_algo: str = "auto", nvls_min_bytes: int = 1 << 20):
         super().__init__()
         self.module = module
         self.device_ids = device_ids
@@ -199,7 +200,14 @@ class DistributedDataParallel(nn.Module):
         if backend == "native" and self.comm is None:
             from .comm import Communicator
             self.comm = Communicator(process_group, timeout_s=comm_timeout)
-        self.arena = ParamArena(params, self.device, comm=self.comm if backend == "native" else None)
+        self.allreduce_algo = allreduce_algo
+        # auto: NVLS only pays off when the in-switch reduction saves link traffic (2(N-1)/N*S vs
+        # S per GPU): measured slower than two-shot at N=2, so it is considered from N >= 4
+        want_nvls = backend == "native" and self.world_size > 1 and (
+            allreduce_algo == "nvls" or (allreduce_algo == "auto" and self.world_size >= 4))
+        self.arena = ParamArena(params, self.device, comm=self.comm if backend == "native" else None,
+                                multicast=want_nvls)
+        self.nvls = want_nvls and hasattr(self.arena.grad_buf, "mc_ptr")
         self._buffer_arena_init()
         if init_sync:
             self._sync_module_states()
@@ -218,6 +226,10 @@ class DistributedDataParallel(nn.Module):
             self.reducer = E.Reducer(specs, len(self.arena.order), self.comm.handle.value or 0,
                                      self.world_size, list(self.arena.grad_buf.peer_ptrs), found, 0,
                                      comm_ctas, bool(profile))
+            if self.nvls:
+                # measured crossover: the multimem kernel wins from ~1 MB up (profiles/README.md)
+                self.reducer.set_nvls(self.arena.grad_buf.mc_ptr,
+                                      0 if allreduce_algo == "nvls" else int(nvls_min_bytes))
             E.register_hooks(self.reducer, list(self.arena.order),
                              [self.arena.grad_view(p) for p in self.arena.order])
         else:
@@ -461,6 +473,8 @@ class DistributedDataParallel(nn.Module):
             "world_size": self.world_size,
             "rank": self.rank,
             "backend_name": self.backend,
+            "allreduce_algo": ("nvls+twoshot" if getattr(self, "nvls", False) else "twoshot")
+            if self.backend == "native" else "torch.distributed",
             "num_parameter_tensors": len(order),
             "total_parameter_size_bytes": sum(p.numel() * 4 for p in order),
             "bucket_cap_bytes": self.bucket_bytes_cap,

@@ -330,3 +330,50 @@ def _stalled_rank_worker(rank, world):
 @needs2
 def test_stalled_rank_times_out_with_diagnostic():
     _run(_stalled_rank_worker, world=2)
+
+
+# --------------------------------------------------------------------------------- NVLS
+def _nvls_worker(rank, world):
+    import torch.distributed as dist
+    from dpt_b200.parallel.comm import Communicator
+    comm = Communicator(timeout_s=20.0)
+    dev = torch.device("cuda", rank)
+    buf = comm.alloc_multicast(64 << 20)
+    if buf is None:
+        if rank == 0:
+            print("NVLS multicast not exposed on this host: skipped")
+        comm.close()
+        return
+    for n in (4, 1024, 4100, 1 << 20, 11181648):
+        for rep in range(2):
+            x = torch.randn(n, device=dev, generator=torch.Generator(device=dev).manual_seed(31 * rank + rep + n % 97))
+            view = buf.view(torch.float32, 0, n)
+            view.copy_(x)
+            ref = x.clone()
+            dist.all_reduce(ref)
+            torch.cuda.synchronize()
+            dist.barrier()
+            comm.allreduce_nvls_(buf, 0, n)
+            torch.cuda.synchronize()
+            err = (view - ref / world).abs().max().item()
+            assert err <= 2e-5 * max(1.0, ref.abs().max().item()), (n, rep, err)
+            lo, hi = view.clone(), view.clone()
+            dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+            dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+            assert torch.equal(lo, hi), n
+    # the same buffer also works with the P2P kernels (unicast peer mappings)
+    n = 65536
+    view = buf.view(torch.float32, 0, n)
+    view.fill_(float(rank + 1))
+    torch.cuda.synchronize()
+    dist.barrier()
+    comm.allreduce_(buf, 0, n, scale=1.0)
+    torch.cuda.synchronize()
+    assert torch.allclose(view, torch.full_like(view, world * (world + 1) / 2))
+    comm.check_health()
+    comm.close()
+
+
+@needs2
+def test_nvls_multicast_allreduce():
+    _run(_nvls_worker)
