@@ -101,6 +101,9 @@ struct Epilogue {
     float lr, mu, wd;
     int nesterov;
     int fused_sgd;
+    // NVLS + fused SGD: multicast mappings of the param / shadow arenas
+    float* param_mc;
+    __nv_bfloat16* shadow_mc;
 };
 
 
@@ -261,6 +264,9 @@ __device__ __forceinline__ float4 multimem_ld_reduce_f32x4(const float4* mc) {
                  : "memory");
     return r;
 }
+__device__ __forceinline__ void multimem_st_b64(void* mc, unsigned long long v) {
+    asm volatile("multimem.st.relaxed.sys.global.b64 [%0], %1;" ::"l"(mc), "l"(v) : "memory");
+}
 __device__ __forceinline__ void multimem_st_f32x4(float4* mc, float4 v) {
     asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(v.x),
                  "f"(v.y), "f"(v.z), "f"(v.w)
@@ -298,7 +304,33 @@ allreduce_nvls_kernel(CommCtx c, float* __restrict__ mc, long long n4, Epilogue 
             s.y *= gs;
             s.z *= gs;
             s.w *= gs;
-            multimem_st_f32x4(mc4 + i, s);
+            if (!ep.fused_sgd) {
+                multimem_st_f32x4(mc4 + i, s);
+            } else {
+                // owner updates its slice of the fp32 master weights + momentum, then one
+                // multicast store each publishes the new weights and their bf16 shadow everywhere
+                float4 pv = reinterpret_cast<float4*>(ep.param[c.rank])[i];
+                float4 mv = reinterpret_cast<float4*>(ep.momentum)[i];
+                float pa[4] = {pv.x, pv.y, pv.z, pv.w};
+                float ma[4] = {mv.x, mv.y, mv.z, mv.w};
+                const float ga[4] = {s.x, s.y, s.z, s.w};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    float d = fmaf(ep.wd, pa[k], ga[k]);
+                    ma[k] = fmaf(ep.mu, ma[k], d);
+                    d = ep.nesterov ? fmaf(ep.mu, ma[k], d) : ma[k];
+                    pa[k] = fmaf(-ep.lr, d, pa[k]);
+                }
+                reinterpret_cast<float4*>(ep.momentum)[i] = make_float4(ma[0], ma[1], ma[2], ma[3]);
+                multimem_st_f32x4(reinterpret_cast<float4*>(ep.param_mc) + i,
+                                  make_float4(pa[0], pa[1], pa[2], pa[3]));
+                __nv_bfloat162 b0 = __floats2bfloat162_rn(pa[0], pa[1]);
+                __nv_bfloat162 b1 = __floats2bfloat162_rn(pa[2], pa[3]);
+                const unsigned long long pk =
+                    static_cast<unsigned long long>(*reinterpret_cast<uint32_t*>(&b0)) |
+                    (static_cast<unsigned long long>(*reinterpret_cast<uint32_t*>(&b1)) << 32);
+                multimem_st_b64(reinterpret_cast<uint2*>(ep.shadow_mc) + i, pk);
+            }
         }
     }
     if (ep.found_inf[0] != nullptr && __any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) {
@@ -522,15 +554,44 @@ extern "C" int dpt_allreduce_oneshot(dpt_comm* c, void* const* in, float* out, l
 
 // NVLS in-place fused all-reduce: `mc` is this rank's mapping of the multicast object covering
 // every rank's buffer (plus the same element offset on every rank).
+extern "C" int dpt_allreduce_nvls_sgd(dpt_comm* c, void* mc, long long n, float scale,
+                                      const float* inv_scale, void* const* found_inf,
+                                      float* param_local, float* momentum, void* param_mc,
+                                      void* shadow_mc, float lr, float mu, float wd, int nesterov,
+                                      int ctas, void* stream);
+
 extern "C" int dpt_allreduce_nvls(dpt_comm* c, void* mc, long long n, float scale,
                                   const float* inv_scale, void* const* found_inf, int ctas,
                                   void* stream) {
+    return dpt_allreduce_nvls_sgd(c, mc, n, scale, inv_scale, found_inf, nullptr, nullptr, nullptr,
+                                  nullptr, 0.f, 0.f, 0.f, 0, ctas, stream);
+}
+
+// NVLS all-reduce with the SGD-momentum update fused in (param_local != NULL): rank r reduces
+// slice r in the switch, updates its slice of the local fp32 masters + momentum and publishes
+// the new weights / bf16 shadow to every rank through the multicast mappings.
+extern "C" int dpt_allreduce_nvls_sgd(dpt_comm* c, void* mc, long long n, float scale,
+                                      const float* inv_scale, void* const* found_inf,
+                                      float* param_local, float* momentum, void* param_mc,
+                                      void* shadow_mc, float lr, float mu, float wd, int nesterov,
+                                      int ctas, void* stream) {
     if (n % 4 != 0) return DPT_ERR_SHAPE;
     const int world = c->ctx.world;
     if (world < 2) return DPT_ERR_ARG;
     const long long n4 = n / 4;
     Epilogue ep;
     fill_epilogue(&ep, world, scale, inv_scale, found_inf);
+    if (param_local != nullptr) {
+        ep.fused_sgd = 1;
+        ep.param[c->ctx.rank] = param_local;
+        ep.momentum = momentum;
+        ep.param_mc = static_cast<float*>(param_mc);
+        ep.shadow_mc = static_cast<__nv_bfloat16*>(shadow_mc);
+        ep.lr = lr;
+        ep.mu = mu;
+        ep.wd = wd;
+        ep.nesterov = nesterov;
+    }
     if (ctas <= 0) ctas = 16;
     ctas = clamp_ctas(ctas, n4, world);
     allreduce_nvls_kernel<<<ctas, kCommThreads, 0, static_cast<cudaStream_t>(stream)>>>(

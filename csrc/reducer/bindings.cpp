@@ -70,7 +70,9 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
         .def_readwrite("lr", &dptr::SgdFusion::lr)
         .def_readwrite("mu", &dptr::SgdFusion::mu)
         .def_readwrite("wd", &dptr::SgdFusion::wd)
-        .def_readwrite("nesterov", &dptr::SgdFusion::nesterov);
+        .def_readwrite("nesterov", &dptr::SgdFusion::nesterov)
+        .def_readwrite("param_mc", &dptr::SgdFusion::param_mc)
+        .def_readwrite("shadow_mc", &dptr::SgdFusion::shadow_mc);
     py::class_<dptr::BucketTiming>(m, "BucketTiming")
         .def_readonly("ready_ms", &dptr::BucketTiming::ready_ms)
         .def_readonly("start_ms", &dptr::BucketTiming::start_ms)

@@ -144,11 +144,18 @@ void Reducer::launch_bucket(int b, cudaStream_t compute) {
         }
     }
     const bool fuse = fusion_.enabled && world_ > 1;
-    if (nvls_mc_ != 0 && !fuse && world_ > 1 && bk.numel * 4 >= nvls_min_bytes_) {
-        int rc2 = dpt_allreduce_nvls(
+    const bool nvls_fuse_ok = !fuse || (fusion_.param_mc != 0 && fusion_.shadow_mc != 0);
+    if (nvls_mc_ != 0 && nvls_fuse_ok && world_ > 1 && bk.numel * 4 >= nvls_min_bytes_) {
+        const int me = rank_;
+        int rc2 = dpt_allreduce_nvls_sgd(
             comm_, reinterpret_cast<void*>(nvls_mc_ + bk.offset * 4), bk.numel,
             1.0f / static_cast<float>(world_), reinterpret_cast<const float*>(inv_scale_),
-            (check_finite_ && !found_inf_ptrs_.empty()) ? finf : nullptr, ctas_, comm_stream_);
+            (check_finite_ && !found_inf_ptrs_.empty()) ? finf : nullptr,
+            fuse ? reinterpret_cast<float*>(fusion_.param_ptrs[me] + bk.offset * 4) : nullptr,
+            fuse ? reinterpret_cast<float*>(fusion_.momentum + bk.offset * 4) : nullptr,
+            fuse ? reinterpret_cast<void*>(fusion_.param_mc + bk.offset * 4) : nullptr,
+            fuse ? reinterpret_cast<void*>(fusion_.shadow_mc + bk.offset * 2) : nullptr, fusion_.lr,
+            fusion_.mu, fusion_.wd, fusion_.nesterov, ctas_, comm_stream_);
         if (rc2 != 0)
             throw std::runtime_error("dpt_allreduce_nvls failed with code " + std::to_string(rc2));
         DPTR_CUDA(cudaEventRecord(ev_done_[b], comm_stream_));

@@ -42,6 +42,8 @@ struct SgdFusion {
     uintptr_t momentum = 0;              // local fp32 momentum arena base
     float lr = 0, mu = 0, wd = 0;
     int nesterov = 0;
+    // NVLS: multicast mappings of the param / shadow arenas (0 = not available)
+    uintptr_t param_mc = 0, shadow_mc = 0;
 };
 
 struct BucketTiming {
@@ -67,9 +69,10 @@ class Reducer {
     void set_enabled(bool on) { enabled_ = on; }  // no_sync()
     // NVLS: base of this rank's multicast mapping of the gradient arena; buckets of at least
     // `min_bytes` use the multimem kernel (unless the fused-SGD epilogue is active).
-    void set_nvls(uintptr_t mc_grad_base, int64_t min_bytes) {
+    void set_nvls(uintptr_t mc_grad_base, int64_t min_bytes, int rank) {
         nvls_mc_ = mc_grad_base;
         nvls_min_bytes_ = min_bytes;
+        rank_ = rank;
     }
 
     void prepare_for_backward(uintptr_t compute_stream);
@@ -109,6 +112,7 @@ class Reducer {
     int64_t launches_ = 0;
     uintptr_t nvls_mc_ = 0;
     int64_t nvls_min_bytes_ = 0;
+    int rank_ = 0;
 };
 
 }  // namespace dptr

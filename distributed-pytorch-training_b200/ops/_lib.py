@@ -60,6 +60,8 @@ _SIGS = {
                             C.POINTER(vp), vp, f32, f32, f32, i32, i32, vp],
     "dpt_allreduce_oneshot": [vp, C.POINTER(vp), vp, i64, f32, vp, C.POINTER(vp), i32, vp],
     "dpt_allreduce_nvls": [vp, vp, i64, f32, vp, C.POINTER(vp), i32, vp],
+    "dpt_allreduce_nvls_sgd": [vp, vp, i64, f32, vp, C.POINTER(vp), vp, vp, vp, vp, f32, f32, f32, i32,
+                               i32, vp],
     "dpt_broadcast": [vp, C.POINTER(vp), i64, i32, i32, vp],
     "dpt_barrier": [vp, vp],
 }

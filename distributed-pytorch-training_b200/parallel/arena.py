@@ -57,11 +57,13 @@ class ParamArena:
         self.numel = max(off, ALIGN)
         self.symmetric = comm is not None and self.device.type == "cuda"
         if self.symmetric:
-            self.param_buf = comm.alloc(self.numel * 4)
+            self.param_buf = (comm.alloc_multicast(self.numel * 4) if multicast else None) \
+                or comm.alloc(self.numel * 4)
             # gradients may additionally be bound to an NVSwitch multicast object (NVLS)
             self.grad_buf = (comm.alloc_multicast(self.numel * 4) if multicast else None) \
                 or comm.alloc(self.numel * 4)
-            self.shadow_buf = comm.alloc(self.numel * 2) if with_shadow else None
+            self.shadow_buf = ((comm.alloc_multicast(self.numel * 2) if multicast else None)
+                               or comm.alloc(self.numel * 2)) if with_shadow else None
             self.param = self.param_buf.view(torch.float32, 0, self.numel)
             self.grad = self.grad_buf.view(torch.float32, 0, self.numel)
             self.shadow = self.shadow_buf.view(torch.bfloat16, 0, self.numel) if with_shadow else None

@@ -229,7 +229,8 @@ class DistributedDataParallel(nn.Module):
             if self.nvls:
                 # measured crossover: the multimem kernel wins from ~1 MB up (profiles/README.md)
                 self.reducer.set_nvls(self.arena.grad_buf.mc_ptr,
-                                      0 if allreduce_algo == "nvls" else int(nvls_min_bytes))
+                                      0 if allreduce_algo == "nvls" else int(nvls_min_bytes),
+                                      self.rank)
             E.register_hooks(self.reducer, list(self.arena.order),
                              [self.arena.grad_view(p) for p in self.arena.order])
         else:
@@ -320,6 +321,10 @@ class DistributedDataParallel(nn.Module):
         f.shadow_ptrs = list(self.arena.shadow_buf.peer_ptrs)
         f.momentum = optimizer._flat_momentum().data_ptr()
         f.lr, f.mu, f.wd, f.nesterov = g["lr"], g["momentum"], g["weight_decay"], int(g["nesterov"])
+        if getattr(self, "nvls", False) and hasattr(self.arena.param_buf, "mc_ptr") \
+                and hasattr(self.arena.shadow_buf, "mc_ptr"):
+            f.param_mc = self.arena.param_buf.mc_ptr
+            f.shadow_mc = self.arena.shadow_buf.mc_ptr
         self.reducer.set_fusion(f)
         optimizer.skip_update = True
         self._fusion_cfg = f

@@ -152,6 +152,10 @@ int dpt_allreduce_oneshot(dpt_comm* c, void* const* in, float* out, long long n,
  * mapping of the multicast object bound to every rank's buffer (parallel/nvls.py sets it up). */
 int dpt_allreduce_nvls(dpt_comm* c, void* mc, long long n, float scale, const float* inv_scale,
                        void* const* found_inf, int ctas, void* stream);
+int dpt_allreduce_nvls_sgd(dpt_comm* c, void* mc, long long n, float scale, const float* inv_scale,
+                           void* const* found_inf, float* param_local, float* momentum,
+                           void* param_mc, void* shadow_mc, float lr, float mu, float wd,
+                           int nesterov, int ctas, void* stream);
 int dpt_broadcast(dpt_comm* c, void* const* bufs, long long bytes, int src, int ctas, void* stream);
 int dpt_barrier(dpt_comm* c, void* stream);
 

@@ -254,10 +254,12 @@ def _trainstep_worker(rank, world):
     from dpt_b200.parallel.ddp import DistributedDataParallel as OurDDP
     dev = torch.device("cuda", rank)
     shape = (32, 3, 32, 32)
-    for graph, fused, fp16_scaler in ((False, False, False), (True, False, False), (True, True, False),
-                                      (True, False, True)):
+    for graph, fused, fp16_scaler, algo in ((False, False, False, "twoshot"), (True, False, False, "twoshot"),
+                                            (True, True, False, "twoshot"), (True, False, True, "twoshot"),
+                                            (True, False, False, "nvls"), (True, True, False, "nvls")):
         torch.manual_seed(11 + rank)
-        model = OurDDP(build_model(dev, "resnet18", 10), device_ids=[rank], backend="native")
+        model = OurDDP(build_model(dev, "resnet18", 10), device_ids=[rank], backend="native",
+                       allreduce_algo=algo)
         opt = SGD(model.parameters(), lr=0.02, momentum=0.9, weight_decay=5e-4)
         if fused:
             assert model.enable_fused_sgd(opt)
@@ -272,12 +274,18 @@ def _trainstep_worker(rank, world):
             losses.append(step.read_loss(lag=0))
         torch.cuda.synchronize()
         model.comm.check_health()
-        assert losses[-1] < losses[0], (graph, fused, losses)
+        assert losses[-1] < losses[0], (graph, fused, algo, losses)
         cs = model.arena.param.double().sum().reshape(1)
         lo, hi = cs.clone(), cs.clone()
         dist.all_reduce(lo, op=dist.ReduceOp.MIN)
         dist.all_reduce(hi, op=dist.ReduceOp.MAX)
-        assert torch.equal(lo, hi), f"replicas diverged (graph={graph}, fused={fused})"
+        assert torch.equal(lo, hi), f"replicas diverged (graph={graph}, fused={fused}, algo={algo})"
+        shc = model.arena.shadow.double().sum().reshape(1)
+        lo2, hi2 = shc.clone(), shc.clone()
+        dist.all_reduce(lo2, op=dist.ReduceOp.MIN)
+        dist.all_reduce(hi2, op=dist.ReduceOp.MAX)
+        assert torch.equal(lo2, hi2), f"bf16 shadows diverged (fused={fused}, algo={algo})"
+        assert torch.equal(model.arena.shadow, model.arena.param.bfloat16()), "shadow != bf16(param)"
         sh = model.arena.shadow.float().sum().reshape(1)
         assert torch.isfinite(sh).all()
         if fp16_scaler:
