@@ -342,14 +342,20 @@ def run_reference(a):
     device = torch.device(f"cuda:{local}")
     ref.set_seed(42, rank)
     torch.backends.cudnn.benchmark = True            # train_ddp.py:329
-    model = ref.build_model(device)                   # torchvision resnet18(num_classes=10)
+    if a.arch == "resnet18":
+        model = ref.build_model(device)               # torchvision resnet18(num_classes=10)
+    else:
+        # the reference only knows resnet18 (train_ddp.py:154); other BASELINE.json configs use
+        # the same torchvision family through the reference's own loop
+        import torchvision
+        model = getattr(torchvision.models, a.arch)(num_classes=a.num_classes).to(device)
     model = ref.maybe_wrap_ddp(model, device, local)  # torch DDP + NCCL when world > 1
     criterion = nn.CrossEntropyLoss().to(device)
     optimizer = optim.SGD(model.parameters(), lr=0.1, momentum=0.9, weight_decay=5e-4)
     scaler = torch.cuda.amp.GradScaler(enabled=True)  # --amp path (fp16 autocast + GradScaler)
     args = types.SimpleNamespace(amp=True, print_freq=10 ** 9)
     shape = (a.batch_size, 3, a.image_size, a.image_size)
-    batches = make_host_batches(8, shape, 10, seed=1234 + rank)
+    batches = make_host_batches(8, shape, a.num_classes, seed=1234 + rank)
 
     class Loader:
         """Stands in for the CIFAR DataLoader (no dataset files offline): yields pinned host
@@ -388,7 +394,7 @@ def run_reference(a):
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "fp16 autocast + GradScaler (the reference's --amp path)", "data": "synthetic",
         "impl": "reference",
-        "config": {"model": "torchvision resnet18(num_classes=10)", "global_batch": gb,
+        "config": {"model": f"torchvision {a.arch}(num_classes={a.num_classes})", "global_batch": gb,
                    "per_gpu_batch": a.batch_size, "seq_len": None, "parallelism": f"dp{world}",
                    "path": "reference train_ddp.train_one_epoch (unmodified) with a synthetic pinned "
                            "loader; torch DDP + NCCL when world > 1; cudnn.benchmark=True",

@@ -878,6 +878,39 @@ nchw_to_nhwc_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y, 
     }
 }
 
+// ------------------------------------------------------------------------------------ augment
+// CIFAR training transform on the device: RandomCrop(S, padding) + RandomHorizontalFlip +
+// ToTensor + Normalize in one pass (reference train_ddp.py:91-96 does this per sample on the
+// host with PIL).  in: uint8 [N, C, S, S]; params: int32 [N, 3] = (dy, dx, flip) with dy, dx in
+// [0, 2*pad]; out: fp32 [N, C, S, S].
+__global__ void __launch_bounds__(kEwThreads)
+augment_crop_flip_norm_kernel(const uint8_t* __restrict__ in, const int* __restrict__ params,
+                              float* __restrict__ out, int N, int C, int S, int pad, float m0,
+                              float m1, float m2, float is0, float is1, float is2) {
+    pdl_launch_dependents();
+    pdl_wait();
+    const long long total = static_cast<long long>(N) * C * S * S;
+    for (long long i = static_cast<long long>(blockIdx.x) * kEwThreads + threadIdx.x; i < total;
+         i += static_cast<long long>(gridDim.x) * kEwThreads) {
+        const int w = static_cast<int>(i % S);
+        long long t = i / S;
+        const int h = static_cast<int>(t % S);
+        t /= S;
+        const int c = static_cast<int>(t % C);
+        const int n = static_cast<int>(t / C);
+        const int dy = params[n * 3 + 0], dx = params[n * 3 + 1], flip = params[n * 3 + 2];
+        const int ws = flip ? (S - 1 - w) : w;
+        const int hs = h + dy - pad, wsrc = ws + dx - pad;
+        float v = 0.f;
+        if (hs >= 0 && hs < S && wsrc >= 0 && wsrc < S)
+            v = static_cast<float>(in[((static_cast<long long>(n) * C + c) * S + hs) * S + wsrc]) *
+                (1.f / 255.f);
+        const float mean = c == 0 ? m0 : (c == 1 ? m1 : m2);
+        const float istd = c == 0 ? is0 : (c == 1 ? is1 : is2);
+        out[i] = (v - mean) * istd;
+    }
+}
+
 }  // namespace dpt
 
 using namespace dpt;
@@ -1187,5 +1220,17 @@ extern "C" int dpt_bn_fwd_train_noalloc(const void* x, const float* gamma, const
         static_cast<const bf16x8*>(x), sum, sq, gamma, beta, static_cast<const bf16x8*>(residual),
         static_cast<bf16x8*>(y), save_mean, save_invstd, running_mean, running_var,
         num_batches_tracked, nvec, C / 8, 1.f / static_cast<float>(M), unbias, momentum, eps, relu);
+    DPT_CHECK_LAUNCH();
+}
+
+extern "C" int dpt_augment_crop_flip_norm(const void* in_u8, const int* params, float* out, int N,
+                                          int C, int S, int pad, const float* mean3,
+                                          const float* std3, void* stream) {
+    if (C > 3 || C < 1) return DPT_ERR_SHAPE;
+    const long long total = static_cast<long long>(N) * C * S * S;
+    ew_pdl_gate();
+    launch_pdl(augment_crop_flip_norm_kernel, dim3(ew_grid(total, 1)), dim3(kEwThreads), 0,
+               static_cast<cudaStream_t>(stream), static_cast<const uint8_t*>(in_u8), params, out, N,
+               C, S, pad, mean3[0], mean3[1], mean3[2], 1.f / std3[0], 1.f / std3[1], 1.f / std3[2]);
     DPT_CHECK_LAUNCH();
 }

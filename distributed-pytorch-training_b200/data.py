@@ -164,3 +164,21 @@ def get_dataloaders(args, rank: int, world_size: int):
     val_loader = DataLoader(test_ds, batch_size=args.batch_size, shuffle=False,
                             num_workers=args.workers, pin_memory=pin, drop_last=False)
     return train_loader, val_loader, sampler
+
+
+class GpuAugment:
+    """RandomCrop(32, padding=4) + RandomHorizontalFlip + Normalize on the device for a uint8
+    batch (one kernel per batch instead of PIL per sample)."""
+
+    def __init__(self, pad: int = 4, mean=CIFAR_MEAN, std=CIFAR_STD, seed: int = 0) -> None:
+        self.pad, self.mean, self.std = pad, mean, std
+        self.gen = torch.Generator().manual_seed(seed)
+
+    def __call__(self, images_u8: torch.Tensor) -> torch.Tensor:
+        from .ops import functional as Fn
+        n = images_u8.shape[0]
+        p = torch.stack([torch.randint(0, 2 * self.pad + 1, (n,), generator=self.gen),
+                         torch.randint(0, 2 * self.pad + 1, (n,), generator=self.gen),
+                         torch.randint(0, 2, (n,), generator=self.gen)], dim=1).to(torch.int32)
+        return Fn.augment_crop_flip_norm(images_u8, p.to(images_u8.device, non_blocking=True),
+                                         self.mean, self.std, self.pad)

@@ -43,6 +43,7 @@ _SIGS = {
     "dpt_cross_entropy": [vp, vp, vp, vp, vp, vp, i32, i32, vp],
     "dpt_im2col_nchw_f32": [vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp],
     "dpt_pad_rows_f32_to_bf16": [vp, vp, i32, i32, i32, vp],
+    "dpt_augment_crop_flip_norm": [vp, vp, vp, i32, i32, i32, i32, vp, vp, vp],
     "dpt_nchw_f32_to_nhwc_bf16": [vp, vp, i32, i32, i32, i32, vp],
     "dpt_amp_unscale": [vp, i64, vp, vp, vp],
     "dpt_amp_update_scale": [vp, vp, vp, vp, f32, f32, i32, vp],

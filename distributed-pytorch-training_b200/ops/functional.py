@@ -274,3 +274,18 @@ def amp_update_scale(scale, growth_tracker, found_inf, inv_scale_out, growth_fac
 def cast_to_bf16(src, dst):
     call("dpt_cast_f32_to_bf16", ptr(src), ptr(dst), src.numel(), stream())
     count()
+
+
+def augment_crop_flip_norm(images_u8, params, mean, std, pad=4, *, out=None):
+    """Device-side CIFAR train transform.  images_u8: uint8 [N,C,S,S] (device); params: int32
+    [N,3] = (dy, dx, flip) on the device; mean/std: sequences of C floats."""
+    import ctypes
+    N, C_, S, _ = images_u8.shape
+    if out is None:
+        out = torch.empty((N, C_, S, S), device=images_u8.device, dtype=torch.float32)
+    m = (ctypes.c_float * 3)(*(list(mean) + [0.0] * 3)[:3])
+    sd = (ctypes.c_float * 3)(*(list(std) + [1.0] * 3)[:3])
+    call("dpt_augment_crop_flip_norm", ptr(images_u8), ptr(params), ptr(out), N, C_, S, pad,
+         ctypes.cast(m, ctypes.c_void_p), ctypes.cast(sd, ctypes.c_void_p), stream())
+    count()
+    return out

@@ -108,6 +108,10 @@ int dpt_cross_entropy(const float* logits, const long long* target, float* loss,
 int dpt_im2col_nchw_f32(const float* x, void* out, int N, int C, int H, int W, int R, int S,
                         int stride, int pad, int ldk, void* stream);
 int dpt_pad_rows_f32_to_bf16(const float* src, void* dst, int rows, int cols, int ld, void* stream);
+/* RandomCrop(pad) + RandomHorizontalFlip + ToTensor + Normalize on the device (the reference does
+ * it per sample on the host, train_ddp.py:91-96); mean3/std3 are HOST pointers to 3 floats. */
+int dpt_augment_crop_flip_norm(const void* in_u8, const int* params, float* out, int N, int C, int S,
+                               int pad, const float* mean3, const float* std3, void* stream);
 int dpt_nchw_f32_to_nhwc_bf16(const float* x, void* y, int N, int C, int H, int W, void* stream);
 
 /* ---- flat-arena optimizer / AMP (csrc/ops/optim.cu) ------------------------------------------

@@ -326,3 +326,24 @@ def test_bn_bwd_fused_single_launch(shape, relu, two):
     _close(dx, ref_dx, 4e-2, "dx")   # bf16 output, sums reduced in a different order
     _close(dg, ref_dg, 5e-3, "dgamma")
     _close(db, ref_db, 5e-3, "dbeta")
+
+
+def test_gpu_augment_matches_host_transform():
+    Fn = _F()
+    from dpt_b200.data import CIFAR_MEAN, CIFAR_STD
+    N = 16
+    img = torch.randint(0, 256, (N, 3, 32, 32), dtype=torch.uint8)
+    params = torch.stack([torch.randint(0, 9, (N,)), torch.randint(0, 9, (N,)),
+                          torch.randint(0, 2, (N,))], dim=1).to(torch.int32)
+    out = Fn.augment_crop_flip_norm(img.cuda(), params.cuda(), CIFAR_MEAN, CIFAR_STD, 4)
+    mean = torch.tensor(CIFAR_MEAN).view(3, 1, 1)
+    std = torch.tensor(CIFAR_STD).view(3, 1, 1)
+    for n in range(N):
+        dy, dx, flip = params[n].tolist()
+        padded = torch.zeros(3, 40, 40, dtype=torch.uint8)
+        padded[:, 4:36, 4:36] = img[n]
+        crop = padded[:, dy:dy + 32, dx:dx + 32]
+        if flip:
+            crop = crop.flip(2)
+        ref = (crop.float() / 255.0 - mean) / std
+        assert torch.allclose(out[n].cpu(), ref, atol=1e-5), n
