@@ -69,10 +69,11 @@ class Reducer {
     void set_enabled(bool on) { enabled_ = on; }  // no_sync()
     // NVLS: base of this rank's multicast mapping of the gradient arena; buckets of at least
     // `min_bytes` use the multimem kernel (unless the fused-SGD epilogue is active).
-    void set_nvls(uintptr_t mc_grad_base, int64_t min_bytes, int rank) {
+    void set_nvls(uintptr_t mc_grad_base, int64_t min_bytes, int rank, bool with_fused_sgd) {
         nvls_mc_ = mc_grad_base;
         nvls_min_bytes_ = min_bytes;
         rank_ = rank;
+        nvls_with_fusion_ = with_fused_sgd;
     }
 
     void prepare_for_backward(uintptr_t compute_stream);
@@ -113,6 +114,7 @@ class Reducer {
     uintptr_t nvls_mc_ = 0;
     int64_t nvls_min_bytes_ = 0;
     int rank_ = 0;
+    bool nvls_with_fusion_ = false;
 };
 
 }  // namespace dptr

@@ -230,7 +230,7 @@ class DistributedDataParallel(nn.Module):
                 # measured crossover: the multimem kernel wins from ~1 MB up (profiles/README.md)
                 self.reducer.set_nvls(self.arena.grad_buf.mc_ptr,
                                       0 if allreduce_algo == "nvls" else int(nvls_min_bytes),
-                                      self.rank)
+                                      self.rank, allreduce_algo == "nvls")
             E.register_hooks(self.reducer, list(self.arena.order),
                              [self.arena.grad_view(p) for p in self.arena.order])
         else:
