@@ -183,7 +183,14 @@ class ResNet(nn.Module):
             eng = self.engine_for(x.shape, self.training)
             self._last_engine = eng
             if self.training and torch.is_grad_enabled():
-                return _EngineFn.apply(x, self.fc.bias, eng)
+                # autograd needs one differentiable input to call backward; a private dummy is
+                # used (NOT a parameter: post-accumulate-grad hooks fire even for None
+                # gradients, which would report a parameter to the reducer twice)
+                anchor = self.__dict__.get("_anchor")
+                if anchor is None or anchor.device != x.device:
+                    anchor = torch.zeros((), device=x.device, requires_grad=True)
+                    self.__dict__["_anchor"] = anchor
+                return _EngineFn.apply(x, anchor, eng)
             return eng.forward(x)
         return self._forward_torch(x)
 

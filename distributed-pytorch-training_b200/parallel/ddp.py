@@ -512,6 +512,7 @@ class DistributedDataParallel(nn.Module):
 
 
 def maybe_wrap_ddp(model, device, local_rank, **kwargs):
+    kwargs = {k: v for k, v in kwargs.items() if v is not None or k == "bucket_cap_mb"}
     """Reference train_ddp.py:303-311: wrap only when distributed."""
     from ..runtime import is_distributed
     if is_distributed() and dist.is_initialized():

@@ -37,9 +37,17 @@ def main(argv=None):
     train_loader, val_loader, train_sampler = get_dataloaders(args, rank, world_size)
 
     model = build_model(device, args.arch, args.num_classes)
+    # per-bucket event timing cannot be recorded inside a captured CUDA graph: with --cuda-graph
+    # the profiler only reports the (event-timed) step time
+    bucket_profile = args.profile_sync and not args.cuda_graph
+    if args.profile_sync and args.cuda_graph and rank == 0:
+        print("[grad-sync] --cuda-graph: per-bucket timing disabled (run without --cuda-graph "
+              "to profile gradient sync)")
+    algo = {"auto": "auto", "oneshot": "twoshot", "twoshot": "twoshot", "nvls": "nvls"}[args.allreduce_algo]
     model = maybe_wrap_ddp(model, device, local_rank, backend=args.backend,
-                           bucket_cap_mb=args.bucket_cap_mb, profile=args.profile_sync,
-                           comm_timeout=args.comm_timeout)
+                           bucket_cap_mb=args.bucket_cap_mb if args.bucket_cap_mb != 25.0 else None,
+                           profile=bucket_profile, comm_timeout=args.comm_timeout,
+                           allreduce_algo=algo)
     ddp = model if isinstance(model, DistributedDataParallel) else None
 
     criterion = CrossEntropyLoss().to(device)

@@ -58,6 +58,11 @@ def train_one_epoch(epoch, model, train_loader, optimizer, criterion, device, ar
         train_step.metrics.zero_()
     start_epoch = time.time()
     accum_time, accum_samples = 0.0, 0
+    # On CUDA the steps are asynchronous (no per-step host sync), so the window's step time is
+    # taken from CUDA events around each step: device time, loader wait excluded — the same
+    # quantity the reference obtains from time.time() + .item() (train_ddp.py:196,217,224).
+    cuda = device.type == "cuda"
+    win_events: list = []
     max_steps = getattr(args, "steps", 0) or 0
     n_steps = len(train_loader) if not max_steps else min(max_steps, len(train_loader))
     for i, (images, targets) in enumerate(train_loader):
@@ -65,6 +70,10 @@ def train_one_epoch(epoch, model, train_loader, optimizer, criterion, device, ar
             break
         batch_start = time.time()
         bsz = images.size(0)
+        if cuda:
+            ev_s = torch.cuda.Event(enable_timing=True)
+            ev_e = torch.cuda.Event(enable_timing=True)
+            ev_s.record()
         fast = train_step is not None and tuple(images.shape) == train_step.batch_shape
         if profiler is not None and profiler.should_sample():
             profiler.step_begin()
@@ -94,6 +103,9 @@ def train_one_epoch(epoch, model, train_loader, optimizer, criterion, device, ar
                 acc[2] += bsz
         if profiler is not None and profiler._ev0 is not None:
             profiler.step_end()
+        if cuda:
+            ev_e.record()
+            win_events.append((ev_s, ev_e))
         printing = rank == 0 and (i + 1) % args.print_freq == 0
         if printing:
             tot = acc.clone()
@@ -103,10 +115,15 @@ def train_one_epoch(epoch, model, train_loader, optimizer, criterion, device, ar
         accum_time += time.time() - batch_start
         accum_samples += bsz * world_size
         if printing:
+            if cuda and win_events:
+                accum_time = sum(a.elapsed_time(b) for a, b in win_events) * 1e-3
             throughput = accum_samples / accum_time if accum_time > 0 else 0.0
             print(M.step_line(epoch, i + 1, n_steps, l / max(t, 1.0), 100.0 * c / max(t, 1.0),
                               throughput))
             accum_time, accum_samples = 0.0, 0
+            win_events = []
+        elif cuda and len(win_events) > 4096:
+            win_events = win_events[-4096:]
     tot = acc.clone()
     if train_step is not None:
         tot += train_step.metrics

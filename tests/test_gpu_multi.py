@@ -385,3 +385,46 @@ def _nvls_worker(rank, world):
 @needs2
 def test_nvls_multicast_allreduce():
     _run(_nvls_worker)
+
+
+# --------------------------------------------------------------------------------- compat loop
+def _compat_loop_worker(rank, world):
+    """Reference-style loop (autocast -> model(x) -> criterion -> backward -> step) through the
+    native engine under the native DDP wrapper: replicas stay identical, loss goes down."""
+    import torch.distributed as dist
+    from dpt_b200.models.resnet import build_model
+    from dpt_b200.ops.loss import CrossEntropyLoss
+    from dpt_b200.optim import SGD
+    from dpt_b200.parallel.ddp import DistributedDataParallel as OurDDP
+    dev = torch.device("cuda", rank)
+    torch.manual_seed(5 + rank)
+    model = OurDDP(build_model(dev, "resnet18", 10), device_ids=[rank], backend="native", profile=True)
+    opt = SGD(model.parameters(), lr=0.02, momentum=0.9, weight_decay=5e-4)
+    crit = CrossEntropyLoss()
+    g = torch.Generator(device=dev).manual_seed(rank)
+    x = torch.randn(32, 3, 32, 32, device=dev, generator=g)
+    t = torch.randint(0, 10, (32,), device=dev, generator=g)
+    losses = []
+    for _ in range(6):
+        opt.zero_grad(set_to_none=True)
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            loss = crit(model(x), t)
+        loss.backward()
+        opt.step()
+        losses.append(loss.item())
+    torch.cuda.synchronize()
+    model.comm.check_health()
+    assert losses[-1] < losses[0], losses
+    cs = model.arena.param.double().sum().reshape(1)
+    lo, hi = cs.clone(), cs.clone()
+    dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+    dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+    assert torch.equal(lo, hi), "replicas diverged in the autograd-bridge path"
+    tm = model.sync_timings()
+    assert len(tm["buckets"]) == len(model.plans)
+    model.shutdown()
+
+
+@needs2
+def test_reference_style_loop_under_native_ddp():
+    _run(_compat_loop_worker, world=2)
