@@ -21,6 +21,7 @@
 // Replaces torch DDP's Reducer -> ProcessGroupNCCL allreduce (reference train_ddp.py:305-310,
 // 207/213), GradScaler's unscale_ + found_inf.item() (:208) and, in F2, optimizer.step() (:214).
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 
 #include <cstdint>
@@ -104,7 +105,18 @@ struct Epilogue {
     // NVLS + fused SGD: multicast mappings of the param / shadow arenas
     float* param_mc;
     __nv_bfloat16* shadow_mc;
+    int shadow_f16;  // 16-bit shadow format: 0 = bf16, 1 = fp16
 };
+
+static int g_comm_shadow_f16 = 0;
+__device__ __forceinline__ uint32_t comm_pack_lp2(float a, float b, int f16) {
+    if (f16) {
+        __half2 h = __floats2half2_rn(a, b);
+        return *reinterpret_cast<uint32_t*>(&h);
+    }
+    __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&h);
+}
 
 
 // grads: symmetric buffers (float), n4 = number of float4.  In place.
@@ -173,11 +185,9 @@ allreduce_twoshot_kernel(CommCtx c, Peers grads, long long n4, Epilogue ep) {
                 }
                 reinterpret_cast<float4*>(ep.momentum)[i] = make_float4(ma[0], ma[1], ma[2], ma[3]);
                 const float4 np = make_float4(pa[0], pa[1], pa[2], pa[3]);
-                __nv_bfloat162 b0 = __floats2bfloat162_rn(pa[0], pa[1]);
-                __nv_bfloat162 b1 = __floats2bfloat162_rn(pa[2], pa[3]);
                 uint2 pk;
-                pk.x = *reinterpret_cast<uint32_t*>(&b0);
-                pk.y = *reinterpret_cast<uint32_t*>(&b1);
+                pk.x = comm_pack_lp2(pa[0], pa[1], ep.shadow_f16);
+                pk.y = comm_pack_lp2(pa[2], pa[3], ep.shadow_f16);
 #pragma unroll
                 for (int p = 0; p < WORLD; ++p) {
                     st_stream(reinterpret_cast<float4*>(ep.param[p]) + i, np);
@@ -324,11 +334,9 @@ allreduce_nvls_kernel(CommCtx c, float* __restrict__ mc, long long n4, Epilogue 
                 reinterpret_cast<float4*>(ep.momentum)[i] = make_float4(ma[0], ma[1], ma[2], ma[3]);
                 multimem_st_f32x4(reinterpret_cast<float4*>(ep.param_mc) + i,
                                   make_float4(pa[0], pa[1], pa[2], pa[3]));
-                __nv_bfloat162 b0 = __floats2bfloat162_rn(pa[0], pa[1]);
-                __nv_bfloat162 b1 = __floats2bfloat162_rn(pa[2], pa[3]);
                 const unsigned long long pk =
-                    static_cast<unsigned long long>(*reinterpret_cast<uint32_t*>(&b0)) |
-                    (static_cast<unsigned long long>(*reinterpret_cast<uint32_t*>(&b1)) << 32);
+                    static_cast<unsigned long long>(comm_pack_lp2(pa[0], pa[1], ep.shadow_f16)) |
+                    (static_cast<unsigned long long>(comm_pack_lp2(pa[2], pa[3], ep.shadow_f16)) << 32);
                 multimem_st_b64(reinterpret_cast<uint2*>(ep.shadow_mc) + i, pk);
             }
         }
@@ -380,6 +388,11 @@ struct dpt_comm {
     uint32_t* err_host;  // pinned, mapped
     void* opened[kMaxWorld];
 };
+
+extern "C" int dpt_comm_set_lowp_dtype(int is_f16) {
+    dpt::g_comm_shadow_f16 = is_f16 ? 1 : 0;
+    return 0;
+}
 
 extern "C" int dpt_symm_alloc(size_t bytes, void** ptr, void* ipc_handle_64) {
     cudaError_t e = cudaMalloc(ptr, bytes);
@@ -453,6 +466,7 @@ static int clamp_ctas(int ctas, long long n4, int world) {
 static void fill_epilogue(Epilogue* ep, int world, float scale, const float* inv_scale,
                           void* const* found_inf) {
     memset(ep, 0, sizeof(*ep));
+    ep->shadow_f16 = g_comm_shadow_f16;
     ep->scale = scale;
     ep->inv_scale = inv_scale;
     if (found_inf != nullptr)

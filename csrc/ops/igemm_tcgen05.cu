@@ -26,6 +26,7 @@
 // torchvision's resnet18 dispatches to (reference train_ddp.py:153-156, 205-213).
 #include <cuda.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 
 #include <cstdint>
@@ -105,7 +106,7 @@ __device__ __forceinline__ float warp_colsum16(float (&v)[16], uint32_t lane) {
     return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 1);
 }
 
-template <int MODE, int BLOCK_N, int NSTAGES>
+template <int MODE, int BLOCK_N, int NSTAGES, bool F16>
 __global__ void __launch_bounds__(kNumThreads, 1)
 igemm_kernel(const __grid_constant__ IgemmMaps maps, const __grid_constant__ IgemmParams prm) {
     constexpr bool A_MN = (MODE == MODE_WGRAD);
@@ -113,7 +114,9 @@ igemm_kernel(const __grid_constant__ IgemmMaps maps, const __grid_constant__ Ige
     constexpr int kBStageBytes = BLOCK_N * kKBlk * 2;
     constexpr int kStageBytes = kAStageBytes + kBStageBytes;
     constexpr uint32_t kTmemCols = BLOCK_N < 32 ? 32 : BLOCK_N;
-    constexpr uint32_t kIdesc = make_idesc_bf16(kTileM, BLOCK_N, A_MN ? 1 : 0, B_MN ? 1 : 0);
+    // operand format field: 1 = BF16, 0 = F16 (bits 7-9 for A, 10-12 for B)
+    constexpr uint32_t kIdesc = make_idesc_bf16(kTileM, BLOCK_N, A_MN ? 1 : 0, B_MN ? 1 : 0) &
+                                (F16 ? ~((1u << 7) | (1u << 10)) : ~0u);
 
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     // SWIZZLE_128B needs 1024-byte aligned stage bases.
@@ -317,13 +320,18 @@ igemm_kernel(const __grid_constant__ IgemmMaps maps, const __grid_constant__ Ige
             if (row_ok) {
                 const long long off = row_off + koff_out + cbase;
                 if (prm.out_mode == OUT_BF16) {
-                    __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(prm.out) + off;
+                    uint16_t* o = reinterpret_cast<uint16_t*>(prm.out) + off;
                     if (full && vec_ok) {
                         uint32_t pk[8];
 #pragma unroll
                         for (int i = 0; i < 8; ++i) {
-                            __nv_bfloat162 h = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
-                            pk[i] = *reinterpret_cast<uint32_t*>(&h);
+                            if (F16) {
+                                __half2 h = __floats2half2_rn(f[2 * i], f[2 * i + 1]);
+                                pk[i] = *reinterpret_cast<uint32_t*>(&h);
+                            } else {
+                                __nv_bfloat162 h = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+                                pk[i] = *reinterpret_cast<uint32_t*>(&h);
+                            }
                         }
                         uint4* o4 = reinterpret_cast<uint4*>(o);
                         o4[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
@@ -331,7 +339,15 @@ igemm_kernel(const __grid_constant__ IgemmMaps maps, const __grid_constant__ Ige
                     } else {
 #pragma unroll
                         for (int i = 0; i < 16; ++i)
-                            if (cbase + i < prm.n_total) o[i] = __float2bfloat16_rn(f[i]);
+                            if (cbase + i < prm.n_total) {
+                                if (F16) {
+                                    const __half h = __float2half_rn(f[i]);
+                                    o[i] = *reinterpret_cast<const uint16_t*>(&h);
+                                } else {
+                                    const __nv_bfloat16 h = __float2bfloat16_rn(f[i]);
+                                    o[i] = *reinterpret_cast<const uint16_t*>(&h);
+                                }
+                            }
                     }
                 } else if (prm.out_mode == OUT_F32) {
                     float* o = reinterpret_cast<float*>(prm.out) + off;
@@ -436,7 +452,10 @@ static PFN_encodeTiled get_encode() {
     return fn;
 }
 
-// bf16 tensor map, up to 4-D, inner box = 64 elements (128 B) with SWIZZLE_128B.
+// Element type of the 16-bit operands (0 = bf16, 1 = fp16), set through dpt_set_lowp_dtype().
+static int g_lowp_f16 = 0;
+
+// 16-bit tensor map, up to 4-D, inner box = 64 elements (128 B) with SWIZZLE_128B.
 // dims/strides are in elements; strides[i] is the stride of dimension i+1.
 static int make_tmap(CUtensorMap* m, const void* base, int rank, const long long* dims,
                      const long long* strides, const int* box) {
@@ -451,7 +470,7 @@ static int make_tmap(CUtensorMap* m, const void* base, int rank, const long long
         bdim[i] = static_cast<cuuint32_t>(box[i]);
     }
     for (int i = 0; i + 1 < rank; ++i) gstr[i] = static_cast<cuuint64_t>(strides[i]) * 2;
-    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(base), gdim, gstr,
+    CUresult r = enc(m, g_lowp_f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(base), gdim, gstr,
                      bdim, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                      CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
@@ -491,13 +510,13 @@ static int launch_cfg(const IgemmMaps& maps, const IgemmParams& prm, dim3 grid, 
     constexpr int kBStageBytes = BLOCK_N * kKBlk * 2;
     constexpr int NST = (BLOCK_N == 128) ? 6 : 8;
     const int smem = NST * (kAStageBytes + kBStageBytes) + 1024;
-    auto kern = igemm_kernel<MODE, BLOCK_N, NST>;
-    static bool attr_done = false;
-    if (!attr_done) {
+    auto kern = g_lowp_f16 ? igemm_kernel<MODE, BLOCK_N, NST, true> : igemm_kernel<MODE, BLOCK_N, NST, false>;
+    static bool attr_done[2] = {false, false};
+    if (!attr_done[g_lowp_f16]) {
         cudaError_t e =
             cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return int(e);
-        attr_done = true;
+        attr_done[g_lowp_f16] = true;
     }
     {
         static int igemm_pdl = -1;
@@ -589,6 +608,12 @@ static void fprop_taps(TapBuilder* tb, int H, int W, int P, int Q, int Cin, int 
 }  // namespace dpt
 
 using namespace dpt;
+
+// called by dpt_set_lowp_dtype (norm_pool_loss.cu) so that every translation unit agrees
+extern "C" int dpt_igemm_set_lowp_dtype(int is_f16) {
+    dpt::g_lowp_f16 = is_f16 ? 1 : 0;
+    return 0;
+}
 
 extern "C" int dpt_conv_fprop(const void* x, const void* w, void* y, int N, int H, int W, int Cin,
                               int Cout, int R, int S, int stride, int pad, float* stat_sum,

@@ -7,6 +7,7 @@
 // autocast weight casts (train_ddp.py:204), GradScaler's unscale/inf-check
 // (torch/amp/grad_scaler.py:292-298) and its host-synchronising found_inf.item() (:371).
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 
 #include <cstdint>
@@ -15,6 +16,26 @@
 #include "../common/ptx.cuh"
 
 namespace dpt {
+
+static int g_shadow_f16 = 0;  // element type of the 16-bit shadow weights (dpt_set_lowp_dtype)
+
+// pack 2 floats into the 16-bit shadow format
+__device__ __forceinline__ uint32_t pack_lp2(float a, float b, int f16) {
+    if (f16) {
+        __half2 h = __floats2half2_rn(a, b);
+        return *reinterpret_cast<uint32_t*>(&h);
+    }
+    __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&h);
+}
+__device__ __forceinline__ uint16_t pack_lp1(float a, int f16) {
+    if (f16) {
+        __half h = __float2half_rn(a);
+        return *reinterpret_cast<uint16_t*>(&h);
+    }
+    __nv_bfloat16 h = __float2bfloat16_rn(a);
+    return *reinterpret_cast<uint16_t*>(&h);
+}
 
 __device__ __forceinline__ bool finite4(float4 v) {
     return isfinite(v.x) && isfinite(v.y) && isfinite(v.z) && isfinite(v.w);
@@ -77,9 +98,9 @@ __global__ void amp_update_scale_kernel(float* scale, int* growth_tracker, float
 // whole update is skipped when *found_inf != 0, and the bf16 shadow copy is refreshed.
 __global__ void __launch_bounds__(256)
 sgd_flat_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
-                __nv_bfloat16* __restrict__ shadow, long long n, float lr, float momentum,
+                uint16_t* __restrict__ shadow, long long n, float lr, float momentum,
                 float dampening, float wd, int nesterov, const float* __restrict__ grad_scale,
-                const float* __restrict__ found_inf) {
+                const float* __restrict__ found_inf, int shadow_f16) {
     pdl_launch_dependents();
     pdl_wait();
     if (found_inf != nullptr && *found_inf > 0.f) return;
@@ -105,11 +126,9 @@ sgd_flat_kernel(float* __restrict__ p, const float* __restrict__ g, float* __res
         reinterpret_cast<float4*>(p)[i] = make_float4(pa[0], pa[1], pa[2], pa[3]);
         reinterpret_cast<float4*>(m)[i] = make_float4(ma[0], ma[1], ma[2], ma[3]);
         if (shadow != nullptr) {
-            __nv_bfloat162 lo = __floats2bfloat162_rn(pa[0], pa[1]);
-            __nv_bfloat162 hi = __floats2bfloat162_rn(pa[2], pa[3]);
             uint2 pk;
-            pk.x = *reinterpret_cast<uint32_t*>(&lo);
-            pk.y = *reinterpret_cast<uint32_t*>(&hi);
+            pk.x = pack_lp2(pa[0], pa[1], shadow_f16);
+            pk.y = pack_lp2(pa[2], pa[3], shadow_f16);
             reinterpret_cast<uint2*>(shadow)[i] = pk;
         }
     }
@@ -121,7 +140,7 @@ sgd_flat_kernel(float* __restrict__ p, const float* __restrict__ g, float* __res
             d = nesterov ? fmaf(momentum, m[i], d) : m[i];
         }
         p[i] = fmaf(-lr, d, p[i]);
-        if (shadow != nullptr) shadow[i] = __float2bfloat16_rn(p[i]);
+        if (shadow != nullptr) shadow[i] = pack_lp1(p[i], shadow_f16);
     }
 }
 
@@ -129,10 +148,10 @@ sgd_flat_kernel(float* __restrict__ p, const float* __restrict__ g, float* __res
 // (each thread reads the pre-increment value + 1; the increment happens in a tail kernel).
 __global__ void __launch_bounds__(256)
 adam_flat_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
-                 float* __restrict__ v, __nv_bfloat16* __restrict__ shadow, long long n, float lr,
+                 float* __restrict__ v, uint16_t* __restrict__ shadow, long long n, float lr,
                  float beta1, float beta2, float eps, float wd, int decoupled,
                  const int* __restrict__ step_count, const float* __restrict__ grad_scale,
-                 const float* __restrict__ found_inf) {
+                 const float* __restrict__ found_inf, int shadow_f16) {
     pdl_launch_dependents();
     pdl_wait();
     if (found_inf != nullptr && *found_inf > 0.f) return;
@@ -156,7 +175,7 @@ adam_flat_kernel(float* __restrict__ p, const float* __restrict__ g, float* __re
         const float denom = sqrtf(vv) * inv_sqrt_bc2 + eps;
         pv -= step_size * mv / denom;
         p[i] = pv;
-        if (shadow != nullptr) shadow[i] = __float2bfloat16_rn(pv);
+        if (shadow != nullptr) shadow[i] = pack_lp1(pv, shadow_f16);
     }
 }
 
@@ -168,12 +187,13 @@ __global__ void step_inc_kernel(int* step_count, const float* found_inf) {
 }
 
 __global__ void __launch_bounds__(256)
-cast_f32_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, long long n) {
+cast_f32_bf16_kernel(const float* __restrict__ src, uint16_t* __restrict__ dst, long long n,
+                     int f16) {
     pdl_launch_dependents();
     pdl_wait();
     for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
          i += static_cast<long long>(gridDim.x) * blockDim.x)
-        dst[i] = __float2bfloat16_rn(src[i]);
+        dst[i] = pack_lp1(src[i], f16);
 }
 
 static inline int flat_grid(long long n) {
@@ -207,8 +227,8 @@ extern "C" int dpt_sgd_flat(float* p, const float* g, float* m, void* shadow, lo
                             float momentum, float dampening, float wd, int nesterov,
                             const float* grad_scale, const float* found_inf, void* stream) {
     launch_pdl(sgd_flat_kernel, dim3(flat_grid(n)), dim3(256), 0, static_cast<cudaStream_t>(stream), 
-        p, g, m, static_cast<__nv_bfloat16*>(shadow), n, lr, momentum, dampening, wd, nesterov,
-        grad_scale, found_inf);
+        p, g, m, static_cast<uint16_t*>(shadow), n, lr, momentum, dampening, wd, nesterov,
+        grad_scale, found_inf, g_shadow_f16);
     return static_cast<int>(cudaGetLastError());
 }
 
@@ -217,21 +237,26 @@ extern "C" int dpt_adam_flat(float* p, const float* g, float* m, float* v, void*
                              int* step_count, const float* grad_scale, const float* found_inf,
                              void* stream) {
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    launch_pdl(adam_flat_kernel, dim3(flat_grid(n)), dim3(256), 0, st, p, g, m, v, static_cast<__nv_bfloat16*>(shadow),
+    launch_pdl(adam_flat_kernel, dim3(flat_grid(n)), dim3(256), 0, st, p, g, m, v, static_cast<uint16_t*>(shadow),
                                                    n, lr, beta1, beta2, eps, wd, decoupled,
-                                                   step_count, grad_scale, found_inf);
+                                                   step_count, grad_scale, found_inf, g_shadow_f16);
     launch_pdl(step_inc_kernel, dim3(1), dim3(1), 0, st, step_count, found_inf);
     return static_cast<int>(cudaGetLastError());
 }
 
 extern "C" int dpt_cast_f32_to_bf16(const float* src, void* dst, long long n, void* stream) {
     launch_pdl(cast_f32_bf16_kernel, dim3(flat_grid(n * 4)), dim3(256), 0, static_cast<cudaStream_t>(stream), 
-        src, static_cast<__nv_bfloat16*>(dst), n);
+        src, static_cast<uint16_t*>(dst), n, g_shadow_f16);
     return static_cast<int>(cudaGetLastError());
 }
 
 // The next kernel launched through this library follows a cross-stream event wait: launch it
 // without the programmatic-dependent-launch attribute (see csrc/common/ptx.cuh).
+extern "C" int dpt_optim_set_lowp_dtype(int is_f16) {
+    dpt::g_shadow_f16 = is_f16 ? 1 : 0;
+    return 0;
+}
+
 extern "C" int dpt_pdl_skip_next() {
     dpt::pdl_skip_flag() = 1;
     return 0;

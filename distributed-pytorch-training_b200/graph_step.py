@@ -23,8 +23,9 @@ from .parallel.ddp import DistributedDataParallel
 
 class TrainStep:
     def __init__(self, model, optimizer, scaler=None, *, batch_shape, cuda_graph: bool = True,
-                 warmup: int = 2, lazy_buffer_sync: bool = True) -> None:
+                 warmup: int = 2, lazy_buffer_sync: bool = True, dtype=torch.bfloat16) -> None:
         self.lazy_buffer_sync = lazy_buffer_sync
+        self.dtype = dtype
         self.ddp = model if isinstance(model, DistributedDataParallel) else None
         self.net = model.module if self.ddp is not None else model
         if not isinstance(self.net, ResNet):
@@ -47,7 +48,10 @@ class TrainStep:
         self.dlogits = torch.zeros((B, K), device=dev, dtype=torch.float32)
         self.metrics = torch.zeros(3, device=dev, dtype=torch.float64)
         self.net.train()
-        self.eng = self.net.engine_for(self.batch_shape, True)
+        from .ops import functional as _Fn
+        _Fn.set_lowp_dtype(dtype)
+        self.arena.set_shadow_dtype(dtype)
+        self.eng = self.net.engine_for(self.batch_shape, True, dtype)
         self.fused_scaler = False
         if self.scaler is not None:
             self.scaler._lazy_init(dev)
@@ -70,6 +74,7 @@ class TrainStep:
     def _body(self) -> None:
         Fn = self.Fn
         ddp = self.ddp
+        Fn.set_lowp_dtype(self.dtype)
         if ddp is not None:
             ddp.sync_buffers(lazy=self.lazy_buffer_sync)
             ddp.prepare_for_backward()

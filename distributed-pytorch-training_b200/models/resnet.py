@@ -168,13 +168,19 @@ class ResNet(nn.Module):
         if self.native == "always":
             return True
         return (torch.is_autocast_enabled("cuda")
-                and torch.get_autocast_dtype("cuda") == torch.bfloat16)
+                and torch.get_autocast_dtype("cuda") in (torch.bfloat16, torch.float16))
 
-    def engine_for(self, shape, training: bool):
-        key = (tuple(shape), bool(training))
+    def _native_dtype(self):
+        if torch.is_autocast_enabled("cuda") and torch.get_autocast_dtype("cuda") == torch.float16:
+            return torch.float16
+        return getattr(self, "native_dtype", torch.bfloat16)
+
+    def engine_for(self, shape, training: bool, dtype=None):
+        dtype = dtype or self._native_dtype()
+        key = (tuple(shape), bool(training), dtype)
         eng = self._engines.get(key)
         if eng is None:
-            eng = ResNetEngine(self, shape, training)
+            eng = ResNetEngine(self, shape, training, dtype)
             self._engines[key] = eng
         return eng
 
@@ -271,7 +277,8 @@ def _pick_splits(tiles: int, ksteps: int, sm_target: int = 0) -> int:
 class ResNetEngine:
     STEM_LDK = 152  # 7*7*3 = 147 padded so that rows are 16-byte aligned for TMA
 
-    def __init__(self, model: ResNet, in_shape, training: bool) -> None:
+    def __init__(self, model: ResNet, in_shape, training: bool, dtype=torch.bfloat16) -> None:
+        self.dtype = dtype
         from ..ops import _lib
         from ..ops import functional as Fn
         self.Fn = Fn
@@ -283,7 +290,7 @@ class ResNetEngine:
         assert C == 3, "stem expects RGB input"
         self.N = N
         self.in_shape = tuple(in_shape)
-        bf = dict(device=self.dev, dtype=torch.bfloat16)
+        bf = dict(device=self.dev, dtype=self.dtype)
         f32 = dict(device=self.dev, dtype=torch.float32)
         self.units: list[_Unit] = []
         self._zero32_plan: list = []
@@ -349,7 +356,7 @@ class ResNetEngine:
     def _unit(self, name, conv, bn, x_shape, y_shape, relu) -> _Unit:
         u = _Unit()
         u.name, u.conv, u.bn, u.x_shape, u.y_shape, u.relu = name, conv, bn, x_shape, y_shape, relu
-        bf = dict(device=self.dev, dtype=torch.bfloat16)
+        bf = dict(device=self.dev, dtype=self.dtype)
         C = y_shape[3]
         u.raw = torch.empty(y_shape, **bf)
         u.y = torch.empty(y_shape, **bf)
@@ -400,7 +407,7 @@ class ResNetEngine:
         return self._unit(name, conv, bn, x_shape, (N, P, Q, conv.out_channels), relu)
 
     def _plan_block(self, name, blk, x_shape):
-        bf = dict(device=self.dev, dtype=torch.bfloat16)
+        bf = dict(device=self.dev, dtype=self.dtype)
         b = {"name": name, "x_shape": x_shape, "kind": "basic" if isinstance(blk, BasicBlock) else "bottle"}
         if b["kind"] == "basic":
             u1 = self._conv_unit(f"{name}.conv1", blk.conv1, blk.bn1, x_shape, True)
@@ -445,13 +452,15 @@ class ResNetEngine:
         arena = getattr(p, "_dpt_arena", None)
         Cout, Cin, R, S = p.shape
         if arena is not None and arena.shadow is not None:
+            if arena.shadow.dtype != self.dtype:
+                arena.set_shadow_dtype(self.dtype)
             return arena.shadow_view(p).view(Cout, R, S, Cin)
         cache = getattr(self, "_wcache", None)
         if cache is None:
             cache = self._wcache = {}
         t = cache.get(id(p))
         if t is None:
-            t = cache[id(p)] = torch.empty((Cout, R, S, Cin), device=self.dev, dtype=torch.bfloat16)
+            t = cache[id(p)] = torch.empty((Cout, R, S, Cin), device=self.dev, dtype=self.dtype)
         t.copy_(p.detach().permute(0, 2, 3, 1))
         return t
 
@@ -502,6 +511,7 @@ class ResNetEngine:
         if x_nchw.dtype != torch.float32:
             x_nchw = x_nchw.float()
         self._last_input = x_nchw
+        Fn.set_lowp_dtype(self.dtype)
         if self.training:
             self.stats.zero_()
             if self._zero32_n:
@@ -639,6 +649,7 @@ class ResNetEngine:
         Fn = self.Fn
         m = self.m
         dlogits = dlogits.contiguous()
+        Fn.set_lowp_dtype(self.dtype)
         if self._z32_pending:
             torch.cuda.current_stream().wait_event(self._z32_ev)
             self._lib.pdl_skip_next()

@@ -51,6 +51,8 @@ _SIGS = {
     "dpt_adam_flat": [vp, vp, vp, vp, vp, i64, f32, f32, f32, f32, f32, i32, vp, vp, vp, vp],
     "dpt_cast_f32_to_bf16": [vp, vp, i64, vp],
     "dpt_pdl_skip_next": [],
+    "dpt_set_lowp_dtype": [i32],
+    "dpt_get_lowp_dtype": [],
     "dpt_symm_alloc": [C.c_size_t, C.POINTER(vp), vp],
     "dpt_symm_open": [vp, C.POINTER(vp)],
     "dpt_symm_close": [vp],
@@ -112,6 +114,11 @@ def check(code: int, what: str) -> None:
 
 def call(name: str, *args) -> None:
     check(getattr(lib(), name)(*args), name)
+
+
+def set_lowp_dtype(dtype) -> None:
+    """16-bit element type used by every kernel launched afterwards (bf16 or fp16)."""
+    lib().dpt_set_lowp_dtype(1 if dtype == torch.float16 else 0)
 
 
 def pdl_skip_next() -> None:

@@ -15,6 +15,11 @@ from ._lib import call, count, ptr, stream
 BF16 = torch.bfloat16
 
 
+def set_lowp_dtype(dtype) -> None:
+    """Select the 16-bit element type (torch.bfloat16 or torch.float16) for subsequent launches."""
+    _lib.set_lowp_dtype(dtype)
+
+
 def conv_out_hw(H: int, W: int, R: int, S: int, stride: int, pad: int) -> tuple[int, int]:
     return (H + 2 * pad - R) // stride + 1, (W + 2 * pad - S) // stride + 1
 
@@ -29,7 +34,7 @@ def conv_fprop(x, w, stride=1, pad=0, *, out=None, stats=None, splits=1):
     atomic = splits > 1
     if out is None:
         out = (torch.zeros if atomic else torch.empty)(
-            (N, P, Q, Cout), device=x.device, dtype=torch.float32 if atomic else BF16)
+            (N, P, Q, Cout), device=x.device, dtype=torch.float32 if atomic else x.dtype)
     s1, s2 = stats if stats is not None else (None, None)
     call("dpt_conv_fprop", ptr(x), ptr(w), ptr(out), N, H, W, Cin, Cout, R, S, stride, pad,
          ptr(s1), ptr(s2), int(atomic), splits, stream())
@@ -45,7 +50,7 @@ def conv_dgrad(dy, w, x_shape, stride=1, pad=0, *, out=None, dy2=None, w2=None, 
     atomic = splits > 1
     if out is None:
         out = (torch.zeros if atomic else torch.empty)(
-            (N, H, W, Cin), device=dy.device, dtype=torch.float32 if atomic else BF16)
+            (N, H, W, Cin), device=dy.device, dtype=torch.float32 if atomic else dy.dtype)
     R2, S2 = (w2.shape[1], w2.shape[2]) if w2 is not None else (0, 0)
     call("dpt_conv_dgrad_ex", ptr(dy), ptr(w), ptr(out), N, H, W, Cin, Cout, R, S, stride, pad,
          ptr(dy2), ptr(w2), R2, S2, pad2, int(atomic), splits, stream())
@@ -163,7 +168,7 @@ def maxpool_fwd(x, *, out=None, idx=None):
     N, H, W, C_ = x.shape
     P, Q = conv_out_hw(H, W, 3, 3, 2, 1)
     if out is None:
-        out = torch.empty((N, P, Q, C_), device=x.device, dtype=BF16)
+        out = torch.empty((N, P, Q, C_), device=x.device, dtype=x.dtype)
     if idx is None:
         idx = torch.empty((N, P, Q, C_), device=x.device, dtype=torch.uint8)
     call("dpt_maxpool3x3s2_fwd", ptr(x), ptr(out), ptr(idx), N, H, W, C_, stream())
@@ -174,7 +179,7 @@ def maxpool_fwd(x, *, out=None, idx=None):
 def maxpool_bwd(dy, idx, x_shape, *, out=None, dy2=None):
     N, H, W, C_ = x_shape
     if out is None:
-        out = torch.empty(x_shape, device=dy.device, dtype=BF16)
+        out = torch.empty(x_shape, device=dy.device, dtype=dy.dtype)
     call("dpt_maxpool3x3s2_bwd", ptr(dy), ptr(dy2), ptr(idx), ptr(out), N, H, W, C_, stream())
     count()
     return out
@@ -193,11 +198,11 @@ def head_fwd(x, w, b, *, pooled=None, logits=None):
     return logits, pooled
 
 
-def head_bwd(dlogits, w, pooled, x_shape, dw, db, *, dx=None):
+def head_bwd(dlogits, w, pooled, x_shape, dw, db, *, dx=None, dtype=BF16):
     N, H, W, C_ = x_shape
     K = w.shape[0]
     if dx is None:
-        dx = torch.empty(x_shape, device=dlogits.device, dtype=BF16)
+        dx = torch.empty(x_shape, device=dlogits.device, dtype=dtype)
     call("dpt_head_bwd", ptr(dlogits), ptr(w), ptr(pooled), ptr(dx), ptr(dw), ptr(db), N, H * W, C_,
          K, stream())
     count(2)
@@ -217,28 +222,28 @@ def cross_entropy(logits, target, *, loss=None, dlogits=None, loss_scale=None, m
     return loss, dlogits
 
 
-def im2col_nchw(x, R, S, stride, pad, ldk, *, out=None):
+def im2col_nchw(x, R, S, stride, pad, ldk, *, out=None, dtype=BF16):
     N, C_, H, W = x.shape
     P, Q = conv_out_hw(H, W, R, S, stride, pad)
     if out is None:
-        out = torch.empty((N * P * Q, ldk), device=x.device, dtype=BF16)
+        out = torch.empty((N * P * Q, ldk), device=x.device, dtype=dtype)
     call("dpt_im2col_nchw_f32", ptr(x), ptr(out), N, C_, H, W, R, S, stride, pad, ldk, stream())
     count()
     return out
 
 
-def pad_rows_to_bf16(src, rows, cols, ld, *, out=None):
+def pad_rows_to_bf16(src, rows, cols, ld, *, out=None, dtype=BF16):
     if out is None:
-        out = torch.empty((rows, ld), device=src.device, dtype=BF16)
+        out = torch.empty((rows, ld), device=src.device, dtype=dtype)
     call("dpt_pad_rows_f32_to_bf16", ptr(src), ptr(out), rows, cols, ld, stream())
     count()
     return out
 
 
-def nchw_to_nhwc_bf16(x, *, out=None):
+def nchw_to_nhwc_bf16(x, *, out=None, dtype=BF16):
     N, C_, H, W = x.shape
     if out is None:
-        out = torch.empty((N, H, W, C_), device=x.device, dtype=BF16)
+        out = torch.empty((N, H, W, C_), device=x.device, dtype=dtype)
     call("dpt_nchw_f32_to_nhwc_bf16", ptr(x), ptr(out), N, C_, H, W, stream())
     count()
     return out

@@ -104,11 +104,19 @@ class ParamArena:
         s = self.slots[id(p)]
         return self.param[s.offset: s.offset + s.numel]
 
+    def set_shadow_dtype(self, dtype) -> None:
+        """Re-type the 16-bit shadow arena (bf16 <-> fp16) and refill it from the fp32 masters."""
+        if self.shadow is None or self.shadow.dtype == dtype:
+            return
+        self.shadow = self.shadow.view(dtype)
+        self.refresh_shadow()
+
     def refresh_shadow(self) -> None:
         if self.shadow is None:
             return
         if self.device.type == "cuda":
             from ..ops import functional as Fn
+            Fn.set_lowp_dtype(self.shadow.dtype)
             Fn.cast_to_bf16(self.param, self.shadow)
         else:
             self.shadow.copy_(self.param)

@@ -66,11 +66,12 @@ def main(argv=None):
             print(f"Resumed from {args.resume} at epoch {start_epoch}")
 
     train_step = None
-    native_ok = device.type == "cuda" and args.amp and args.amp_dtype == "bf16"
+    native_ok = device.type == "cuda" and args.amp
     if args.cuda_graph and native_ok and getattr(optimizer, "_flat", False):
         from .graph_step import TrainStep
         shape = (args.batch_size, 3, args.image_size, args.image_size)
-        train_step = TrainStep(model, optimizer, scaler, batch_shape=shape, cuda_graph=True)
+        train_step = TrainStep(model, optimizer, scaler, batch_shape=shape, cuda_graph=True,
+                               dtype=torch.float16 if fp16 else torch.bfloat16)
     profiler = GradSyncProfiler(ddp) if args.profile_sync else None
 
     csv = M.MetricsCSV(args.output_dir, enabled=(rank == 0))

@@ -143,10 +143,10 @@ def validate(model, val_loader, criterion, device, rank, world_size, args=None):
     inference kernels (BN folded to scale/shift) instead — a documented deviation."""
     model.eval()
     acc = torch.zeros(3, device=device, dtype=torch.float64)
-    native_eval = (args is not None and getattr(args, "amp", False) and device.type == "cuda"
-                   and getattr(args, "amp_dtype", "bf16") == "bf16")
+    native_eval = args is not None and getattr(args, "amp", False) and device.type == "cuda"
     import contextlib
-    ctx = torch.autocast("cuda", dtype=torch.bfloat16) if native_eval else contextlib.nullcontext()
+    edt = torch.float16 if (args is not None and getattr(args, "amp_dtype", "bf16") == "fp16") else torch.bfloat16
+    ctx = torch.autocast("cuda", dtype=edt) if native_eval else contextlib.nullcontext()
     max_steps = (getattr(args, "steps", 0) or 0) if args is not None else 0
     for i, (images, targets) in enumerate(val_loader):
         if max_steps and i >= max_steps:

@@ -23,6 +23,11 @@ extern "C" {
 #define DPT_ERR_TIMEOUT (-5)
 #define DPT_ERR_TOO_LARGE (-6) /* size beyond a built-in fixed-capacity buffer */
 
+/* 16-bit element type of activations / shadow weights for every entry point below: 0 = bf16
+ * (default), 1 = fp16 (the reference's autocast default, train_ddp.py:204).  Process-wide. */
+int dpt_set_lowp_dtype(int is_f16);
+int dpt_get_lowp_dtype(void);
+
 /* ---- tcgen05 / TMA implicit-GEMM convolution (csrc/ops/igemm_tcgen05.cu) ----------------
  * Stand in for the cuDNN convolution forward / backward-data / backward-filter calls that
  * torchvision's resnet18 makes on the reference path (train_ddp.py:153-156, 205-213). */
