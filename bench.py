@@ -38,6 +38,9 @@ def parse():
     p.add_argument("--image-size", type=int, default=32)
     p.add_argument("--num-classes", type=int, default=10)
     p.add_argument("--no-graph", action="store_true")
+    p.add_argument("--amp-dtype", default="bf16", choices=["bf16", "fp16"],
+                   help="16-bit compute dtype of this framework's arm (fp16 adds the dynamic GradScaler, "
+                        "i.e. exactly the reference's --amp numerics)")
     p.add_argument("--l2-flush", action="store_true",
                    help="flush L2 (untimed 256 MiB memset) between timed steps; default is no flush "
                         "because one step touches ~207 MB > 126 MB L2")
@@ -163,13 +166,17 @@ def run_ours(a):
                                               allreduce_algo=a.allreduce_algo)
     opt = SGD(model.parameters(), lr=0.1, momentum=0.9, weight_decay=5e-4)
     if a.fused_optimizer is None:
-        a.fused_optimizer = world > 1
+        a.fused_optimizer = world > 1 and a.amp_dtype != "fp16"
     if ddp is not None and a.fused_optimizer:
         a.fused_optimizer = bool(ddp.enable_fused_sgd(opt))
-    scaler = GradScaler(device=device, enabled=False)  # bf16: no loss scaling needed
+    fp16 = a.amp_dtype == "fp16"
+    if fp16 and a.fused_optimizer:
+        a.fused_optimizer = False        # GradScaler skip-step semantics need the separate update
+    scaler = GradScaler(device=device, enabled=fp16)  # bf16: no loss scaling needed
     shape = (a.batch_size, 3, a.image_size, a.image_size)
     step = TrainStep(model, opt, scaler, batch_shape=shape, cuda_graph=not a.no_graph,
-                     lazy_buffer_sync=not a.eager_buffer_sync)
+                     lazy_buffer_sync=not a.eager_buffer_sync,
+                     dtype=torch.float16 if fp16 else torch.bfloat16)
     batches = make_host_batches(8, shape, a.num_classes, seed=1234 + rank)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=device) if a.l2_flush else None
 
@@ -236,13 +243,14 @@ def run_ours(a):
         "ms_per_step": dev_ms / K,
         "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None if BASELINE_VALUE is None else gb * K / (dev_ms * 1e-3) / BASELINE_VALUE,
-        "dtype": "bf16", "data": "synthetic (random-init weights, random CIFAR-shaped batches)",
+        "dtype": a.amp_dtype + (" + dynamic GradScaler" if fp16 else ""),
+        "data": "synthetic (random-init weights, random CIFAR-shaped batches)",
         "impl": "ours",
         "config": {"model": f"{a.arch}(num_classes={a.num_classes})",
                    "global_batch": gb, "per_gpu_batch": a.batch_size,
                    "input": f"{a.batch_size}x3x{a.image_size}x{a.image_size} fp32 NCHW per GPU",
                    "seq_len": None, "parallelism": f"dp{world}", "optimizer": "SGD(0.1, m=0.9, wd=5e-4)",
-                   "amp": "bf16 activations/weights, fp32 master+grads+BN stats",
+                   "amp": f"{a.amp_dtype} activations/weights, fp32 master+grads+BN stats",
                    "cuda_graph": step.graph is not None,
                    "l2": "flushed between timed steps (untimed 256 MiB memset)" if flush is not None
                          else "not flushed: one step touches ~207 MB (fp32 params+grads+momentum, bf16 shadow, "
