@@ -38,7 +38,7 @@ def parse():
     p.add_argument("--image-size", type=int, default=32)
     p.add_argument("--num-classes", type=int, default=10)
     p.add_argument("--no-graph", action="store_true")
-    p.add_argument("--amp-dtype", default="bf16", choices=["bf16", "fp16"],
+    p.add_argument("--amp-dtype", default="bf16", choices=["bf16", "fp16", "fp32"],
                    help="16-bit compute dtype of this framework's arm (fp16 adds the dynamic GradScaler, "
                         "i.e. exactly the reference's --amp numerics)")
     p.add_argument("--l2-flush", action="store_true",
@@ -176,7 +176,7 @@ def run_ours(a):
     shape = (a.batch_size, 3, a.image_size, a.image_size)
     step = TrainStep(model, opt, scaler, batch_shape=shape, cuda_graph=not a.no_graph,
                      lazy_buffer_sync=not a.eager_buffer_sync,
-                     dtype=torch.float16 if fp16 else torch.bfloat16)
+                     dtype={"fp16": torch.float16, "fp32": torch.float32}.get(a.amp_dtype, torch.bfloat16))
     batches = make_host_batches(8, shape, a.num_classes, seed=1234 + rank)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=device) if a.l2_flush else None
 
@@ -243,7 +243,8 @@ def run_ours(a):
         "ms_per_step": dev_ms / K,
         "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None if BASELINE_VALUE is None else gb * K / (dev_ms * 1e-3) / BASELINE_VALUE,
-        "dtype": a.amp_dtype + (" + dynamic GradScaler" if fp16 else ""),
+        "dtype": a.amp_dtype + (" + dynamic GradScaler" if fp16 else "") +
+                 (" activations, TF32 tensor-core math (no AMP)" if a.amp_dtype == "fp32" else ""),
         "data": "synthetic (random-init weights, random CIFAR-shaped batches)",
         "impl": "ours",
         "config": {"model": f"{a.arch}(num_classes={a.num_classes})",

@@ -390,7 +390,7 @@ struct dpt_comm {
 };
 
 extern "C" int dpt_comm_set_lowp_dtype(int is_f16) {
-    dpt::g_comm_shadow_f16 = is_f16 ? 1 : 0;
+    dpt::g_comm_shadow_f16 = (is_f16 == 1) ? 1 : 0;
     return 0;
 }
 

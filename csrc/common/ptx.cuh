@@ -121,6 +121,18 @@ __device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t desc_a, uint6
         "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// Same with fp32 operands consumed as TF32 (K = 8 per instruction).
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b,
+                                          uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+        "}\n" ::"r"(tmem_d),
+        "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
 // Arrive on an mbarrier once all previously issued tcgen05.mma of this thread retire.
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile(
@@ -156,6 +168,29 @@ __device__ __forceinline__ uint64_t make_smem_desc_sw128(uint32_t saddr, uint32_
     return d;
 }
 
+// General form: layout_type 2 = SWIZZLE_128B, 1 = SWIZZLE_128B_BASE32B (32-bit MN-major operands:
+// 32-byte swizzle chunks, 4-row K atoms; pairs with CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B).
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_bytes,
+                                                   uint32_t sbo_bytes, uint32_t layout_type) {
+    uint64_t d = 0;
+    d |= static_cast<uint64_t>((saddr >> 4) & 0x3FFF);
+    d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFF) << 16;
+    d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3FFF) << 32;
+    d |= static_cast<uint64_t>(1) << 46;
+    d |= static_cast<uint64_t>(layout_type & 7) << 61;
+    return d;
+}
+
+// Instruction descriptor with fp32 D; operand format: 0 = F16, 1 = BF16, 2 = TF32.
+__host__ __device__ constexpr uint32_t make_idesc(int M, int N, int a_mn_major, int b_mn_major,
+                                                  int fmt) {
+    return (1u << 4)                           // D format: F32
+           | (uint32_t(fmt) << 7)              // A format
+           | (uint32_t(fmt) << 10)             // B format
+           | (uint32_t(a_mn_major) << 15)      // A major: 0 = K, 1 = MN
+           | (uint32_t(b_mn_major) << 16)      // B major
+           | (uint32_t(N >> 3) << 17) | (uint32_t(M >> 4) << 24);
+}
 // Instruction descriptor for kind::f16 with bf16 A/B and fp32 D.
 __host__ __device__ constexpr uint32_t make_idesc_bf16(int M, int N, int a_mn_major,
                                                        int b_mn_major) {

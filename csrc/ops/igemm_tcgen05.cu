@@ -106,17 +106,25 @@ __device__ __forceinline__ float warp_colsum16(float (&v)[16], uint32_t lane) {
     return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 1);
 }
 
-template <int MODE, int BLOCK_N, int NSTAGES, bool F16>
+// DT: element type of both operands: 0 = bf16, 1 = fp16 (kind::f16), 2 = fp32 read as TF32
+// (kind::tf32; the reference's FP32 mode also runs its convolutions in TF32 through cuDNN).
+template <int MODE, int BLOCK_N, int NSTAGES, int DT>
 __global__ void __launch_bounds__(kNumThreads, 1)
 igemm_kernel(const __grid_constant__ IgemmMaps maps, const __grid_constant__ IgemmParams prm) {
     constexpr bool A_MN = (MODE == MODE_WGRAD);
     constexpr bool B_MN = (MODE != MODE_FPROP);
-    constexpr int kBStageBytes = BLOCK_N * kKBlk * 2;
+    constexpr bool F16 = (DT == 1);
+    constexpr int ESZ = (DT == 2) ? 4 : 2;
+    constexpr int kKB = 128 / ESZ;             // k elements (K-major) or k rows (MN-major) per stage
+    constexpr int kMnBlk = 128 / ESZ;          // MN elements in one 128-byte swizzle block
+    constexpr int kMnBlkBytes = kKB * 128;     // one MN block = kKB rows x 128 B
+    constexpr int kUmmaK = 32 / ESZ;           // 16 (16-bit) or 8 (tf32)
+    constexpr int kBStageBytes = BLOCK_N * 128;
     constexpr int kStageBytes = kAStageBytes + kBStageBytes;
     constexpr uint32_t kTmemCols = BLOCK_N < 32 ? 32 : BLOCK_N;
     // operand format field: 1 = BF16, 0 = F16 (bits 7-9 for A, 10-12 for B)
-    constexpr uint32_t kIdesc = make_idesc_bf16(kTileM, BLOCK_N, A_MN ? 1 : 0, B_MN ? 1 : 0) &
-                                (F16 ? ~((1u << 7) | (1u << 10)) : ~0u);
+    constexpr uint32_t kIdesc =
+        make_idesc(kTileM, BLOCK_N, A_MN ? 1 : 0, B_MN ? 1 : 0, DT == 0 ? 1 : (DT == 1 ? 0 : 2));
 
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     // SWIZZLE_128B needs 1024-byte aligned stage bases.
@@ -204,19 +212,19 @@ igemm_kernel(const __grid_constant__ IgemmMaps maps, const __grid_constant__ Ige
                     const int ti = prm.cls_begin[cls] + k / prm.chunks;
                     const int j = k % prm.chunks;
                     const IgemmTap tp = prm.taps[ti];
-                    tma_load_4d(sa, &maps.a[tp.a_map], &full_bar[stage], j * kKBlk, q0 + tp.dw,
+                    tma_load_4d(sa, &maps.a[tp.a_map], &full_bar[stage], j * kKB, q0 + tp.dw,
                                 p0 + tp.dh, n0);
-                    tma_load_2d(sb, &maps.b[tp.b_map], &full_bar[stage], tp.koff + j * kKBlk, col0);
+                    tma_load_2d(sb, &maps.b[tp.b_map], &full_bar[stage], tp.koff + j * kKB, col0);
                 } else if (MODE == MODE_DGRAD) {
                     const int ti = prm.cls_begin[cls] + k / prm.chunks;
                     const int j = k % prm.chunks;
                     const IgemmTap tp = prm.taps[ti];
-                    tma_load_4d(sa, &maps.a[tp.a_map], &full_bar[stage], j * kKBlk, q0 + tp.dw,
+                    tma_load_4d(sa, &maps.a[tp.a_map], &full_bar[stage], j * kKB, q0 + tp.dw,
                                 p0 + tp.dh, n0);
 #pragma unroll
-                    for (int nb = 0; nb < BLOCK_N / 64; ++nb)
-                        tma_load_2d(sb + nb * 8192, &maps.b[tp.b_map], &full_bar[stage],
-                                    tp.koff + col0 + nb * 64, j * kKBlk);
+                    for (int nb = 0; nb < BLOCK_N / kMnBlk; ++nb)
+                        tma_load_2d(sb + nb * kMnBlkBytes, &maps.b[tp.b_map], &full_bar[stage],
+                                    tp.koff + col0 + nb * kMnBlk, j * kKB);
                 } else {
                     int t = k;
                     const int wq = (t % prm.tiles_q) * prm.bq;
@@ -226,13 +234,13 @@ igemm_kernel(const __grid_constant__ IgemmMaps maps, const __grid_constant__ Ige
                     const int wn = t * prm.bn;
                     const IgemmTap tp = prm.taps[tap_w];
 #pragma unroll
-                    for (int mb = 0; mb < kTileM / 64; ++mb)
-                        tma_load_4d(sa + mb * 8192, &maps.a[0], &full_bar[stage], row0_w + mb * 64,
-                                    wq, wp, wn);
+                    for (int mb = 0; mb < kTileM / kMnBlk; ++mb)
+                        tma_load_4d(sa + mb * kMnBlkBytes, &maps.a[0], &full_bar[stage],
+                                    row0_w + mb * kMnBlk, wq, wp, wn);
 #pragma unroll
-                    for (int nb = 0; nb < BLOCK_N / 64; ++nb)
-                        tma_load_4d(sb + nb * 8192, &maps.b[tp.b_map], &full_bar[stage],
-                                    col0 + nb * 64, wq + tp.dw, wp + tp.dh, wn);
+                    for (int nb = 0; nb < BLOCK_N / kMnBlk; ++nb)
+                        tma_load_4d(sb + nb * kMnBlkBytes, &maps.b[tp.b_map], &full_bar[stage],
+                                    col0 + nb * kMnBlk, wq + tp.dw, wp + tp.dh, wn);
                 }
                 if (++stage == NSTAGES) {
                     stage = 0;
@@ -251,14 +259,22 @@ igemm_kernel(const __grid_constant__ IgemmMaps maps, const __grid_constant__ Ige
                 const uint32_t sa = smem_u32(smem + stage * kStageBytes);
                 const uint32_t sb = sa + kAStageBytes;
 #pragma unroll
-                for (int kk = 0; kk < kKBlk / 16; ++kk) {
-                    // K-major: 16 bf16 = 32 B further inside the 128 B swizzle row.
-                    // MN-major: 16 k-rows = 2048 B further; LBO = next 64-wide MN block.
-                    const uint64_t da = A_MN ? make_smem_desc_sw128(sa + kk * 2048, 8192, 1024)
-                                             : make_smem_desc_sw128(sa + kk * 32, 16, 1024);
-                    const uint64_t db = B_MN ? make_smem_desc_sw128(sb + kk * 2048, 8192, 1024)
-                                             : make_smem_desc_sw128(sb + kk * 32, 16, 1024);
-                    umma_f16(tmem_base, da, db, kIdesc, (k | kk) != 0 ? 1u : 0u);
+                for (int kk = 0; kk < kKB / kUmmaK; ++kk) {
+                    // K-major: one instruction's K (32 bytes) further inside the 128 B swizzle row.
+                    // MN-major: kUmmaK k-rows of 128 B further; LBO = next MN block.
+                    // 32-bit MN-major operands use the 32-byte-base swizzle (4-row K atoms)
+                    constexpr uint32_t kMnSbo = (DT == 2) ? 512 : 1024;
+                    constexpr uint32_t kMnLayout = (DT == 2) ? 1 : 2;
+                    const uint64_t da =
+                        A_MN ? make_smem_desc(sa + kk * (kUmmaK * 128), kMnBlkBytes, kMnSbo, kMnLayout)
+                             : make_smem_desc_sw128(sa + kk * 32, 16, 1024);
+                    const uint64_t db =
+                        B_MN ? make_smem_desc(sb + kk * (kUmmaK * 128), kMnBlkBytes, kMnSbo, kMnLayout)
+                             : make_smem_desc_sw128(sb + kk * 32, 16, 1024);
+                    if (DT == 2)
+                        umma_tf32(tmem_base, da, db, kIdesc, (k | kk) != 0 ? 1u : 0u);
+                    else
+                        umma_f16(tmem_base, da, db, kIdesc, (k | kk) != 0 ? 1u : 0u);
                 }
                 umma_commit(&empty_bar[stage]);  // frees the smem slot when the MMAs retire
                 if (++stage == NSTAGES) {
@@ -452,13 +468,17 @@ static PFN_encodeTiled get_encode() {
     return fn;
 }
 
-// Element type of the 16-bit operands (0 = bf16, 1 = fp16), set through dpt_set_lowp_dtype().
+// Element type of the operands (0 = bf16, 1 = fp16, 2 = fp32/TF32), set through
+// dpt_set_lowp_dtype().
 static int g_lowp_f16 = 0;
+static inline int esz() { return g_lowp_f16 == 2 ? 4 : 2; }
+static inline int kblk() { return 128 / esz(); }      // elements per 128-byte swizzle row
+static inline int lowp_out_mode() { return g_lowp_f16 == 2 ? OUT_F32 : OUT_BF16; }
 
 // 16-bit tensor map, up to 4-D, inner box = 64 elements (128 B) with SWIZZLE_128B.
 // dims/strides are in elements; strides[i] is the stride of dimension i+1.
 static int make_tmap(CUtensorMap* m, const void* base, int rank, const long long* dims,
-                     const long long* strides, const int* box) {
+                     const long long* strides, const int* box, bool mn_major = false) {
     PFN_encodeTiled enc = get_encode();
     if (enc == nullptr) return DPT_ERR_DRIVER;
     cuuint64_t gdim[4];
@@ -469,9 +489,14 @@ static int make_tmap(CUtensorMap* m, const void* base, int rank, const long long
         gdim[i] = static_cast<cuuint64_t>(dims[i] > 0 ? dims[i] : 1);
         bdim[i] = static_cast<cuuint32_t>(box[i]);
     }
-    for (int i = 0; i + 1 < rank; ++i) gstr[i] = static_cast<cuuint64_t>(strides[i]) * 2;
-    CUresult r = enc(m, g_lowp_f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(base), gdim, gstr,
-                     bdim, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+    for (int i = 0; i + 1 < rank; ++i) gstr[i] = static_cast<cuuint64_t>(strides[i]) * esz();
+    const CUtensorMapDataType tdt = g_lowp_f16 == 2   ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
+                                    : g_lowp_f16 == 1 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16
+                                                      : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+    CUresult r = enc(m, tdt, rank, const_cast<void*>(base), gdim, gstr,
+                     bdim, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     (mn_major && g_lowp_f16 == 2) ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B
+                                                   : CU_TENSOR_MAP_SWIZZLE_128B,
                      CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
         fprintf(stderr,
@@ -507,11 +532,13 @@ static void pick_box(int rows, int Q, int P, int N, int* bq, int* bp, int* bn) {
 
 template <int MODE, int BLOCK_N>
 static int launch_cfg(const IgemmMaps& maps, const IgemmParams& prm, dim3 grid, cudaStream_t st) {
-    constexpr int kBStageBytes = BLOCK_N * kKBlk * 2;
+    constexpr int kBStageBytes = BLOCK_N * 128;
     constexpr int NST = (BLOCK_N == 128) ? 6 : 8;
     const int smem = NST * (kAStageBytes + kBStageBytes) + 1024;
-    auto kern = g_lowp_f16 ? igemm_kernel<MODE, BLOCK_N, NST, true> : igemm_kernel<MODE, BLOCK_N, NST, false>;
-    static bool attr_done[2] = {false, false};
+    auto kern = g_lowp_f16 == 2   ? igemm_kernel<MODE, BLOCK_N, NST, 2>
+                : g_lowp_f16 == 1 ? igemm_kernel<MODE, BLOCK_N, NST, 1>
+                                  : igemm_kernel<MODE, BLOCK_N, NST, 0>;
+    static bool attr_done[3] = {false, false, false};
     if (!attr_done[g_lowp_f16]) {
         cudaError_t e =
             cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
@@ -548,28 +575,28 @@ struct TapBuilder {
 };
 
 static int build_act_maps(CUtensorMap* maps4, const void* x, int N, int H, int W, int C, int stride,
-                          int rows, int bq, int bp, int bn) {
+                          int rows, int bq, int bp, int bn, bool mn_major = false) {
     (void)rows;
-    const int box[4] = {64, bq, bp, bn};
+    const int box[4] = {kblk(), bq, bp, bn};
     if (stride == 1) {
         const long long dims[4] = {C, W, H, N};
         const long long str[3] = {C, (long long)W * C, (long long)H * W * C};
-        int e = make_tmap(&maps4[0], x, 4, dims, str, box);
+        int e = make_tmap(&maps4[0], x, 4, dims, str, box, mn_major);
         if (e) return e;
         for (int i = 1; i < 4; ++i) maps4[i] = maps4[0];
         return 0;
     }
     for (int ph = 0; ph < 2; ++ph)
         for (int pw = 0; pw < 2; ++pw) {
-            const __nv_bfloat16* base =
-                reinterpret_cast<const __nv_bfloat16*>(x) + ((long long)ph * W + pw) * C;
+            const char* base =
+                reinterpret_cast<const char*>(x) + ((long long)ph * W + pw) * C * esz();
             const long long dims[4] = {C, (W - pw + 1) / 2, (H - ph + 1) / 2, N};
             const long long str[3] = {2LL * C, 2LL * W * C, (long long)H * W * C};
             if (dims[1] <= 0 || dims[2] <= 0) {
                 maps4[ph * 2 + pw] = maps4[0];
                 continue;
             }
-            int e = make_tmap(&maps4[ph * 2 + pw], base, 4, dims, str, box);
+            int e = make_tmap(&maps4[ph * 2 + pw], base, 4, dims, str, box, mn_major);
             if (e) return e;
         }
     return 0;
@@ -611,14 +638,14 @@ using namespace dpt;
 
 // called by dpt_set_lowp_dtype (norm_pool_loss.cu) so that every translation unit agrees
 extern "C" int dpt_igemm_set_lowp_dtype(int is_f16) {
-    dpt::g_lowp_f16 = is_f16 ? 1 : 0;
+    dpt::g_lowp_f16 = (is_f16 >= 0 && is_f16 <= 2) ? is_f16 : 0;
     return 0;
 }
 
 extern "C" int dpt_conv_fprop(const void* x, const void* w, void* y, int N, int H, int W, int Cin,
                               int Cout, int R, int S, int stride, int pad, float* stat_sum,
                               float* stat_sq, int out_f32_atomic, int splits, void* stream) {
-    if (Cin % 8 != 0 || (stride != 1 && stride != 2) || R * S > kMaxTaps) return DPT_ERR_SHAPE;
+    if (Cin % (16 / esz()) != 0 || (stride != 1 && stride != 2) || R * S > kMaxTaps) return DPT_ERR_SHAPE;
     const int P = (H + 2 * pad - R) / stride + 1, Q = (W + 2 * pad - S) / stride + 1;
     IgemmMaps maps;
     IgemmParams prm;
@@ -630,7 +657,7 @@ extern "C" int dpt_conv_fprop(const void* x, const void* w, void* y, int N, int 
     {
         const long long dims[2] = {(long long)R * S * Cin, Cout};
         const long long str[1] = {(long long)R * S * Cin};
-        const int box[2] = {64, block_n};
+        const int box[2] = {kblk(), block_n};
         e = make_tmap(&maps.b[0], w, 2, dims, str, box);
         if (e) return e;
         for (int i = 1; i < 4; ++i) maps.b[i] = maps.b[0];
@@ -645,7 +672,7 @@ extern "C" int dpt_conv_fprop(const void* x, const void* w, void* y, int N, int 
     prm.Q = Q;
     prm.P = P;
     prm.NB = N;
-    prm.chunks = (Cin + 63) / 64;
+    prm.chunks = (Cin + kblk() - 1) / kblk();
     const int ksteps = tb.ntaps * prm.chunks;
     if (splits < 1) splits = 1;
     if (splits > ksteps) splits = ksteps;
@@ -661,7 +688,7 @@ extern "C" int dpt_conv_fprop(const void* x, const void* w, void* y, int N, int 
     prm.cls_begin[1] = tb.ntaps;
     prm.n_total = Cout;
     prm.out = y;
-    prm.out_mode = out_f32_atomic ? OUT_F32_ATOMIC : OUT_BF16;
+    prm.out_mode = out_f32_atomic ? OUT_F32_ATOMIC : lowp_out_mode();
     prm.ldo = Cout;
     prm.OH = P;
     prm.OW = Q;
@@ -692,7 +719,7 @@ extern "C" int dpt_conv_dgrad_ex(const void* dy, const void* w, void* dx, int N,
                                  int Cin, int Cout, int R, int S, int stride, int pad,
                                  const void* dy2, const void* w2, int R2, int S2, int pad2,
                                  int out_f32_atomic, int splits, void* stream) {
-    if (Cin % 8 != 0 || Cout % 8 != 0 || (stride != 1 && stride != 2)) return DPT_ERR_SHAPE;
+    if (Cin % (16 / esz()) != 0 || Cout % (16 / esz()) != 0 || (stride != 1 && stride != 2)) return DPT_ERR_SHAPE;
     const int P = (H + 2 * pad - R) / stride + 1, Q = (W + 2 * pad - S) / stride + 1;
     IgemmMaps maps;
     IgemmParams prm;
@@ -700,7 +727,7 @@ extern "C" int dpt_conv_dgrad_ex(const void* dy, const void* w, void* dx, int N,
     // Row space: dX pixels of one parity class (all pixels for stride 1).
     const int HC = (H + stride - 1) / stride, WC = (W + stride - 1) / stride;
     pick_box(kTileM, WC, HC, N, &prm.bq, &prm.bp, &prm.bn);
-    const int box[4] = {64, prm.bq, prm.bp, prm.bn};
+    const int box[4] = {kblk(), prm.bq, prm.bp, prm.bn};
     {
         const long long dims[4] = {Cout, Q, P, N};
         const long long str[3] = {Cout, (long long)Q * Cout, (long long)P * Q * Cout};
@@ -719,14 +746,14 @@ extern "C" int dpt_conv_dgrad_ex(const void* dy, const void* w, void* dx, int N,
     {
         const long long dims[2] = {(long long)R * S * Cin, Cout};
         const long long str[1] = {(long long)R * S * Cin};
-        const int bbox[2] = {64, 64};
-        int e = make_tmap(&maps.b[0], w, 2, dims, str, bbox);
+        const int bbox[2] = {kblk(), kblk()};
+        int e = make_tmap(&maps.b[0], w, 2, dims, str, bbox, /*mn_major=*/true);
         if (e) return e;
         maps.b[1] = maps.b[0];
         if (dy2 != nullptr) {
             const long long dims2[2] = {(long long)R2 * S2 * Cin, Cout};
             const long long str2[1] = {(long long)R2 * S2 * Cin};
-            e = make_tmap(&maps.b[1], w2, 2, dims2, str2, bbox);
+            e = make_tmap(&maps.b[1], w2, 2, dims2, str2, bbox, /*mn_major=*/true);
             if (e) return e;
         }
         maps.b[2] = maps.b[3] = maps.b[0];
@@ -765,13 +792,13 @@ extern "C" int dpt_conv_dgrad_ex(const void* dy, const void* w, void* dx, int N,
     prm.P = HC;
     prm.NB = N;
     // (odd H/W with stride 2: classes hp=1 have one row fewer; mask through OH/OW below)
-    prm.chunks = (Cout + 63) / 64;
+    prm.chunks = (Cout + kblk() - 1) / kblk();
     if (!out_f32_atomic || splits < 1) splits = 1;
     prm.splits = splits;
     prm.nclasses = ncls;
     prm.n_total = Cin;
     prm.out = dx;
-    prm.out_mode = out_f32_atomic ? OUT_F32_ATOMIC : OUT_BF16;
+    prm.out_mode = out_f32_atomic ? OUT_F32_ATOMIC : lowp_out_mode();
     prm.ldo = Cin;
     prm.OH = H;
     prm.OW = W;
@@ -786,21 +813,22 @@ extern "C" int dpt_conv_dgrad_ex(const void* dy, const void* w, void* dx, int N,
 extern "C" int dpt_conv_wgrad(const void* dy, const void* x, float* dw, int N, int H, int W,
                               int Cin, int Cout, int R, int S, int stride, int pad, int splits,
                               void* stream) {
-    if (Cin % 8 != 0 || Cout % 8 != 0 || (stride != 1 && stride != 2)) return DPT_ERR_SHAPE;
+    if (Cin % (16 / esz()) != 0 || Cout % (16 / esz()) != 0 || (stride != 1 && stride != 2)) return DPT_ERR_SHAPE;
     const int P = (H + 2 * pad - R) / stride + 1, Q = (W + 2 * pad - S) / stride + 1;
     IgemmMaps maps;
     IgemmParams prm;
     memset(&prm, 0, sizeof(prm));
-    pick_box(kKBlk, Q, P, N, &prm.bq, &prm.bp, &prm.bn);
-    const int box[4] = {64, prm.bq, prm.bp, prm.bn};
+    pick_box(kblk(), Q, P, N, &prm.bq, &prm.bp, &prm.bn);
+    const int box[4] = {kblk(), prm.bq, prm.bp, prm.bn};
     {
         const long long dims[4] = {Cout, Q, P, N};
         const long long str[3] = {Cout, (long long)Q * Cout, (long long)P * Q * Cout};
-        int e = make_tmap(&maps.a[0], dy, 4, dims, str, box);
+        int e = make_tmap(&maps.a[0], dy, 4, dims, str, box, /*mn_major=*/true);
         if (e) return e;
         for (int i = 1; i < 4; ++i) maps.a[i] = maps.a[0];
     }
-    int e = build_act_maps(maps.b, x, N, H, W, Cin, stride, kKBlk, prm.bq, prm.bp, prm.bn);
+    int e = build_act_maps(maps.b, x, N, H, W, Cin, stride, kblk(), prm.bq, prm.bp, prm.bn,
+                           /*mn_major=*/true);
     if (e) return e;
     TapBuilder tb;
     fprop_taps(&tb, H, W, P, Q, Cin, R, S, stride, pad, 0);
@@ -847,7 +875,8 @@ extern "C" int dpt_gemm_bf16(int op, const void* A, const void* B, void* C, int 
                              long long lda, long long ldb, long long ldc, int out_mode,
                              const float* bias, float* stat_sum, float* stat_sq, int splits,
                              void* stream) {
-    if (lda % 8 != 0 || ldb % 8 != 0 || op < 0 || op > 2) return DPT_ERR_SHAPE;
+    if (lda % (16 / esz()) != 0 || ldb % (16 / esz()) != 0 || op < 0 || op > 2) return DPT_ERR_SHAPE;
+    if (out_mode == OUT_BF16) out_mode = lowp_out_mode();
     IgemmMaps maps;
     IgemmParams prm;
     memset(&prm, 0, sizeof(prm));
@@ -869,19 +898,19 @@ extern "C" int dpt_gemm_bf16(int op, const void* A, const void* B, void* C, int 
     if (op == 0 || op == 1) {
         const long long dims[4] = {K, M, 1, 1};
         const long long str[3] = {lda, lda * M, lda * M};
-        const int box[4] = {64, kTileM, 1, 1};
+        const int box[4] = {kblk(), kTileM, 1, 1};
         int e = make_tmap(&maps.a[0], A, 4, dims, str, box);
         if (e) return e;
         if (op == 0) {
             const long long bd[2] = {K, N};
             const long long bs[1] = {ldb};
-            const int bb[2] = {64, block_n};
+            const int bb[2] = {kblk(), block_n};
             e = make_tmap(&maps.b[0], B, 2, bd, bs, bb);
         } else {
             const long long bd[2] = {N, K};
             const long long bs[1] = {ldb};
-            const int bb[2] = {64, 64};
-            e = make_tmap(&maps.b[0], B, 2, bd, bs, bb);
+            const int bb[2] = {kblk(), kblk()};
+            e = make_tmap(&maps.b[0], B, 2, bd, bs, bb, /*mn_major=*/true);
         }
         if (e) return e;
         for (int i = 1; i < 4; ++i) {
@@ -892,7 +921,7 @@ extern "C" int dpt_gemm_bf16(int op, const void* A, const void* B, void* C, int 
         prm.tiles_q = (M + kTileM - 1) / kTileM;
         prm.Q = M;
         prm.OW = M;
-        prm.chunks = (K + 63) / 64;
+        prm.chunks = (K + kblk() - 1) / kblk();
         if (out_mode != OUT_F32_ATOMIC) splits = 1;
         if (splits > prm.chunks) splits = prm.chunks;
         {
@@ -913,18 +942,18 @@ extern "C" int dpt_gemm_bf16(int op, const void* A, const void* B, void* C, int 
         const long long as[3] = {lda, lda * K, lda * K};
         const long long bd[4] = {N, K, 1, 1};
         const long long bs[3] = {ldb, ldb * K, ldb * K};
-        const int box[4] = {64, kKBlk, 1, 1};
-        int e = make_tmap(&maps.a[0], A, 4, ad, as, box);
+        const int box[4] = {kblk(), kblk(), 1, 1};
+        int e = make_tmap(&maps.a[0], A, 4, ad, as, box, /*mn_major=*/true);
         if (e) return e;
-        e = make_tmap(&maps.b[0], B, 4, bd, bs, box);
+        e = make_tmap(&maps.b[0], B, 4, bd, bs, box, /*mn_major=*/true);
         if (e) return e;
         for (int i = 1; i < 4; ++i) {
             maps.a[i] = maps.a[0];
             maps.b[i] = maps.b[0];
         }
     }
-    prm.bq = kKBlk;
-    prm.tiles_q = (K + kKBlk - 1) / kKBlk;
+    prm.bq = kblk();
+    prm.tiles_q = (K + kblk() - 1) / kblk();
     prm.m_total = M;
     prm.ntile_per_tap = (N + block_n - 1) / block_n;
     if (out_mode != OUT_F32_ATOMIC) splits = 1;

@@ -25,7 +25,7 @@
 // points dispatch on the process-wide setting made with dpt_set_lowp_dtype().
 namespace dpt {
 inline int& lowp_dtype_flag() {
-    static int f = 0;  // 0 = bf16, 1 = fp16
+    static int f = 0;  // 0 = bf16, 1 = fp16, 2 = fp32 (TF32 tensor-core math)
     return f;
 }
 inline bool lowp_is_f16() { return lowp_dtype_flag() == 1; }
@@ -35,7 +35,8 @@ extern "C" int dpt_igemm_set_lowp_dtype(int is_f16);
 extern "C" int dpt_optim_set_lowp_dtype(int is_f16);
 extern "C" int dpt_comm_set_lowp_dtype(int is_f16);
 extern "C" int dpt_set_lowp_dtype(int is_f16) {
-    dpt::lowp_dtype_flag() = is_f16 ? 1 : 0;
+    if (is_f16 < 0 || is_f16 > 2) is_f16 = 0;
+    dpt::lowp_dtype_flag() = is_f16;
     dpt_igemm_set_lowp_dtype(is_f16);
     dpt_optim_set_lowp_dtype(is_f16);
     dpt_comm_set_lowp_dtype(is_f16);
@@ -66,87 +67,148 @@ __device__ __forceinline__ lowp float_to_lp(float v) { return __float2half_rn(v)
 #define DPT_NS dpt_lp_f16
 #define DPT_LOWP_IS_F16 1
 #include "norm_pool_loss_impl.cuh"
+#undef DPT_NS
+
+// fp32 activations (the reference's FP32 mode; convolutions then run as TF32 on the tensor cores)
+namespace dpt_lp_f32 {
+using lowp = float;
+using lowp2 = float2;
+__device__ __forceinline__ float2 lp2_to_float2(lowp2 v) { return v; }
+__device__ __forceinline__ lowp2 floats_to_lp2(float a, float b) { return make_float2(a, b); }
+__device__ __forceinline__ float lp_to_float(lowp v) { return v; }
+__device__ __forceinline__ lowp float_to_lp(float v) { return v; }
+}  // namespace dpt_lp_f32
+#define DPT_NS dpt_lp_f32
+#include "norm_pool_loss_impl.cuh"
 #undef DPT_LOWP_IS_F16
 #undef DPT_NS
 
 extern "C" int dpt_bn_stats(const void* x, float* sum, float* sq, long long M, int C, void* stream) {
-    return dpt::lowp_is_f16() ? dpt_lp_f16::dpt_bn_stats(x, sum, sq, M, C, stream)
-                               : dpt_lp_bf16::dpt_bn_stats(x, sum, sq, M, C, stream);
+    switch (dpt::lowp_dtype_flag()) {
+        case 1: return dpt_lp_f16::dpt_bn_stats(x, sum, sq, M, C, stream);
+        case 2: return dpt_lp_f32::dpt_bn_stats(x, sum, sq, M, C, stream);
+        default: return dpt_lp_bf16::dpt_bn_stats(x, sum, sq, M, C, stream);
+    }
 }
 
 extern "C" int dpt_bn_fwd_train(const void* x, const float* sum, const float* sq, const float* gamma, const float* beta, const void* residual, void* y, float* save_mean, float* save_invstd, float* running_mean, float* running_var, long long* num_batches_tracked, long long M, int C, float momentum, float eps, int relu, void* stream) {
-    return dpt::lowp_is_f16() ? dpt_lp_f16::dpt_bn_fwd_train(x, sum, sq, gamma, beta, residual, y, save_mean, save_invstd, running_mean, running_var, num_batches_tracked, M, C, momentum, eps, relu, stream)
-                               : dpt_lp_bf16::dpt_bn_fwd_train(x, sum, sq, gamma, beta, residual, y, save_mean, save_invstd, running_mean, running_var, num_batches_tracked, M, C, momentum, eps, relu, stream);
+    switch (dpt::lowp_dtype_flag()) {
+        case 1: return dpt_lp_f16::dpt_bn_fwd_train(x, sum, sq, gamma, beta, residual, y, save_mean, save_invstd, running_mean, running_var, num_batches_tracked, M, C, momentum, eps, relu, stream);
+        case 2: return dpt_lp_f32::dpt_bn_fwd_train(x, sum, sq, gamma, beta, residual, y, save_mean, save_invstd, running_mean, running_var, num_batches_tracked, M, C, momentum, eps, relu, stream);
+        default: return dpt_lp_bf16::dpt_bn_fwd_train(x, sum, sq, gamma, beta, residual, y, save_mean, save_invstd, running_mean, running_var, num_batches_tracked, M, C, momentum, eps, relu, stream);
+    }
 }
 
 extern "C" int dpt_bn_fwd_train_small_f32(const float* x, const float* gamma, const float* beta, const void* residual, void* y, void* x_bf16, float* save_mean, float* save_invstd, float* running_mean, float* running_var, long long* num_batches_tracked, long long M, int C, float momentum, float eps, int relu, void* stream) {
-    return dpt::lowp_is_f16() ? dpt_lp_f16::dpt_bn_fwd_train_small_f32(x, gamma, beta, residual, y, x_bf16, save_mean, save_invstd, running_mean, running_var, num_batches_tracked, M, C, momentum, eps, relu, stream)
-                               : dpt_lp_bf16::dpt_bn_fwd_train_small_f32(x, gamma, beta, residual, y, x_bf16, save_mean, save_invstd, running_mean, running_var, num_batches_tracked, M, C, momentum, eps, relu, stream);
+    switch (dpt::lowp_dtype_flag()) {
+        case 1: return dpt_lp_f16::dpt_bn_fwd_train_small_f32(x, gamma, beta, residual, y, x_bf16, save_mean, save_invstd, running_mean, running_var, num_batches_tracked, M, C, momentum, eps, relu, stream);
+        case 2: return dpt_lp_f32::dpt_bn_fwd_train_small_f32(x, gamma, beta, residual, y, x_bf16, save_mean, save_invstd, running_mean, running_var, num_batches_tracked, M, C, momentum, eps, relu, stream);
+        default: return dpt_lp_bf16::dpt_bn_fwd_train_small_f32(x, gamma, beta, residual, y, x_bf16, save_mean, save_invstd, running_mean, running_var, num_batches_tracked, M, C, momentum, eps, relu, stream);
+    }
 }
 
 extern "C" int dpt_bn_fwd_eval(const void* x, const float* gamma, const float* beta, const float* running_mean, const float* running_var, const void* residual, void* y, long long M, int C, float eps, int relu, void* stream) {
-    return dpt::lowp_is_f16() ? dpt_lp_f16::dpt_bn_fwd_eval(x, gamma, beta, running_mean, running_var, residual, y, M, C, eps, relu, stream)
-                               : dpt_lp_bf16::dpt_bn_fwd_eval(x, gamma, beta, running_mean, running_var, residual, y, M, C, eps, relu, stream);
+    switch (dpt::lowp_dtype_flag()) {
+        case 1: return dpt_lp_f16::dpt_bn_fwd_eval(x, gamma, beta, running_mean, running_var, residual, y, M, C, eps, relu, stream);
+        case 2: return dpt_lp_f32::dpt_bn_fwd_eval(x, gamma, beta, running_mean, running_var, residual, y, M, C, eps, relu, stream);
+        default: return dpt_lp_bf16::dpt_bn_fwd_eval(x, gamma, beta, running_mean, running_var, residual, y, M, C, eps, relu, stream);
+    }
 }
 
 extern "C" int dpt_bn_bwd_reduce_ex(const void* dy1, int dy1_is_f32, const void* dy2, const void* y, const void* x, const float* save_mean, const float* save_invstd, void* g_out, float* dgamma, float* dbeta, long long M, int C, void* stream) {
-    return dpt::lowp_is_f16() ? dpt_lp_f16::dpt_bn_bwd_reduce_ex(dy1, dy1_is_f32, dy2, y, x, save_mean, save_invstd, g_out, dgamma, dbeta, M, C, stream)
-                               : dpt_lp_bf16::dpt_bn_bwd_reduce_ex(dy1, dy1_is_f32, dy2, y, x, save_mean, save_invstd, g_out, dgamma, dbeta, M, C, stream);
+    switch (dpt::lowp_dtype_flag()) {
+        case 1: return dpt_lp_f16::dpt_bn_bwd_reduce_ex(dy1, dy1_is_f32, dy2, y, x, save_mean, save_invstd, g_out, dgamma, dbeta, M, C, stream);
+        case 2: return dpt_lp_f32::dpt_bn_bwd_reduce_ex(dy1, dy1_is_f32, dy2, y, x, save_mean, save_invstd, g_out, dgamma, dbeta, M, C, stream);
+        default: return dpt_lp_bf16::dpt_bn_bwd_reduce_ex(dy1, dy1_is_f32, dy2, y, x, save_mean, save_invstd, g_out, dgamma, dbeta, M, C, stream);
+    }
 }
 
 extern "C" int dpt_bn_bwd_reduce(const void* dy1, const void* dy2, const void* y, const void* x, const float* save_mean, const float* save_invstd, void* g_out, float* dgamma, float* dbeta, long long M, int C, void* stream) {
-    return dpt::lowp_is_f16() ? dpt_lp_f16::dpt_bn_bwd_reduce(dy1, dy2, y, x, save_mean, save_invstd, g_out, dgamma, dbeta, M, C, stream)
-                               : dpt_lp_bf16::dpt_bn_bwd_reduce(dy1, dy2, y, x, save_mean, save_invstd, g_out, dgamma, dbeta, M, C, stream);
+    switch (dpt::lowp_dtype_flag()) {
+        case 1: return dpt_lp_f16::dpt_bn_bwd_reduce(dy1, dy2, y, x, save_mean, save_invstd, g_out, dgamma, dbeta, M, C, stream);
+        case 2: return dpt_lp_f32::dpt_bn_bwd_reduce(dy1, dy2, y, x, save_mean, save_invstd, g_out, dgamma, dbeta, M, C, stream);
+        default: return dpt_lp_bf16::dpt_bn_bwd_reduce(dy1, dy2, y, x, save_mean, save_invstd, g_out, dgamma, dbeta, M, C, stream);
+    }
 }
 
 extern "C" int dpt_bn_bwd_fused(const void* dy1, int dy1_is_f32, const void* dy2, const void* y, const void* x, const float* save_mean, const float* save_invstd, const float* gamma, void* g_out, float* dgamma, float* dbeta, float* scratch, unsigned int* counter, void* dx, long long M, int C, void* stream) {
-    return dpt::lowp_is_f16() ? dpt_lp_f16::dpt_bn_bwd_fused(dy1, dy1_is_f32, dy2, y, x, save_mean, save_invstd, gamma, g_out, dgamma, dbeta, scratch, counter, dx, M, C, stream)
-                               : dpt_lp_bf16::dpt_bn_bwd_fused(dy1, dy1_is_f32, dy2, y, x, save_mean, save_invstd, gamma, g_out, dgamma, dbeta, scratch, counter, dx, M, C, stream);
+    switch (dpt::lowp_dtype_flag()) {
+        case 1: return dpt_lp_f16::dpt_bn_bwd_fused(dy1, dy1_is_f32, dy2, y, x, save_mean, save_invstd, gamma, g_out, dgamma, dbeta, scratch, counter, dx, M, C, stream);
+        case 2: return dpt_lp_f32::dpt_bn_bwd_fused(dy1, dy1_is_f32, dy2, y, x, save_mean, save_invstd, gamma, g_out, dgamma, dbeta, scratch, counter, dx, M, C, stream);
+        default: return dpt_lp_bf16::dpt_bn_bwd_fused(dy1, dy1_is_f32, dy2, y, x, save_mean, save_invstd, gamma, g_out, dgamma, dbeta, scratch, counter, dx, M, C, stream);
+    }
 }
 
 extern "C" int dpt_bn_bwd_apply(const void* g, const void* x, const float* save_mean, const float* save_invstd, const float* gamma, const float* dgamma, const float* dbeta, void* dx, long long M, int C, void* stream) {
-    return dpt::lowp_is_f16() ? dpt_lp_f16::dpt_bn_bwd_apply(g, x, save_mean, save_invstd, gamma, dgamma, dbeta, dx, M, C, stream)
-                               : dpt_lp_bf16::dpt_bn_bwd_apply(g, x, save_mean, save_invstd, gamma, dgamma, dbeta, dx, M, C, stream);
+    switch (dpt::lowp_dtype_flag()) {
+        case 1: return dpt_lp_f16::dpt_bn_bwd_apply(g, x, save_mean, save_invstd, gamma, dgamma, dbeta, dx, M, C, stream);
+        case 2: return dpt_lp_f32::dpt_bn_bwd_apply(g, x, save_mean, save_invstd, gamma, dgamma, dbeta, dx, M, C, stream);
+        default: return dpt_lp_bf16::dpt_bn_bwd_apply(g, x, save_mean, save_invstd, gamma, dgamma, dbeta, dx, M, C, stream);
+    }
 }
 
 extern "C" int dpt_maxpool3x3s2_fwd(const void* x, void* y, void* idx, int N, int H, int W, int C, void* stream) {
-    return dpt::lowp_is_f16() ? dpt_lp_f16::dpt_maxpool3x3s2_fwd(x, y, idx, N, H, W, C, stream)
-                               : dpt_lp_bf16::dpt_maxpool3x3s2_fwd(x, y, idx, N, H, W, C, stream);
+    switch (dpt::lowp_dtype_flag()) {
+        case 1: return dpt_lp_f16::dpt_maxpool3x3s2_fwd(x, y, idx, N, H, W, C, stream);
+        case 2: return dpt_lp_f32::dpt_maxpool3x3s2_fwd(x, y, idx, N, H, W, C, stream);
+        default: return dpt_lp_bf16::dpt_maxpool3x3s2_fwd(x, y, idx, N, H, W, C, stream);
+    }
 }
 
 extern "C" int dpt_maxpool3x3s2_bwd(const void* dy, const void* dy2, const void* idx, void* dx, int N, int H, int W, int C, void* stream) {
-    return dpt::lowp_is_f16() ? dpt_lp_f16::dpt_maxpool3x3s2_bwd(dy, dy2, idx, dx, N, H, W, C, stream)
-                               : dpt_lp_bf16::dpt_maxpool3x3s2_bwd(dy, dy2, idx, dx, N, H, W, C, stream);
+    switch (dpt::lowp_dtype_flag()) {
+        case 1: return dpt_lp_f16::dpt_maxpool3x3s2_bwd(dy, dy2, idx, dx, N, H, W, C, stream);
+        case 2: return dpt_lp_f32::dpt_maxpool3x3s2_bwd(dy, dy2, idx, dx, N, H, W, C, stream);
+        default: return dpt_lp_bf16::dpt_maxpool3x3s2_bwd(dy, dy2, idx, dx, N, H, W, C, stream);
+    }
 }
 
 extern "C" int dpt_head_fwd(const void* x, const float* w, const float* b, float* pooled, float* logits, int B, int HW, int C, int K, void* stream) {
-    return dpt::lowp_is_f16() ? dpt_lp_f16::dpt_head_fwd(x, w, b, pooled, logits, B, HW, C, K, stream)
-                               : dpt_lp_bf16::dpt_head_fwd(x, w, b, pooled, logits, B, HW, C, K, stream);
+    switch (dpt::lowp_dtype_flag()) {
+        case 1: return dpt_lp_f16::dpt_head_fwd(x, w, b, pooled, logits, B, HW, C, K, stream);
+        case 2: return dpt_lp_f32::dpt_head_fwd(x, w, b, pooled, logits, B, HW, C, K, stream);
+        default: return dpt_lp_bf16::dpt_head_fwd(x, w, b, pooled, logits, B, HW, C, K, stream);
+    }
 }
 
 extern "C" int dpt_head_bwd(const float* dlogits, const float* w, const float* pooled, void* dx, float* dw, float* db, int B, int HW, int C, int K, void* stream) {
-    return dpt::lowp_is_f16() ? dpt_lp_f16::dpt_head_bwd(dlogits, w, pooled, dx, dw, db, B, HW, C, K, stream)
-                               : dpt_lp_bf16::dpt_head_bwd(dlogits, w, pooled, dx, dw, db, B, HW, C, K, stream);
+    switch (dpt::lowp_dtype_flag()) {
+        case 1: return dpt_lp_f16::dpt_head_bwd(dlogits, w, pooled, dx, dw, db, B, HW, C, K, stream);
+        case 2: return dpt_lp_f32::dpt_head_bwd(dlogits, w, pooled, dx, dw, db, B, HW, C, K, stream);
+        default: return dpt_lp_bf16::dpt_head_bwd(dlogits, w, pooled, dx, dw, db, B, HW, C, K, stream);
+    }
 }
 
 extern "C" int dpt_cross_entropy(const float* logits, const long long* target, float* loss, float* dlogits, const float* loss_scale, double* metrics, int B, int K, void* stream) {
-    return dpt::lowp_is_f16() ? dpt_lp_f16::dpt_cross_entropy(logits, target, loss, dlogits, loss_scale, metrics, B, K, stream)
-                               : dpt_lp_bf16::dpt_cross_entropy(logits, target, loss, dlogits, loss_scale, metrics, B, K, stream);
+    switch (dpt::lowp_dtype_flag()) {
+        case 1: return dpt_lp_f16::dpt_cross_entropy(logits, target, loss, dlogits, loss_scale, metrics, B, K, stream);
+        case 2: return dpt_lp_f32::dpt_cross_entropy(logits, target, loss, dlogits, loss_scale, metrics, B, K, stream);
+        default: return dpt_lp_bf16::dpt_cross_entropy(logits, target, loss, dlogits, loss_scale, metrics, B, K, stream);
+    }
 }
 
 extern "C" int dpt_im2col_nchw_f32(const float* x, void* out, int N, int C, int H, int W, int R, int S, int stride, int pad, int ldk, void* stream) {
-    return dpt::lowp_is_f16() ? dpt_lp_f16::dpt_im2col_nchw_f32(x, out, N, C, H, W, R, S, stride, pad, ldk, stream)
-                               : dpt_lp_bf16::dpt_im2col_nchw_f32(x, out, N, C, H, W, R, S, stride, pad, ldk, stream);
+    switch (dpt::lowp_dtype_flag()) {
+        case 1: return dpt_lp_f16::dpt_im2col_nchw_f32(x, out, N, C, H, W, R, S, stride, pad, ldk, stream);
+        case 2: return dpt_lp_f32::dpt_im2col_nchw_f32(x, out, N, C, H, W, R, S, stride, pad, ldk, stream);
+        default: return dpt_lp_bf16::dpt_im2col_nchw_f32(x, out, N, C, H, W, R, S, stride, pad, ldk, stream);
+    }
 }
 
 extern "C" int dpt_pad_rows_f32_to_bf16(const float* src, void* dst, int rows, int cols, int ld, void* stream) {
-    return dpt::lowp_is_f16() ? dpt_lp_f16::dpt_pad_rows_f32_to_bf16(src, dst, rows, cols, ld, stream)
-                               : dpt_lp_bf16::dpt_pad_rows_f32_to_bf16(src, dst, rows, cols, ld, stream);
+    switch (dpt::lowp_dtype_flag()) {
+        case 1: return dpt_lp_f16::dpt_pad_rows_f32_to_bf16(src, dst, rows, cols, ld, stream);
+        case 2: return dpt_lp_f32::dpt_pad_rows_f32_to_bf16(src, dst, rows, cols, ld, stream);
+        default: return dpt_lp_bf16::dpt_pad_rows_f32_to_bf16(src, dst, rows, cols, ld, stream);
+    }
 }
 
 extern "C" int dpt_nchw_f32_to_nhwc_bf16(const float* x, void* y, int N, int C, int H, int W, void* stream) {
-    return dpt::lowp_is_f16() ? dpt_lp_f16::dpt_nchw_f32_to_nhwc_bf16(x, y, N, C, H, W, stream)
-                               : dpt_lp_bf16::dpt_nchw_f32_to_nhwc_bf16(x, y, N, C, H, W, stream);
+    switch (dpt::lowp_dtype_flag()) {
+        case 1: return dpt_lp_f16::dpt_nchw_f32_to_nhwc_bf16(x, y, N, C, H, W, stream);
+        case 2: return dpt_lp_f32::dpt_nchw_f32_to_nhwc_bf16(x, y, N, C, H, W, stream);
+        default: return dpt_lp_bf16::dpt_nchw_f32_to_nhwc_bf16(x, y, N, C, H, W, stream);
+    }
 }
 
 extern "C" int dpt_bn_fwd_train_noalloc(const void* x, const float* gamma, const float* beta, const void* residual, void* y, float* save_mean, float* save_invstd, float* running_mean, float* running_var, long long* num_batches_tracked, long long M, int C, float momentum, float eps, int relu, void* stream) {
@@ -154,6 +216,9 @@ extern "C" int dpt_bn_fwd_train_noalloc(const void* x, const float* gamma, const
 }
 
 extern "C" int dpt_augment_crop_flip_norm(const void* in_u8, const int* params, float* out, int N, int C, int S, int pad, const float* mean3, const float* std3, void* stream) {
-    return dpt::lowp_is_f16() ? dpt_lp_f16::dpt_augment_crop_flip_norm(in_u8, params, out, N, C, S, pad, mean3, std3, stream)
-                               : dpt_lp_bf16::dpt_augment_crop_flip_norm(in_u8, params, out, N, C, S, pad, mean3, std3, stream);
+    switch (dpt::lowp_dtype_flag()) {
+        case 1: return dpt_lp_f16::dpt_augment_crop_flip_norm(in_u8, params, out, N, C, S, pad, mean3, std3, stream);
+        case 2: return dpt_lp_f32::dpt_augment_crop_flip_norm(in_u8, params, out, N, C, S, pad, mean3, std3, stream);
+        default: return dpt_lp_bf16::dpt_augment_crop_flip_norm(in_u8, params, out, N, C, S, pad, mean3, std3, stream);
+    }
 }

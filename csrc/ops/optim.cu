@@ -253,7 +253,7 @@ extern "C" int dpt_cast_f32_to_bf16(const float* src, void* dst, long long n, vo
 // The next kernel launched through this library follows a cross-stream event wait: launch it
 // without the programmatic-dependent-launch attribute (see csrc/common/ptx.cuh).
 extern "C" int dpt_optim_set_lowp_dtype(int is_f16) {
-    dpt::g_shadow_f16 = is_f16 ? 1 : 0;
+    dpt::g_shadow_f16 = (is_f16 == 1) ? 1 : 0;
     return 0;
 }
 

@@ -50,7 +50,8 @@ class TrainStep:
         self.net.train()
         from .ops import functional as _Fn
         _Fn.set_lowp_dtype(dtype)
-        self.arena.set_shadow_dtype(dtype)
+        if dtype != torch.float32:          # FP32 mode reads the fp32 masters, no shadow retyping
+            self.arena.set_shadow_dtype(dtype)
         self.eng = self.net.engine_for(self.batch_shape, True, dtype)
         self.fused_scaler = False
         if self.scaler is not None:

@@ -146,6 +146,7 @@ class ResNet(nn.Module):
         self.fc = Linear(512 * block.expansion, num_classes)
         self.num_classes = num_classes
         self.native = "auto"      # "auto" | "always" | "never"
+        self.native_fp32 = True   # without autocast: native fp32/TF32 kernels (False -> ATen ops)
         self._engines: dict = {}
         self._grad_sink: Optional[Callable] = None  # set by the DDP wrapper (bucket-ready hook)
         self._last_engine = None
@@ -167,13 +168,18 @@ class ResNet(nn.Module):
             return False
         if self.native == "always":
             return True
-        return (torch.is_autocast_enabled("cuda")
-                and torch.get_autocast_dtype("cuda") in (torch.bfloat16, torch.float16))
+        if torch.is_autocast_enabled("cuda"):
+            return torch.get_autocast_dtype("cuda") in (torch.bfloat16, torch.float16)
+        return self.native_fp32          # no autocast: fp32 activations, TF32 tensor-core math
 
     def _native_dtype(self):
-        if torch.is_autocast_enabled("cuda") and torch.get_autocast_dtype("cuda") == torch.float16:
-            return torch.float16
-        return getattr(self, "native_dtype", torch.bfloat16)
+        if torch.is_autocast_enabled("cuda"):
+            dt = torch.get_autocast_dtype("cuda")
+            if dt in (torch.float16, torch.bfloat16):
+                return dt
+        if self.native == "always":
+            return getattr(self, "native_dtype", torch.bfloat16)
+        return torch.float32
 
     def engine_for(self, shape, training: bool, dtype=None):
         dtype = dtype or self._native_dtype()
@@ -451,6 +457,14 @@ class ResNetEngine:
         p = conv.weight
         arena = getattr(p, "_dpt_arena", None)
         Cout, Cin, R, S = p.shape
+        if self.dtype == torch.float32:
+            # FP32 mode: the tensor cores read the fp32 masters directly (as TF32), no shadow copy
+            if arena is not None:
+                return arena.flat_param_view(p).view(Cout, R, S, Cin)
+            w = p.detach()
+            if w.dim() == 4 and not w.is_contiguous():
+                return w.permute(0, 2, 3, 1)          # channels_last storage is already KRSC
+            return w.permute(0, 2, 3, 1).contiguous() if (R > 1 or S > 1) else w.view(Cout, R, S, Cin)
         if arena is not None and arena.shadow is not None:
             if arena.shadow.dtype != self.dtype:
                 arena.set_shadow_dtype(self.dtype)

@@ -118,7 +118,7 @@ def call(name: str, *args) -> None:
 
 def set_lowp_dtype(dtype) -> None:
     """16-bit element type used by every kernel launched afterwards (bf16 or fp16)."""
-    lib().dpt_set_lowp_dtype(1 if dtype == torch.float16 else 0)
+    lib().dpt_set_lowp_dtype({torch.float16: 1, torch.float32: 2}.get(dtype, 0))
 
 
 def pdl_skip_next() -> None:

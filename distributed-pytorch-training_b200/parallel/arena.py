@@ -106,7 +106,7 @@ class ParamArena:
 
     def set_shadow_dtype(self, dtype) -> None:
         """Re-type the 16-bit shadow arena (bf16 <-> fp16) and refill it from the fp32 masters."""
-        if self.shadow is None or self.shadow.dtype == dtype:
+        if self.shadow is None or self.shadow.dtype == dtype or dtype == torch.float32:
             return
         self.shadow = self.shadow.view(dtype)
         self.refresh_shadow()

@@ -66,12 +66,13 @@ def main(argv=None):
             print(f"Resumed from {args.resume} at epoch {start_epoch}")
 
     train_step = None
-    native_ok = device.type == "cuda" and args.amp
+    native_ok = device.type == "cuda"
     if args.cuda_graph and native_ok and getattr(optimizer, "_flat", False):
         from .graph_step import TrainStep
         shape = (args.batch_size, 3, args.image_size, args.image_size)
+        step_dtype = torch.float32 if not args.amp else (torch.float16 if fp16 else torch.bfloat16)
         train_step = TrainStep(model, optimizer, scaler, batch_shape=shape, cuda_graph=True,
-                               dtype=torch.float16 if fp16 else torch.bfloat16)
+                               dtype=step_dtype)
     profiler = GradSyncProfiler(ddp) if args.profile_sync else None
 
     csv = M.MetricsCSV(args.output_dir, enabled=(rank == 0))
