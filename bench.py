@@ -361,8 +361,9 @@ def run_reference(a):
     model = ref.maybe_wrap_ddp(model, device, local)  # torch DDP + NCCL when world > 1
     criterion = nn.CrossEntropyLoss().to(device)
     optimizer = optim.SGD(model.parameters(), lr=0.1, momentum=0.9, weight_decay=5e-4)
-    scaler = torch.cuda.amp.GradScaler(enabled=True)  # --amp path (fp16 autocast + GradScaler)
-    args = types.SimpleNamespace(amp=True, print_freq=10 ** 9)
+    ref_amp = a.amp_dtype != "fp32"                   # --amp-dtype fp32 = the reference's FP32 branch
+    scaler = torch.cuda.amp.GradScaler(enabled=ref_amp)  # --amp path (fp16 autocast + GradScaler)
+    args = types.SimpleNamespace(amp=ref_amp, print_freq=10 ** 9)
     shape = (a.batch_size, 3, a.image_size, a.image_size)
     batches = make_host_batches(8, shape, a.num_classes, seed=1234 + rank)
 
@@ -401,7 +402,9 @@ def run_reference(a):
         "metric": "samples/sec (device-timed, max over ranks)", "value": val, "unit": "samples/s",
         "n_gpus": world, "steps": a.steps, "warmup": W, "ms_per_step": ms / a.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "fp16 autocast + GradScaler (the reference's --amp path)", "data": "synthetic",
+        "dtype": "fp16 autocast + GradScaler (the reference's --amp path)" if ref_amp
+                 else "fp32 (TF32 cuDNN convolutions; the reference's non-AMP branch)",
+        "data": "synthetic",
         "impl": "reference",
         "config": {"model": f"torchvision {a.arch}(num_classes={a.num_classes})", "global_batch": gb,
                    "per_gpu_batch": a.batch_size, "seq_len": None, "parallelism": f"dp{world}",
