@@ -145,10 +145,15 @@ class TrainStep:
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
         before = _lib.LAUNCHES
+        red = getattr(self.ddp, "reducer", None) if self.ddp is not None else None
+        red_before = red.launches() if (red is not None and hasattr(red, "launches")) else 0
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g, capture_error_mode="thread_local"):
             self._body()
-        self.launches_per_step = _lib.LAUNCHES - before + 2  # + the two memsets
+        # kernels of this library in one step: Python-launched ones + the reducer's bucket
+        # all-reduces (launched from C++) + the memset kernels of the step
+        red_n = (red.launches() - red_before) if (red is not None and hasattr(red, "launches")) else 0
+        self.launches_per_step = _lib.LAUNCHES - before + red_n + 2
         self.graph = g
         self._restore(snap)
         torch.cuda.synchronize()

@@ -10,6 +10,15 @@ if ROOT not in sys.path:
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: test needs a CUDA device (run on the B200 box)")
+    # the native artefacts are git-ignored: build them when a fresh checkout runs the tests
+    native = os.path.join(ROOT, "distributed-pytorch-training_b200", "_native")
+    if not (os.path.exists(os.path.join(native, "libdptb200.so"))
+            and os.path.exists(os.path.join(native, "_dptb200_C.so"))):
+        try:
+            import build_native
+            build_native.build_all(verbose=True)
+        except Exception as e:  # noqa: BLE001
+            print(f"[conftest] native build failed: {e}")
 
 
 def pytest_collection_modifyitems(config, items):
