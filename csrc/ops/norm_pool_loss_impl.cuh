@@ -730,6 +730,7 @@ ce_fwd_bwd_kernel(const float* __restrict__ logits, const long long* __restrict_
     const float scale = (loss_scale != nullptr ? *loss_scale : 1.f) / B;
     float wl = 0.f;
     int wc = 0;
+#pragma unroll 4
     for (int n = warp; n < B; n += nw) {
         const float* z = logits + static_cast<long long>(n) * K;
         float mx = -INFINITY;
@@ -1070,13 +1071,19 @@ inline int dpt_head_fwd(const void* x, const float* w, const float* b, float* po
 inline int dpt_head_bwd(const float* dlogits, const float* w, const float* pooled, void* dx,
                             float* dw, float* db, int B, int HW, int C, int K, void* stream) {
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    if (dx != nullptr)
+    // dx == NULL or dw == NULL skips that half (the two kernels are independent, so callers may
+    // issue them on different streams)
+    if (dx != nullptr) {
         ew_pdl_gate();
-    launch_pdl(head_bwd_dx_kernel, dim3(B), dim3(256), K * sizeof(float), st, 
-            dlogits, w, static_cast<lowp*>(dx), HW, C, K);
-    dim3 grid((C + 63) / 64, K);
-    ew_pdl_gate();
-    launch_pdl(head_bwd_dw_kernel, dim3(grid), dim3(64), 0, st, dlogits, pooled, dw, db, B, C, K, 1.f);
+        launch_pdl(head_bwd_dx_kernel, dim3(B), dim3(256), K * sizeof(float), st, dlogits, w,
+                   static_cast<lowp*>(dx), HW, C, K);
+    }
+    if (dw != nullptr) {
+        dim3 grid((C + 63) / 64, K);
+        ew_pdl_gate();
+        launch_pdl(head_bwd_dw_kernel, dim3(grid), dim3(64), 0, st, dlogits, pooled, dw, db, B, C, K,
+                   1.f);
+    }
     DPT_CHECK_LAUNCH();
 }
 

@@ -68,8 +68,55 @@ class TrainStep:
         self.steps = 0
         self.graph = None
         self.launches_per_step = 0
+        self._setup_chunked_sgd()
         if cuda_graph and dev.type == "cuda":
             self._capture(warmup)
+
+    # ------------------------------------------------------------------ chunked optimizer
+    def _setup_chunked_sgd(self) -> None:
+        """Single-GPU counterpart of the fused-SGD all-reduce: the SGD update of a chunk of the
+        arena is launched on the engine's side stream as soon as the last weight gradient of
+        that chunk has been produced, so the 246 MB optimizer sweep overlaps the rest of backward
+        instead of trailing it.  Only without a scaler (skip-step needs the global found_inf)."""
+        from .optim import SGD
+        from .parallel.bucket import plan_arena_buckets
+        self._chunks = None
+        if self.ddp is not None or self.scaler is not None or not isinstance(self.optimizer, SGD):
+            return
+        if self.device.type != "cuda" or getattr(self.net, "_grad_sink", None) is not None:
+            return
+        g0 = self.optimizer.param_groups[0]
+        if g0["momentum"] == 0:
+            return
+        plans = plan_arena_buckets(self.arena, 4 << 20, 1 << 20)
+        index = {id(p): i for i, p in enumerate(self.arena.order)}
+        owner = {}
+        for b, pl in enumerate(plans):
+            for i in pl["params"]:
+                owner[i] = b
+        self._chunks = {"plans": plans, "index": index, "owner": owner, "pending": [0] * len(plans)}
+        self.net._grad_sink = self._chunk_sink
+
+    def _chunk_reset(self) -> None:
+        c = self._chunks
+        c["pending"] = [len(pl["params"]) for pl in c["plans"]]
+
+    def _chunk_sink(self, params) -> None:
+        from .ops import _lib
+        c = self._chunks
+        g0 = self.optimizer.param_groups[0]
+        for p in params:
+            b = c["owner"][c["index"][id(p)]]
+            c["pending"][b] -= 1
+            if c["pending"][b] == 0:
+                pl = c["plans"][b]
+                lo, hi = pl["offset"], pl["offset"] + pl["numel"]
+                a = self.arena
+                shadow = a.shadow[lo:hi] if (a.shadow is not None and self.dtype != torch.float32) else None
+                _lib.pdl_skip_next()      # reads gradients accumulated with REDs by wgrad kernels
+                self.Fn.sgd_flat(a.param[lo:hi], a.grad[lo:hi], self.optimizer._flat_momentum()[lo:hi],
+                                 shadow, g0["lr"], g0["momentum"], g0["dampening"], g0["weight_decay"],
+                                 g0["nesterov"])
 
     # ------------------------------------------------------------------ the step
     def _body(self) -> None:
@@ -80,6 +127,8 @@ class TrainStep:
             ddp.sync_buffers(lazy=self.lazy_buffer_sync)
             ddp.prepare_for_backward()
         self.arena.grad.zero_()
+        if self._chunks is not None:
+            self._chunk_reset()
         logits = self.eng.forward(self.x)
         Fn.cross_entropy(logits, self.t, loss=self.loss, dlogits=self.dlogits,
                          loss_scale=self.scaler.scale_tensor if self.scaler is not None else None,
@@ -90,7 +139,9 @@ class TrainStep:
         from .ops import _lib
         _lib.pdl_skip_next()          # the optimizer kernel follows cross-stream joins
         sc = self.scaler
-        if sc is None:
+        if self._chunks is not None:
+            pass                          # every chunk was updated on the side stream already
+        elif sc is None:
             self.optimizer.step()
         else:
             if not self.fused_scaler:

@@ -198,14 +198,17 @@ def head_fwd(x, w, b, *, pooled=None, logits=None):
     return logits, pooled
 
 
-def head_bwd(dlogits, w, pooled, x_shape, dw, db, *, dx=None, dtype=BF16):
+def head_bwd(dlogits, w, pooled, x_shape, dw, db, *, dx=None, dtype=BF16, part="both"):
+    """part: "both" | "dx" (input gradient only) | "dw" (weight / bias gradients only) — the two
+    kernels are independent, so an engine can put the weight gradient on its side stream."""
     N, H, W, C_ = x_shape
     K = w.shape[0]
-    if dx is None:
+    if dx is None and part != "dw":
         dx = torch.empty(x_shape, device=dlogits.device, dtype=dtype)
-    call("dpt_head_bwd", ptr(dlogits), ptr(w), ptr(pooled), ptr(dx), ptr(dw), ptr(db), N, H * W, C_,
-         K, stream())
-    count(2)
+    call("dpt_head_bwd", ptr(dlogits), ptr(w), ptr(pooled), ptr(dx) if part != "dw" else None,
+         ptr(dw) if part != "dx" else None, ptr(db) if part != "dx" else None, N, H * W, C_, K,
+         stream())
+    count(2 if part == "both" else 1)
     return dx
 
 
