@@ -351,10 +351,16 @@ class ResNetEngine:
         # weight-gradient kernels are off the critical path (nothing in backward consumes
         # them): they run on a second stream, concurrently with the dgrad / BN-backward chain
         self.side = torch.cuda.Stream(device=self.dev) if training else None
+        # the 1x1 downsample branch (forward conv+BN, backward BN) is independent of the main
+        # branch of its block: it runs on a third stream and joins where its result is consumed
+        self.side2 = torch.cuda.Stream(device=self.dev) if training else None
+        self._ev2 = [torch.cuda.Event() for _ in range(32)] if training else []
+        self._ev2_i = 0
         self._ev_pool = [torch.cuda.Event() for _ in range(64)] if training else []
         self._ev_i = 0
         import os
         self._fuse_bn_bwd = os.environ.get("DPT_FUSE_BN_BWD", "0") == "1"
+        self._branch_streams = os.environ.get("DPT_BRANCH_STREAMS", "1") == "1"
         self._z32_ev = torch.cuda.Event() if training else None
         self._z32_pending = False
 
@@ -492,9 +498,18 @@ class ResNetEngine:
         return g.view(-1)
 
     # ------------------------------------------------------------------ forward
-    def _fwd_unit(self, u: _Unit, x, residual=None):
+    def _ev2_next(self):
+        ev = self._ev2[self._ev2_i % len(self._ev2)]
+        self._ev2_i += 1
+        return ev
+
+    def _fwd_unit(self, u: _Unit, x, residual=None, residual_event=None):
         Fn = self.Fn
         conv, bn = u.conv, u.bn
+        if residual_event is not None:
+            # the residual comes from the downsample branch on side2: run our conv first, then
+            # join right before the BN kernel that consumes it
+            return self._fwd_unit_join(u, x, residual, residual_event)
         if self.training and u.fsplit > 1:
             # tiny tile grid: split-K over CTAs into an fp32 accumulator, then one column-strip
             # kernel does statistics + normalisation (+residual, +ReLU)
@@ -516,6 +531,30 @@ class ResNetEngine:
             Fn.conv_fprop(x, self._w(conv), conv.stride, conv.padding, out=u.raw)
             Fn.bn_fwd_eval(u.raw, bn.weight, bn.bias, bn.running_mean, bn.running_var,
                            residual=residual, relu=u.relu, out=u.y, eps=bn.eps)
+        return u.y
+
+    def _fwd_unit_join(self, u: _Unit, x, residual, ev):
+        Fn = self.Fn
+        conv, bn = u.conv, u.bn
+        split = u.fsplit > 1
+        if split:
+            Fn.conv_fprop(x, self._w(conv), conv.stride, conv.padding, out=u.raw32, splits=u.fsplit)
+        else:
+            Fn.conv_fprop(x, self._w(conv), conv.stride, conv.padding, out=u.raw, stats=(u.sum, u.sq))
+        torch.cuda.current_stream().wait_event(ev)
+        self._lib.pdl_skip_next()
+        if split:
+            Fn.bn_fwd_train_small_f32(u.raw32, bn.weight, bn.bias, residual=residual, relu=u.relu,
+                                      out=u.y, x_bf16=u.raw, save_mean=u.mean, save_invstd=u.invstd,
+                                      running_mean=bn.running_mean, running_var=bn.running_var,
+                                      num_batches_tracked=bn.num_batches_tracked,
+                                      momentum=bn.momentum, eps=bn.eps)
+        else:
+            Fn.bn_fwd_train(u.raw, u.sum, u.sq, bn.weight, bn.bias, residual=residual, relu=u.relu,
+                            out=u.y, save_mean=u.mean, save_invstd=u.invstd,
+                            running_mean=bn.running_mean, running_var=bn.running_var,
+                            num_batches_tracked=bn.num_batches_tracked, momentum=bn.momentum,
+                            eps=bn.eps)
         return u.y
 
     def forward(self, x_nchw: torch.Tensor) -> torch.Tensor:
@@ -562,11 +601,25 @@ class ResNetEngine:
                 torch.cuda.current_stream().wait_event(self._z32_ev)
                 self._lib.pdl_skip_next()
                 self._z32_pending = False
-            idn = x if b["ds"] is None else self._fwd_unit(b["ds"], x)
+            ds_ev = None
+            if b["ds"] is None:
+                idn = x
+            elif self.training and self._branch_streams:
+                # downsample branch on side2, concurrently with the main branch
+                ev = self._ev2_next()
+                ev.record(torch.cuda.current_stream())
+                self.side2.wait_event(ev)
+                self._lib.pdl_skip_next()
+                with torch.cuda.stream(self.side2):
+                    idn = self._fwd_unit(b["ds"], x)
+                    ds_ev = self._ev2_next()
+                    ds_ev.record(self.side2)
+            else:
+                idn = self._fwd_unit(b["ds"], x)
             h = x
             for u in b["units"][:-1]:
                 h = self._fwd_unit(u, h)
-            x = self._fwd_unit(b["units"][-1], h, residual=idn)
+            x = self._fwd_unit(b["units"][-1], h, residual=idn, residual_event=ds_ev)
         # ---- head -----------------------------------------------------------------------
         Fn.head_fwd(x, m.fc.weight, m.fc.bias, pooled=self.pooled, logits=self.logits)
         return self.logits
@@ -636,6 +689,16 @@ class ResNetEngine:
         # block output: sum the incoming pair, apply the output-ReLU mask, BN backward
         self._bn_bwd(units[-1], dy, dy2)
         g_skip = units[-1].g                       # gradient flowing into the identity branch
+        if ds is not None and self._branch_streams:
+            ev = self._ev2_next()
+            ev.record(torch.cuda.current_stream())
+            self.side2.wait_event(ev)
+            self._lib.pdl_skip_next()
+            with torch.cuda.stream(self.side2):
+                self._bn_bwd(ds, g_skip)
+                dev_ = self._ev2_next()
+                dev_.record(self.side2)
+            b["_ds_bwd_ev"] = dev_
         for i in range(k - 1, 0, -1):
             u, prev = units[i], units[i - 1]
             d_in = self._dgrad(u, prev.y_shape, b["d_mid"][i - 1])
@@ -646,7 +709,15 @@ class ResNetEngine:
             self._dgrad(u1, b["x_shape"], b["dx"])
             self._wgrad(u1, b["x"])
             return b["dx"], g_skip
-        self._bn_bwd(ds, g_skip)
+        ds_ev = None
+        if self._branch_streams:
+            # g_skip exists since the block-output BN backward; the downsample BN backward does
+            # not depend on the main branch, so it ran on side2 (issued below, before the chain)
+            ds_ev = b.get("_ds_bwd_ev")
+            torch.cuda.current_stream().wait_event(ds_ev)
+            self._lib.pdl_skip_next()
+        else:
+            self._bn_bwd(ds, g_skip)
         if self._can_fuse_dgrad(u1, ds):
             # conv1 and the 1x1 downsample read the same block input: one fused dgrad kernel
             self._dgrad(u1, b["x_shape"], b["dx"], ds)
