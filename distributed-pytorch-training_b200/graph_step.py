@@ -65,6 +65,18 @@ class TrainStep:
             if dev.type == "cuda" else torch.zeros(self._ring)
         self._events = [None] * self._ring
         self._slot = 0
+        # host->device staging on a copy stream: the next batch's H2D overlaps the current
+        # step's compute (the call returns without waiting, so the caller is already copying
+        # batch t+1 while step t runs)
+        if dev.type == "cuda":
+            self.copy_stream = torch.cuda.Stream(device=dev)
+            self.x_stage = torch.zeros_like(self.x)
+            self.t_stage = torch.zeros_like(self.t)
+            self._stage_ready = torch.cuda.Event()
+            self._stage_free = torch.cuda.Event()
+            self._stage_free.record()
+        else:
+            self.copy_stream = None
         self.steps = 0
         self.graph = None
         self.launches_per_step = 0
@@ -215,8 +227,21 @@ class TrainStep:
     def __call__(self, images: torch.Tensor, targets: torch.Tensor) -> torch.Tensor:
         """Runs one optimisation step on a (host-pinned or device) batch; returns the device
         loss scalar (valid until the next call).  Never blocks the host."""
-        self.x.copy_(images, non_blocking=True)
-        self.t.copy_(targets, non_blocking=True)
+        if self.copy_stream is not None and not images.is_cuda:
+            cs = self.copy_stream
+            cs.wait_event(self._stage_free)            # the previous step has consumed the stage
+            with torch.cuda.stream(cs):
+                self.x_stage.copy_(images, non_blocking=True)
+                self.t_stage.copy_(targets, non_blocking=True)
+                self._stage_ready.record(cs)
+            main = torch.cuda.current_stream()
+            main.wait_event(self._stage_ready)
+            self.x.copy_(self.x_stage, non_blocking=True)
+            self.t.copy_(self.t_stage, non_blocking=True)
+            self._stage_free.record(main)
+        else:
+            self.x.copy_(images, non_blocking=True)
+            self.t.copy_(targets, non_blocking=True)
         if self.graph is not None:
             self.graph.replay()
         else:

@@ -20,6 +20,7 @@ Two execution paths share the parameters:
 from __future__ import annotations
 
 import math
+import os
 from typing import Callable, Optional
 
 import torch
