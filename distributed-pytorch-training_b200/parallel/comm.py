@@ -138,6 +138,50 @@ class Communicator:
         self.launches += 1
         _lib.count()
 
+    def autotune(self, buf, sizes=(1 << 18, 1 << 20, 1 << 22, 1 << 24), iters: int = 20,
+                 ctas: int = 0) -> dict:
+        """Init-time micro-benchmark: times the two-shot and, when ``buf`` is a
+        multicast buffer, the NVLS all-reduce on ``buf`` for a few message sizes (CUDA events,
+        max over ranks) and returns {"table": {bytes: {"twoshot_us", "nvls_us"}},
+        "nvls_min_bytes": smallest size from which NVLS is the faster kernel (None if never)}.
+        The buffer content is overwritten and zeroed again afterwards."""
+        has_nvls = hasattr(buf, "mc_ptr")
+        table = {}
+        for nbytes in sizes:
+            nbytes = min(int(nbytes), buf.nbytes) // 16 * 16
+            n = nbytes // 4
+            row = {}
+            for name in (("twoshot", "nvls") if has_nvls else ("twoshot",)):
+                fn = (lambda: self.allreduce_(buf, 0, n, ctas=ctas)) if name == "twoshot" else \
+                    (lambda: self.allreduce_nvls_(buf, 0, n, ctas=ctas))
+                for _ in range(3):
+                    fn()
+                torch.cuda.synchronize()
+                self.host_barrier()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for _ in range(iters):
+                    fn()
+                e1.record()
+                torch.cuda.synchronize()
+                t = torch.tensor([e0.elapsed_time(e1) / iters * 1e3], device=self.device)
+                if self.world > 1:
+                    dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+                row[name + "_us"] = float(t.item())
+            table[nbytes] = row
+        nvls_min = None
+        if has_nvls:
+            for nbytes in sorted(table, reverse=True):
+                if table[nbytes]["nvls_us"] < table[nbytes]["twoshot_us"]:
+                    nvls_min = nbytes
+                else:
+                    break
+        buf.local.zero_()
+        torch.cuda.synchronize()
+        self.host_barrier()
+        self.check_health()
+        return {"table": table, "nvls_min_bytes": nvls_min}
+
     def host_barrier(self) -> None:
         if self.world > 1:
             dist.barrier(group=self.group)

@@ -204,7 +204,7 @@ class DistributedDataParallel(nn.Module):
         # auto: NVLS only pays off when the in-switch reduction saves link traffic (2(N-1)/N*S vs
         # S per GPU): measured slower than two-shot at N=2, so it is considered from N >= 4
         want_nvls = backend == "native" and self.world_size > 1 and (
-            allreduce_algo == "nvls" or (allreduce_algo == "auto" and self.world_size >= 4))
+            allreduce_algo in ("nvls", "autotune") or (allreduce_algo == "auto" and self.world_size >= 4))
         self.arena = ParamArena(params, self.device, comm=self.comm if backend == "native" else None,
                                 multicast=want_nvls)
         self.nvls = want_nvls and hasattr(self.arena.grad_buf, "mc_ptr")
@@ -226,6 +226,16 @@ class DistributedDataParallel(nn.Module):
             self.reducer = E.Reducer(specs, len(self.arena.order), self.comm.handle.value or 0,
                                      self.world_size, list(self.arena.grad_buf.peer_ptrs), found, 0,
                                      comm_ctas, bool(profile))
+            self.autotune_result = None
+            if allreduce_algo == "autotune" and self.world_size > 1:
+                # pick the NVLS / two-shot crossover from bus bandwidth measured right now
+                self.autotune_result = self.comm.autotune(self.arena.grad_buf, ctas=comm_ctas)
+                thr = self.autotune_result["nvls_min_bytes"]
+                if thr is None:
+                    self.nvls = False
+                else:
+                    nvls_min_bytes = thr
+                self._logging["autotune"] = str(self.autotune_result["table"])
             if self.nvls:
                 # measured crossover: the multimem kernel wins from ~1 MB up (profiles/README.md)
                 self.reducer.set_nvls(self.arena.grad_buf.mc_ptr,

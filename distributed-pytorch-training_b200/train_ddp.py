@@ -43,7 +43,8 @@ def main(argv=None):
     if args.profile_sync and args.cuda_graph and rank == 0:
         print("[grad-sync] --cuda-graph: per-bucket timing disabled (run without --cuda-graph "
               "to profile gradient sync)")
-    algo = {"auto": "auto", "oneshot": "twoshot", "twoshot": "twoshot", "nvls": "nvls"}[args.allreduce_algo]
+    algo = {"auto": "auto", "autotune": "autotune", "oneshot": "twoshot", "twoshot": "twoshot",
+            "nvls": "nvls"}[args.allreduce_algo]
     model = maybe_wrap_ddp(model, device, local_rank, backend=args.backend,
                            bucket_cap_mb=args.bucket_cap_mb if args.bucket_cap_mb != 25.0 else None,
                            profile=bucket_profile, comm_timeout=args.comm_timeout,

@@ -129,6 +129,28 @@ def _run(worker, world=2):
         assert msg == "ok", f"rank {rank}:\n{msg}"
 
 
+def _mismatch_worker(rank, world, port, q):
+    try:
+        _init(rank, world, port)
+        from dpt_b200.parallel.ddp import DistributedDataParallel as OurDDP
+        net = torch.nn.Linear(8, 16 + rank)          # different shapes on different ranks
+        try:
+            OurDDP(net, backend="gloo")
+            q.put((rank, "constructor accepted mismatching replicas"))
+        except RuntimeError as e:
+            q.put((rank, "ok" if "same model across all ranks" in str(e) else str(e)))
+    except Exception:  # noqa: BLE001
+        import traceback
+        q.put((rank, traceback.format_exc()))
+    finally:
+        if dist.is_initialized():
+            dist.destroy_process_group()
+
+
+def test_parameter_shape_verification_across_ranks():
+    _run(_mismatch_worker)
+
+
 def test_ddp_wrapper_matches_torch_ddp_gloo():
     _run(_ddp_parity_worker)
 

@@ -369,6 +369,13 @@ def _nvls_worker(rank, world):
             dist.all_reduce(lo, op=dist.ReduceOp.MIN)
             dist.all_reduce(hi, op=dist.ReduceOp.MAX)
             assert torch.equal(lo, hi), n
+    # init-time autotune: measured table + crossover, identical on every rank
+    res = comm.autotune(buf, sizes=(1 << 16, 1 << 20, 1 << 22), iters=5)
+    assert set(res["table"]) == {1 << 16, 1 << 20, 1 << 22}
+    assert all(r["twoshot_us"] > 0 and r["nvls_us"] > 0 for r in res["table"].values())
+    gathered = [None] * world
+    dist.all_gather_object(gathered, res["nvls_min_bytes"])
+    assert all(g == gathered[0] for g in gathered)
     # the same buffer also works with the P2P kernels (unicast peer mappings)
     n = 65536
     view = buf.view(torch.float32, 0, n)
