@@ -7,10 +7,12 @@ at N GPUs of one node (BASELINE.json config 2).
 
 For N > 1 launch with torchrun (RANK / LOCAL_RANK / WORLD_SIZE / MASTER_* from the env).
 Rank 0 prints ONE JSON line.  Timing: W >= 3 warm-up steps, then exactly K steps bracketed by
-barrier + cuda synchronize, device-timed with CUDA events, max over ranks; L2 is flushed between
-timed steps (untimed 256 MiB memset); SM clocks / throttle reasons are sampled through NVML
-during the timed region.  `e2e` is the same metric through the public API (TrainStep.__call__)
-with every step's inputs copied from pinned host memory and the step's loss read back.
+barrier + cuda synchronize, device-timed with CUDA events, max over ranks.  One step touches
+~207 MB (fp32 params + grads + momentum, 16-bit shadow, activations) > 126 MB of L2, so no
+explicit flush by default (`--l2-flush` adds an untimed 256 MiB memset between steps); SM clocks /
+throttle reasons are sampled through NVML during the timed region.  `e2e` is the same metric
+through the public API (TrainStep.__call__) with every step's inputs copied from pinned host
+memory and the step's loss read back.
 """
 from __future__ import annotations
 
