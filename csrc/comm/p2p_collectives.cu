@@ -454,6 +454,20 @@ extern "C" int dpt_comm_destroy(dpt_comm* c) {
 // 0 = healthy; otherwise bit31 set, bits 24..30 = peer that never arrived, low 24 bits = epoch.
 extern "C" unsigned dpt_comm_error(const dpt_comm* c) { return c ? *c->err_host : 0u; }
 
+// Debug aid: copies the per-CTA barrier epoch counters (up to kMaxCommCtas words) to host memory
+// after synchronising the device.  Every rank launches the same collectives with the same CTA
+// counts, so after a completed step the counters must be identical on all ranks; a difference
+// means a rank skipped or repeated a collective.  Returns the number of words written.
+extern "C" int dpt_comm_epochs(const dpt_comm* c, unsigned* out, int n) {
+    if (c == nullptr || out == nullptr || n <= 0) return DPT_ERR_ARG;
+    if (n > kMaxCommCtas) n = kMaxCommCtas;
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) return -static_cast<int>(e) - 100;
+    e = cudaMemcpy(out, c->ctx.epoch, sizeof(uint32_t) * n, cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) return -static_cast<int>(e) - 100;
+    return n;
+}
+
 static int clamp_ctas(int ctas, long long n4, int world) {
     if (ctas <= 0) ctas = 32;
     if (ctas > kMaxCommCtas) ctas = kMaxCommCtas;

@@ -51,6 +51,9 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--profile-sync", action="store_true",
                    help="record per-step gradient-sync timing (device events, max over ranks)")
     p.add_argument("--metrics-json", default="", type=str, help="write per-epoch metrics as JSON")
+    p.add_argument("--check-sync-every", default=0, type=int,
+                   help="assert bit-identical parameters on all ranks every N steps (0 = off)")
+    p.add_argument("--nvtx", action="store_true", help="emit NVTX ranges for the step phases")
     p.add_argument("--no-validate", action="store_true", help="skip the validation pass")
     p.add_argument("--comm-timeout", default=30.0, type=float,
                    help="seconds a device-side flag wait may spin before reporting a dead peer")

@@ -80,6 +80,12 @@ class TrainStep:
         self.steps = 0
         self.graph = None
         self.launches_per_step = 0
+        # debug: poison the gradient arena once the optimizer has consumed it, so
+        # anything that reads gradients after their consumption (a late bucket kernel, a stale
+        # view) turns into NaNs instead of silently using old data.  The next step's memset
+        # clears the poison.
+        import os
+        self._poison = os.environ.get("DPT_DEBUG_POISON", "0") == "1"
         self._setup_chunked_sgd()
         if cuda_graph and dev.type == "cuda":
             self._capture(warmup)
@@ -160,6 +166,8 @@ class TrainStep:
                 Fn.amp_unscale(self.arena.grad, sc.inv_scale, sc.found_inf)
             self.optimizer.step(found_inf=sc.found_inf)
             sc.update()
+        if self._poison:
+            self.arena.grad.fill_(float("nan"))
 
     def _snapshot(self):
         snap = {"param": self.arena.param.clone(), "metrics": self.metrics.clone()}

@@ -59,6 +59,7 @@ _SIGS = {
     "dpt_symm_free": [vp],
     "dpt_comm_create": [i32, i32, C.POINTER(vp), f64, C.POINTER(vp)],
     "dpt_comm_destroy": [vp],
+    "dpt_comm_epochs": [vp, vp, i32],
     "dpt_allreduce_fused": [vp, C.POINTER(vp), i64, f32, vp, C.POINTER(vp), C.POINTER(vp),
                             C.POINTER(vp), vp, f32, f32, f32, i32, i32, vp],
     "dpt_allreduce_oneshot": [vp, C.POINTER(vp), vp, i64, f32, vp, C.POINTER(vp), i32, vp],

@@ -242,6 +242,30 @@ class Communicator:
             raise RuntimeError(f"[rank {self.rank}] peer-memory collective timed out waiting for "
                                f"rank {peer} (epoch {code & 0xFFFFFF}); a rank died or stalled")
 
+    def epochs(self) -> list[int]:
+        """Per-CTA barrier epoch counters of this rank (synchronises the device; debug only)."""
+        out = (C.c_uint * 64)()
+        n = int(self.lib.dpt_comm_epochs(self.handle, out, 64))
+        if n < 0:
+            raise RuntimeError(f"dpt_comm_epochs failed ({n})")
+        return [int(out[i]) for i in range(n)]
+
+    def validate_epochs(self) -> list[int]:
+        """Debug check: every rank issues the same collectives with the same CTA
+        counts, so at a quiescent point (after a step, all ranks) the epoch counters must agree.
+        A mismatch means a rank skipped / repeated a collective — the next barrier would either
+        time out or, worse, match a flag from a different collective."""
+        mine = self.epochs()
+        if self.world == 1:
+            return mine
+        everyone = [None] * self.world
+        dist.all_gather_object(everyone, mine, group=self.group)
+        for r, other in enumerate(everyone):
+            if other != everyone[0]:
+                raise RuntimeError(f"[rank {self.rank}] collective epochs differ between rank 0 and "
+                                   f"rank {r}: {everyone[0][:8]}… vs {other[:8]}…")
+        return mine
+
     # ------------------------------------------------------------------ watchdog / heartbeat
     def start_watchdog(self, interval_s: float = 1.0, abort: bool = False, heartbeat: bool = True):
         """Host thread that (a) polls the device-written error word, so a peer that died or

@@ -476,6 +476,41 @@ class DistributedDataParallel(nn.Module):
                 self.module._grad_sink = self._sink
         self.reducer.comm_hook = (state, hook)
 
+    def _set_static_graph(self) -> None:
+        """torch distributed.py:2395.  The bucket plan here is always static (planned once in
+        gradient-ready order), so this only records the flag."""
+        self.static_graph = True
+
+    def _register_fused_optim(self, optimizer, *args, **kwargs) -> bool:
+        """torch distributed.py:2097 (optimizer step overlapped with the all-reduce): here the
+        SGD update runs inside the all-reduce kernel — same as ``enable_fused_sgd``."""
+        return self.enable_fused_sgd(optimizer)
+
+    # ------------------------------------------------------------------ replica consistency
+    def param_checksum(self) -> torch.Tensor:
+        """Bit-exact digest of the fp32 parameter arena: wrap-around int64 sum of the raw 32-bit
+        words and of the words weighted by (index mod 65521), one small reduction kernel each."""
+        words = self.arena.param.view(torch.int32).to(torch.int64)
+        idx = torch.arange(words.numel(), device=words.device, dtype=torch.int64) % 65521
+        return torch.stack([words.sum(), (words * (idx + 1)).sum()])
+
+    def verify_replicas(self, raise_on_mismatch: bool = True) -> bool:
+        """Cross-rank desync check: every rank's parameters must be bit-identical
+        after a step (rank 0's weights are broadcast at wrap time and every rank applies the
+        same reduced gradient).  Compares ``param_checksum()`` of all ranks; cold path, call it
+        every K steps (``--check-sync-every K``)."""
+        if self.world_size == 1:
+            return True
+        mine = self.param_checksum()
+        everyone = [torch.empty_like(mine) for _ in range(self.world_size)]
+        dist.all_gather(everyone, mine, group=self.process_group)
+        sums = [tuple(t.tolist()) for t in everyone]
+        ok = all(s == sums[0] for s in sums)
+        if not ok and raise_on_mismatch:
+            raise RuntimeError(f"[rank {self.rank}] parameter replicas diverged at iteration "
+                               f"{self._iter}: checksums {sums}")
+        return ok
+
     # ------------------------------------------------------------------ introspection
     def bucket_sizes(self):
         return [pl["bytes"] for pl in self.plans]
@@ -522,8 +557,8 @@ class DistributedDataParallel(nn.Module):
 
 
 def maybe_wrap_ddp(model, device, local_rank, **kwargs):
-    kwargs = {k: v for k, v in kwargs.items() if v is not None or k == "bucket_cap_mb"}
     """Reference train_ddp.py:303-311: wrap only when distributed."""
+    kwargs = {k: v for k, v in kwargs.items() if v is not None or k == "bucket_cap_mb"}
     from ..runtime import is_distributed
     if is_distributed() and dist.is_initialized():
         if device.type == "cuda":

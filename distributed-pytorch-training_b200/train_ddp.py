@@ -22,12 +22,15 @@ from .parallel.ddp import DistributedDataParallel, maybe_wrap_ddp
 from .profiler import GradSyncProfiler
 from .runtime import cleanup_distributed, pick_device, set_seed, setup_distributed
 from .trainer import train_one_epoch, validate
+from .utils import nvtx
 
 
 def main(argv=None):
     args = parse_args(argv)
     Path(args.output_dir).mkdir(parents=True, exist_ok=True)
 
+    if args.nvtx:
+        nvtx.enable()
     rank, world_size, local_rank = setup_distributed(args.backend)
     set_seed(args.seed, rank)
     device = pick_device(local_rank)

@@ -16,6 +16,7 @@ import torch.distributed as dist
 
 from . import metrics as M
 from .runtime import is_distributed
+from .utils import nvtx
 
 
 def reduce_tensor(tensor: torch.Tensor, op=None) -> torch.Tensor:
@@ -64,6 +65,7 @@ def train_one_epoch(epoch, model, train_loader, optimizer, criterion, device, ar
     cuda = device.type == "cuda"
     win_events: list = []
     max_steps = getattr(args, "steps", 0) or 0
+    check_every = getattr(args, "check_sync_every", 0) or 0
     n_steps = len(train_loader) if not max_steps else min(max_steps, len(train_loader))
     for i, (images, targets) in enumerate(train_loader):
         if max_steps and i >= max_steps:
@@ -82,27 +84,35 @@ def train_one_epoch(epoch, model, train_loader, optimizer, criterion, device, ar
                 profiler._step += 1
                 profiler._ev0 = None
         if fast:
-            train_step(images, targets)
+            with nvtx.range("train_step(graph)"):
+                train_step(images, targets)
         else:
-            images = images.to(device, non_blocking=True)
-            targets = targets.to(device, non_blocking=True)
+            with nvtx.range("h2d"):
+                images = images.to(device, non_blocking=True)
+                targets = targets.to(device, non_blocking=True)
             optimizer.zero_grad(set_to_none=True)
-            with _autocast(args, device):
+            with nvtx.range("forward"), _autocast(args, device):
                 outputs = model(images)
                 loss = criterion(outputs, targets)
             if use_scaler:
-                scaler.scale(loss).backward()
-                scaler.step(optimizer)
-                scaler.update()
+                with nvtx.range("backward+grad_sync"):
+                    scaler.scale(loss).backward()
+                with nvtx.range("optimizer"):
+                    scaler.step(optimizer)
+                    scaler.update()
             else:
-                loss.backward()
-                optimizer.step()
+                with nvtx.range("backward+grad_sync"):
+                    loss.backward()
+                with nvtx.range("optimizer"):
+                    optimizer.step()
             with torch.no_grad():
                 acc[0] += loss.detach().double() * bsz
                 acc[1] += (outputs.detach().argmax(1) == targets).sum().double()
                 acc[2] += bsz
         if profiler is not None and profiler._ev0 is not None:
             profiler.step_end()
+        if check_every and (i + 1) % check_every == 0 and hasattr(model, "verify_replicas"):
+            model.verify_replicas()
         if cuda:
             ev_e.record()
             win_events.append((ev_s, ev_e))

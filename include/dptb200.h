@@ -151,6 +151,10 @@ size_t dpt_comm_flag_bytes(void);
 int dpt_comm_create(int rank, int world, void* const* flags, double timeout_s, dpt_comm** out);
 int dpt_comm_destroy(dpt_comm* c);
 unsigned dpt_comm_error(const dpt_comm* c);
+/* Debug: device-synchronising copy of the per-CTA barrier epoch counters (<= 64 words) to host
+ * memory; returns the number of words written (negative on error).  Equal on all ranks after a
+ * completed step. */
+int dpt_comm_epochs(const dpt_comm* c, unsigned* out, int n);
 int dpt_allreduce_fused(dpt_comm* c, void* const* bufs, long long n, float scale,
                         const float* inv_scale, void* const* found_inf, void* const* param,
                         void* const* shadow, float* momentum, float lr, float mu, float wd,

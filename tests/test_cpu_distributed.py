@@ -147,6 +147,77 @@ def _mismatch_worker(rank, world, port, q):
             dist.destroy_process_group()
 
 
+def _builtin_hooks_worker(rank, world, port, q):
+    try:
+        _init(rank, world, port)
+        from dpt_b200.parallel import comm_hooks
+        from dpt_b200.parallel.ddp import DistributedDataParallel as OurDDP
+        x = torch.full((2, 8), float(rank + 1))
+        grads = {}
+        for name in ("allreduce_hook", "fp16_compress_hook", "bf16_compress_hook", "noop_hook"):
+            torch.manual_seed(0)
+            net = torch.nn.Sequential(torch.nn.Linear(8, 16), torch.nn.ReLU(), torch.nn.Linear(16, 4))
+            ddp = OurDDP(net, backend="gloo")
+            ddp.register_comm_hook(None, getattr(comm_hooks, name))
+            ddp(x).sum().backward()
+            grads[name] = torch.cat([p.grad.flatten() for p in ddp.parameters()]).clone()
+        ref = grads["allreduce_hook"]
+        both = [torch.empty_like(ref) for _ in range(world)]
+        dist.all_gather(both, ref)
+        assert torch.equal(both[0], both[1]), "all-reduce hook left replicas different"
+        assert torch.allclose(grads["fp16_compress_hook"], ref, rtol=2e-3, atol=1e-3)
+        assert torch.allclose(grads["bf16_compress_hook"], ref, rtol=2e-2, atol=1e-2)
+        local = [torch.empty_like(ref) for _ in range(world)]
+        dist.all_gather(local, grads["noop_hook"])
+        assert not torch.equal(local[0], local[1]), "noop hook must not communicate"
+        assert torch.allclose((local[0] + local[1]) / world, ref, rtol=1e-5, atol=1e-6)
+        q.put((rank, "ok"))
+    except Exception:  # noqa: BLE001
+        import traceback
+        q.put((rank, traceback.format_exc()))
+    finally:
+        if dist.is_initialized():
+            dist.destroy_process_group()
+
+
+def _verify_replicas_worker(rank, world, port, q):
+    try:
+        _init(rank, world, port)
+        from dpt_b200.parallel.ddp import DistributedDataParallel as OurDDP
+        torch.manual_seed(5 + rank)
+        net = torch.nn.Sequential(torch.nn.Linear(8, 16), torch.nn.ReLU(), torch.nn.Linear(16, 4))
+        ddp = OurDDP(net, backend="gloo")
+        assert ddp.verify_replicas()                     # rank 0's weights were broadcast
+        ddp(torch.randn(2, 8)).sum().backward()
+        with torch.no_grad():
+            for p in ddp.parameters():
+                p -= 0.1 * p.grad
+        assert ddp.verify_replicas()                     # same reduced gradient everywhere
+        if rank == 1:
+            with torch.no_grad():
+                next(ddp.parameters()).view(-1)[3] += 1e-7   # one-ulp-scale silent desync
+        assert ddp.verify_replicas(raise_on_mismatch=False) is False
+        try:
+            ddp.verify_replicas()
+            q.put((rank, "desync not reported"))
+        except RuntimeError as e:
+            q.put((rank, "ok" if "diverged" in str(e) else str(e)))
+    except Exception:  # noqa: BLE001
+        import traceback
+        q.put((rank, traceback.format_exc()))
+    finally:
+        if dist.is_initialized():
+            dist.destroy_process_group()
+
+
+def test_builtin_comm_hooks_gloo():
+    _run(_builtin_hooks_worker)
+
+
+def test_verify_replicas_detects_desync():
+    _run(_verify_replicas_worker)
+
+
 def test_parameter_shape_verification_across_ranks():
     _run(_mismatch_worker)
 
@@ -165,7 +236,7 @@ def _entry(outdir):
     from dpt_b200.train_ddp import main
     main(["--synthetic", "--synthetic-size", "32", "--epochs", "1", "--batch-size", "4",
           "--workers", "0", "--print-freq", "2", "--output-dir", outdir, "--backend", "gloo",
-          "--steps", "3", "--save-every", "1"])
+          "--steps", "3", "--save-every", "1", "--check-sync-every", "1", "--nvtx"])
 
 
 def test_entry_point_two_process_gloo(tmp_path):

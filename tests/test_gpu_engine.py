@@ -119,6 +119,31 @@ def test_trainstep_graph_equals_eager_and_learns():
     assert m0[2] == m1[2] == 6 * 32
 
 
+def test_gradient_poisoning_debug_mode_is_harmless(monkeypatch):
+    """DPT_DEBUG_POISON=1 fills the gradient arena with NaN after the optimizer consumed it;
+    a correct step never reads gradients after that point, so training is unaffected."""
+    from dpt_b200.graph_step import TrainStep
+    from dpt_b200.models.resnet import build_model
+    from dpt_b200.optim import SGD
+    monkeypatch.setenv("DPT_DEBUG_POISON", "1")
+    dev = torch.device("cuda")
+    shape = (16, 3, 32, 32)
+    torch.manual_seed(11)
+    model = build_model(dev, "resnet18", 10)
+    opt = SGD(model.parameters(), lr=0.01, momentum=0.9, weight_decay=5e-4)
+    step = TrainStep(model, opt, None, batch_shape=shape, cuda_graph=True)
+    assert step._poison
+    x = torch.randn(shape).pin_memory()
+    t = torch.randint(0, 10, (16,)).pin_memory()
+    losses = []
+    for _ in range(5):
+        step(x, t)
+        losses.append(step.read_loss(lag=0))
+    torch.cuda.synchronize()
+    assert torch.isnan(opt.arena.grad).all()            # poisoned after consumption
+    assert torch.isfinite(opt.arena.param).all() and losses[-1] < losses[0], losses
+
+
 def test_compat_loop_with_scaler_and_autocast():
     """Reference-style loop (autocast + GradScaler API) drives the native engine."""
     from dpt_b200.amp import GradScaler

@@ -275,6 +275,9 @@ def _trainstep_worker(rank, world):
         torch.cuda.synchronize()
         model.comm.check_health()
         assert losses[-1] < losses[0], (graph, fused, algo, losses)
+        assert model.verify_replicas()                 # bit-exact parameter digest, all ranks
+        ep = model.comm.validate_epochs()              # same collectives issued everywhere
+        assert max(ep) > 0
         cs = model.arena.param.double().sum().reshape(1)
         lo, hi = cs.clone(), cs.clone()
         dist.all_reduce(lo, op=dist.ReduceOp.MIN)
