@@ -89,6 +89,17 @@ __device__ __forceinline__ void tma_load_4d(void* smem_dst, const void* tmap, ui
         : "memory");
 }
 
+// 1-D bulk copy global -> shared through the TMA unit (no tensor map): `bytes` is a multiple of
+// 16, both addresses 16-byte aligned; completion is counted on `bar` (complete_tx).
+__device__ __forceinline__ void bulk_load_1d(void* smem_dst, const void* gsrc, uint32_t bytes,
+                                             uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
+            "r"(smem_u32(smem_dst)),
+        "l"(reinterpret_cast<uint64_t>(gsrc)), "r"(bytes), "r"(smem_u32(bar))
+        : "memory");
+}
+
 // ----------------------------------------------------------------------------- tcgen05
 __device__ __forceinline__ void tmem_alloc(uint32_t* smem_result, uint32_t ncols) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(

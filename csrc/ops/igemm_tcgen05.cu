@@ -530,10 +530,9 @@ static void pick_box(int rows, int Q, int P, int N, int* bq, int* bp, int* bn) {
     *bn = n;
 }
 
-template <int MODE, int BLOCK_N>
+template <int MODE, int BLOCK_N, int NST>
 static int launch_cfg(const IgemmMaps& maps, const IgemmParams& prm, dim3 grid, cudaStream_t st) {
     constexpr int kBStageBytes = BLOCK_N * 128;
-    constexpr int NST = (BLOCK_N == 128) ? 6 : 8;
     const int smem = NST * (kAStageBytes + kBStageBytes) + 1024;
     auto kern = g_lowp_f16 == 2   ? igemm_kernel<MODE, BLOCK_N, NST, 2>
                 : g_lowp_f16 == 1 ? igemm_kernel<MODE, BLOCK_N, NST, 1>
@@ -558,11 +557,52 @@ static int launch_cfg(const IgemmMaps& maps, const IgemmParams& prm, dim3 grid, 
     return int(cudaGetLastError());
 }
 
+// k-loop length of one CTA (the longest over the dgrad parity classes).
+template <int MODE>
+static int ksteps_per_cta(const IgemmParams& prm) {
+    const int splits = prm.splits > 0 ? prm.splits : 1;
+    if (MODE == MODE_WGRAD) {
+        const int total = prm.tiles_q * prm.tiles_p * prm.tiles_n;
+        return (total + splits - 1) / splits;
+    }
+    int worst = 0;
+    const int ncls = prm.nclasses > 0 ? prm.nclasses : 1;
+    for (int c = 0; c < ncls; ++c) {
+        const int total = (prm.cls_begin[c + 1] - prm.cls_begin[c]) * prm.chunks;
+        const int per = (total + splits - 1) / splits;
+        if (per > worst) worst = per;
+    }
+    return worst;
+}
+
+// Pipeline depth / co-residency policy.
+//   * Grids of up to a few waves (every ResNet-18 / CIFAR shape): one CTA per SM with a deep ring
+//     (6 x 32 KB or 8 x 24 KB) — the CTA has to cover the TMA latency on its own.
+//   * Grids of >= 4 waves (ResNet-50 @224: 6272 row tiles in layer1): a 128 x BLOCK_N tile with a
+//     short k loop is latency bound end to end (load -> MMA -> TMEM read -> store, nothing
+//     overlapping inside one CTA), so the smem footprint is cut to 2-4 stages and 2-4 CTAs share
+//     an SM: one CTA's epilogue overlaps its neighbours' loads and MMAs.  TMEM is not the limit
+//     (<= 4 x 128 columns); registers are <= 64 per thread.
+// DPT_IGEMM_CORESIDENT=0 forces the deep single-CTA configuration.
 template <int MODE>
 static int launch(const IgemmMaps& maps, const IgemmParams& prm, dim3 grid, int block_n,
                   cudaStream_t st) {
-    if (block_n == 128) return launch_cfg<MODE, 128>(maps, prm, grid, st);
-    return launch_cfg<MODE, 64>(maps, prm, grid, st);
+    static int coresident = -1;
+    if (coresident < 0) {
+        const char* e = std::getenv("DPT_IGEMM_CORESIDENT");
+        coresident = (e == nullptr || e[0] != '0') ? 1 : 0;
+    }
+    const long long ctas = static_cast<long long>(grid.x) * grid.y * grid.z;
+    const bool many = coresident && ctas >= 4 * 148;
+    const int nk = ksteps_per_cta<MODE>(prm);
+    if (block_n == 128) {
+        if (many && nk <= 4) return launch_cfg<MODE, 128, 2>(maps, prm, grid, st);   // 3 CTAs / SM
+        if (many) return launch_cfg<MODE, 128, 3>(maps, prm, grid, st);              // 2 CTAs / SM
+        return launch_cfg<MODE, 128, 6>(maps, prm, grid, st);
+    }
+    if (many && nk <= 4) return launch_cfg<MODE, 64, 2>(maps, prm, grid, st);        // 4 CTAs / SM
+    if (many) return launch_cfg<MODE, 64, 4>(maps, prm, grid, st);                   // 2 CTAs / SM
+    return launch_cfg<MODE, 64, 8>(maps, prm, grid, st);
 }
 
 // A-side activation maps for a conv whose taps read X[n, p*stride + r - pad, q*stride + s - pad].

@@ -85,9 +85,23 @@ __device__ __forceinline__ void block_reduce_cg(float (&s1)[8], float (&s2)[8], 
 
 // Per-channel reductions finish with atomics on a handful of cache lines (2*C floats), which the
 // L2 serialises per line: keep the CTA count at one per SM and use 16-byte vector RED.
-static inline int reduce_grid(long long nvec) {
+// That rule is for the small tensors of the CIFAR models, where the kernel is a few microseconds
+// long and the atomic tail would dominate.  Long streaming reductions get up to 4 CTAs per SM
+// (all co-resident: <= 64 registers, 18 KB smem); the 4x REDs are amortised over >= 64 loop trips.
+// (The ResNet-50-sized tensors go through the bulk-copy kernels further down instead.)
+static inline int reduce_grid_resident(long long nvec) {
+    // for kernels with a grid-wide spin barrier: never more than one CTA per SM
     long long blocks = (nvec + kEwThreads - 1) / kEwThreads;
     if (blocks > 148) blocks = 148;
+    if (blocks < 1) blocks = 1;
+    return static_cast<int>(blocks);
+}
+static inline int reduce_grid(long long nvec) {
+    long long blocks = (nvec + kEwThreads - 1) / kEwThreads;
+    const long long sms = 148;
+    if (blocks >= sms * 64) return static_cast<int>(sms * 4);
+    if (blocks >= sms * 16) return static_cast<int>(sms * 2);
+    if (blocks > sms) blocks = sms;
     if (blocks < 1) blocks = 1;
     return static_cast<int>(blocks);
 }
@@ -440,6 +454,258 @@ bn_bwd_apply_kernel(const bf16x8* __restrict__ g, const bf16x8* __restrict__ x,
         }
         dx[i] = pack8(o);
     }
+}
+
+// ------------------------------------------------------------------ bulk-copy streaming variants
+// For tensors of hundreds of megabytes (ResNet-50 @224) the register-file-bound kernels above top
+// out at ~3 TB/s: every byte in flight needs a destination register, and 64 registers x 1024
+// threads leave room for ~48 KB of outstanding loads per SM.  These variants move the operands
+// with the TMA unit instead: one thread issues 4 KB (8 KB in FP32 mode) 1-D bulk copies (cp.async.bulk, completion on
+// an mbarrier) into a ring of kBulkStages shared-memory slots per operand, so 48-64 KB per CTA
+// (2-3 CTAs per SM) are in flight regardless of registers; the 256 threads then read their 16
+// bytes from shared memory, `__syncthreads()` hands the slot back to the producer thread, and the
+// math overlaps the copies already in flight.  A chunk is 256 consecutive vectors, so the
+// thread <-> channel-group binding (256 % cvec == 0) is the same as in the kernels above.
+constexpr int kBulkStages = 4;
+constexpr int kBulkVec = static_cast<int>(sizeof(bf16x8));   // 16 B (16-bit types) or 32 B (fp32)
+constexpr int kBulkChunk = kEwThreads * kBulkVec;             // bytes per operand per stage
+
+template <int NOPS, typename Body>
+__device__ __forceinline__ void bulk_stream(const bf16x8* const (&src)[NOPS], long long nvec,
+                                            uint8_t* ring, uint64_t* full, Body&& body) {
+    const long long nchunks = (nvec + kEwThreads - 1) / kEwThreads;
+    const long long first = blockIdx.x, step = gridDim.x;
+    auto issue = [&](long long chunk, int stage) {
+        const long long v0 = chunk * kEwThreads;
+        const long long left = nvec - v0;
+        const uint32_t bytes = static_cast<uint32_t>(left < kEwThreads ? left : kEwThreads) * kBulkVec;
+        uint32_t total = 0;
+#pragma unroll
+        for (int o = 0; o < NOPS; ++o)
+            if (src[o] != nullptr) total += bytes;
+        mbar_expect_tx(&full[stage], total);
+#pragma unroll
+        for (int o = 0; o < NOPS; ++o)
+            if (src[o] != nullptr)
+                bulk_load_1d(ring + (stage * NOPS + o) * kBulkChunk, src[o] + v0, bytes, &full[stage]);
+    };
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kBulkStages; ++s) {
+            const long long chunk = first + s * step;
+            if (chunk < nchunks) issue(chunk, s);
+        }
+    }
+    int stage = 0;
+    uint32_t phase = 0;
+    for (long long chunk = first; chunk < nchunks; chunk += step) {
+        mbar_wait(&full[stage], phase);
+        const long long idx = chunk * kEwThreads + threadIdx.x;
+        const bool live = idx < nvec;
+        bf16x8 v[NOPS];
+        if (live) {
+#pragma unroll
+            for (int o = 0; o < NOPS; ++o)
+                if (src[o] != nullptr)
+                    v[o] = *reinterpret_cast<const bf16x8*>(ring + (stage * NOPS + o) * kBulkChunk +
+                                                            threadIdx.x * kBulkVec);
+        }
+        __syncthreads();   // every thread has copied its vectors out: the slot can be refilled
+        if (threadIdx.x == 0) {
+            const long long next = chunk + static_cast<long long>(kBulkStages) * step;
+            if (next < nchunks) issue(next, stage);
+        }
+        if (live) body(idx, v);
+        if (++stage == kBulkStages) {
+            stage = 0;
+            phase ^= 1;
+        }
+    }
+}
+
+__device__ __forceinline__ void bulk_ring_init(uint64_t* full) {
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kBulkStages; ++s) mbar_init(&full[s], 1);
+        fence_mbar_init();
+    }
+    __syncthreads();
+}
+
+static inline int bulk_grid(long long nvec, int ctas_per_sm) {
+    long long chunks = (nvec + kEwThreads - 1) / kEwThreads;
+    long long g = 148LL * ctas_per_sm;
+    if (g > chunks) g = chunks;
+    return static_cast<int>(g < 1 ? 1 : g);
+}
+// the bulk variants pay off once every CTA streams many chunks
+static inline bool bulk_worthwhile(long long nvec) {
+    static int on = -1;
+    if (on < 0) {
+        const char* e = std::getenv("DPT_BULK_EW");
+        on = (e == nullptr || e[0] != '0') ? 1 : 0;
+    }
+    return on && nvec >= 148LL * 2 * kEwThreads * 16;
+}
+
+// bn_fwd_kernel for large tensors (same arguments and results).
+__global__ void __launch_bounds__(kEwThreads)
+bn_fwd_bulk_kernel(const bf16x8* __restrict__ x, const float* __restrict__ sum,
+                   const float* __restrict__ sq, const float* __restrict__ gamma,
+                   const float* __restrict__ beta, const bf16x8* __restrict__ residual,
+                   bf16x8* __restrict__ y, float* __restrict__ save_mean,
+                   float* __restrict__ save_invstd, float* __restrict__ running_mean,
+                   float* __restrict__ running_var, long long* __restrict__ num_batches_tracked,
+                   long long nvec, int cvec, float inv_m, float unbias, float momentum, float eps,
+                   int relu) {
+    extern __shared__ __align__(128) uint8_t bulk_ring[];
+    __shared__ __align__(8) uint64_t full[kBulkStages];
+    bulk_ring_init(full);
+    pdl_launch_dependents();
+    pdl_wait();
+    const int cg = static_cast<int>(threadIdx.x % cvec);
+    float sc[8], sf[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const int c = cg * 8 + k;
+        const float mean = sum[c] * inv_m;
+        const float var = fmaxf(sq[c] * inv_m - mean * mean, 0.f);
+        const float invstd = rsqrtf(var + eps);
+        sc[k] = gamma[c] * invstd;
+        sf[k] = beta[c] - mean * sc[k];
+        if (blockIdx.x == 0 && threadIdx.x < cvec) {
+            save_mean[c] = mean;
+            save_invstd[c] = invstd;
+            if (running_mean != nullptr) {
+                running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+                running_var[c] = (1.f - momentum) * running_var[c] + momentum * var * unbias;
+            }
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0 && num_batches_tracked != nullptr)
+        *num_batches_tracked += 1;
+    const bool has_res = residual != nullptr;
+    const bf16x8* const src[2] = {x, residual};
+    bulk_stream<2>(src, nvec, bulk_ring, full, [&](long long idx, const bf16x8 (&v)[2]) {
+        float f[8];
+        unpack8(v[0], f);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) f[k] = fmaf(f[k], sc[k], sf[k]);
+        if (has_res) {
+            float r[8];
+            unpack8(v[1], r);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) f[k] += r[k];
+        }
+        if (relu) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) f[k] = fmaxf(f[k], 0.f);
+        }
+        y[idx] = pack8(f);
+    });
+}
+
+// bn_bwd_reduce_kernel<false> for large tensors (16-bit dy1).
+__global__ void __launch_bounds__(kEwThreads)
+bn_bwd_reduce_bulk_kernel(const bf16x8* __restrict__ dy1, const bf16x8* __restrict__ dy2,
+                          const bf16x8* __restrict__ y, const bf16x8* __restrict__ x,
+                          const float* __restrict__ save_mean,
+                          const float* __restrict__ save_invstd, bf16x8* __restrict__ g_out,
+                          float* __restrict__ dgamma, float* __restrict__ dbeta, long long nvec,
+                          int cvec) {
+    extern __shared__ __align__(128) uint8_t bulk_ring[];
+    __shared__ __align__(8) uint64_t full[kBulkStages];
+    __shared__ float sh[2][kEwThreads / 32][32][8 + 1];
+    bulk_ring_init(full);
+    pdl_launch_dependents();
+    pdl_wait();
+    const int cg = static_cast<int>(threadIdx.x % cvec);
+    float mean[8], istd[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        mean[k] = save_mean[cg * 8 + k];
+        istd[k] = save_invstd[cg * 8 + k];
+    }
+    float s1[8] = {0, 0, 0, 0, 0, 0, 0, 0}, s2[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    const bool has_dy2 = dy2 != nullptr, has_y = y != nullptr;
+    const bf16x8* const src[4] = {dy1, dy2, y, x};
+    bulk_stream<4>(src, nvec, bulk_ring, full, [&](long long idx, const bf16x8 (&v)[4]) {
+        float g[8], xv[8];
+        unpack8(v[0], g);
+        if (has_dy2) {
+            float t[8];
+            unpack8(v[1], t);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) g[k] += t[k];
+        }
+        if (has_y) {
+            float yv[8];
+            unpack8(v[2], yv);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) g[k] = yv[k] > 0.f ? g[k] : 0.f;
+        }
+        if (g_out != nullptr) {
+            const bf16x8 gb = pack8(g);
+            g_out[idx] = gb;
+            unpack8(gb, g);  // reduce exactly what pass 2 will read
+        }
+        unpack8(v[3], xv);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            s1[k] += g[k];
+            s2[k] += g[k] * (xv[k] - mean[k]) * istd[k];
+        }
+    });
+    block_reduce_cg(s1, s2, cvec, sh);
+    if (threadIdx.x < cvec) {
+        red_add8(dbeta + cg * 8, s1);
+        red_add8(dgamma + cg * 8, s2);
+    }
+}
+
+// bn_bwd_apply_kernel for large tensors.
+__global__ void __launch_bounds__(kEwThreads)
+bn_bwd_apply_bulk_kernel(const bf16x8* __restrict__ g, const bf16x8* __restrict__ x,
+                         const float* __restrict__ save_mean,
+                         const float* __restrict__ save_invstd, const float* __restrict__ gamma,
+                         const float* __restrict__ dgamma, const float* __restrict__ dbeta,
+                         bf16x8* __restrict__ dx, long long nvec, int cvec, float inv_m,
+                         float grad_unscale) {
+    extern __shared__ __align__(128) uint8_t bulk_ring[];
+    __shared__ __align__(8) uint64_t full[kBulkStages];
+    bulk_ring_init(full);
+    pdl_launch_dependents();
+    pdl_wait();
+    const int cg = static_cast<int>(threadIdx.x % cvec);
+    float mean[8], istd[8], a[8], b[8], c2[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const int c = cg * 8 + k;
+        mean[k] = save_mean[c];
+        istd[k] = save_invstd[c];
+        a[k] = gamma[c] * istd[k];
+        b[k] = dbeta[c] * inv_m * grad_unscale;
+        c2[k] = dgamma[c] * inv_m * grad_unscale;
+    }
+    const bf16x8* const src[2] = {g, x};
+    bulk_stream<2>(src, nvec, bulk_ring, full, [&](long long idx, const bf16x8 (&v)[2]) {
+        float gv[8], xv[8], o[8];
+        unpack8(v[0], gv);
+        unpack8(v[1], xv);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const float xh = (xv[k] - mean[k]) * istd[k];
+            o[k] = a[k] * (gv[k] - b[k] - xh * c2[k]);
+        }
+        dx[idx] = pack8(o);
+    });
+}
+
+template <typename K>
+static inline int bulk_smem_attr(K kern, int nops) {
+    const int smem = kBulkStages * nops * kBulkChunk;
+    if (smem > 48 * 1024)
+        return static_cast<int>(
+            cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    return 0;
 }
 
 // Single-launch BatchNorm backward: pass 1 (masked-gradient sums) and pass 2 (dx) in one kernel
@@ -805,6 +1071,27 @@ im2col_nchw_kernel(const float* __restrict__ x, lowp* __restrict__ out, int N, i
     const int cv = ldk / 8;
     const long long total = static_cast<long long>(N) * P * Q * cv;
     const int K = R * S * C;
+    // column -> (input offset, tap) table: keeps the four runtime-divisor divisions per element
+    // out of the main loop (the 224x224 stem builds 3.2M rows x 160 columns per step)
+    constexpr int kTab = 512;
+    __shared__ int s_off[kTab];
+    __shared__ short s_rs[kTab];
+    const bool use_tab = ldk <= kTab;
+    if (use_tab) {
+        for (int col = threadIdx.x; col < ldk; col += kEwThreads) {
+            if (col < K) {
+                const int c = col % C;
+                const int rs = col / C;
+                const int s = rs % S, r = rs / S;
+                s_off[col] = (c * H + r) * W + s;
+                s_rs[col] = static_cast<short>((r << 8) | s);
+            } else {
+                s_off[col] = 0;
+                s_rs[col] = -1;
+            }
+        }
+        __syncthreads();
+    }
     for (long long i = static_cast<long long>(blockIdx.x) * kEwThreads + threadIdx.x; i < total;
          i += static_cast<long long>(gridDim.x) * kEwThreads) {
         const int col0 = static_cast<int>(i % cv) * 8;
@@ -814,19 +1101,34 @@ im2col_nchw_kernel(const float* __restrict__ x, lowp* __restrict__ out, int N, i
         const int p = static_cast<int>(t % P);
         const int n = static_cast<int>(t / P);
         float v[8];
+        if (use_tab) {
+            const int h0 = p * stride - pad, w0 = q * stride - pad;
+            const float* base = x + (static_cast<long long>(n) * C * H + h0) * W + w0;
 #pragma unroll
-        for (int e = 0; e < 8; ++e) {
-            const int col = col0 + e;
-            float val = 0.f;
-            if (col < K) {
-                const int c = col % C;
-                const int rs = col / C;
-                const int s = rs % S, r = rs / S;
-                const int h = p * stride - pad + r, w = q * stride - pad + s;
-                if (h >= 0 && h < H && w >= 0 && w < W)
-                    val = __ldg(x + ((static_cast<long long>(n) * C + c) * H + h) * W + w);
+            for (int e = 0; e < 8; ++e) {
+                const int rs = s_rs[col0 + e];
+                float val = 0.f;
+                if (rs >= 0) {
+                    const int h = h0 + (rs >> 8), w = w0 + (rs & 255);
+                    if (h >= 0 && h < H && w >= 0 && w < W) val = __ldg(base + s_off[col0 + e]);
+                }
+                v[e] = val;
             }
-            v[e] = val;
+        } else {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                const int col = col0 + e;
+                float val = 0.f;
+                if (col < K) {
+                    const int c = col % C;
+                    const int rs = col / C;
+                    const int s = rs % S, r = rs / S;
+                    const int h = p * stride - pad + r, w = q * stride - pad + s;
+                    if (h >= 0 && h < H && w >= 0 && w < W)
+                        val = __ldg(x + ((static_cast<long long>(n) * C + c) * H + h) * W + w);
+                }
+                v[e] = val;
+            }
         }
         reinterpret_cast<bf16x8*>(out)[i] = pack8(v);
     }
@@ -932,6 +1234,17 @@ inline int dpt_bn_fwd_train(const void* x, const float* sum, const float* sq, co
     const long long nvec = M * (C / 8);
     const float unbias = M > 1 ? static_cast<float>(M) / static_cast<float>(M - 1) : 1.f;
     ew_pdl_gate();
+    if (bulk_worthwhile(nvec)) {
+        static int attr = bulk_smem_attr(bn_fwd_bulk_kernel, 2);
+        if (attr != 0) return attr;
+        launch_pdl(bn_fwd_bulk_kernel, dim3(bulk_grid(nvec, 3)), dim3(kEwThreads),
+                   static_cast<size_t>(kBulkStages * 2 * kBulkChunk), static_cast<cudaStream_t>(stream),
+                   static_cast<const bf16x8*>(x), sum, sq, gamma, beta,
+                   static_cast<const bf16x8*>(residual), static_cast<bf16x8*>(y), save_mean,
+                   save_invstd, running_mean, running_var, num_batches_tracked, nvec, C / 8,
+                   1.f / static_cast<float>(M), unbias, momentum, eps, relu);
+        DPT_CHECK_LAUNCH();
+    }
     launch_pdl(bn_fwd_kernel, dim3(ew_grid(nvec, C / 8)), dim3(kEwThreads), 0, static_cast<cudaStream_t>(stream), 
         static_cast<const bf16x8*>(x), sum, sq, gamma, beta, static_cast<const bf16x8*>(residual),
         static_cast<bf16x8*>(y), save_mean, save_invstd, running_mean, running_var,
@@ -996,6 +1309,16 @@ inline int dpt_bn_bwd_reduce_ex(const void* dy1, int dy1_is_f32, const void* dy2
     const long long nvec = M * (C / 8);
     auto kern = dy1_is_f32 ? bn_bwd_reduce_kernel<true> : bn_bwd_reduce_kernel<false>;
     ew_pdl_gate();
+    if (!dy1_is_f32 && bulk_worthwhile(nvec)) {
+        static int attr = bulk_smem_attr(bn_bwd_reduce_bulk_kernel, 4);
+        if (attr != 0) return attr;
+        launch_pdl(bn_bwd_reduce_bulk_kernel, dim3(bulk_grid(nvec, 2)), dim3(kEwThreads),
+                   static_cast<size_t>(kBulkStages * 4 * kBulkChunk), static_cast<cudaStream_t>(stream),
+                   static_cast<const bf16x8*>(dy1), static_cast<const bf16x8*>(dy2),
+                   static_cast<const bf16x8*>(y), static_cast<const bf16x8*>(x), save_mean,
+                   save_invstd, static_cast<bf16x8*>(g_out), dgamma, dbeta, nvec, C / 8);
+        DPT_CHECK_LAUNCH();
+    }
     if (dy1_is_f32) pdl_skip_flag() = 1;  // dy1 was accumulated with REDs by a split-K dgrad
     launch_pdl(kern, dim3(reduce_grid(nvec)), dim3(kEwThreads), 0, static_cast<cudaStream_t>(stream), 
         dy1, static_cast<const bf16x8*>(dy2),
@@ -1016,7 +1339,7 @@ inline int dpt_bn_bwd_fused(const void* dy1, int dy1_is_f32, const void* dy2, co
     auto kern = dy1_is_f32 ? bn_bwd_fused_kernel<true> : bn_bwd_fused_kernel<false>;
     ew_pdl_gate();
     if (dy1_is_f32) pdl_skip_flag() = 1;  // dy1 was accumulated with REDs by a split-K dgrad
-    launch_pdl(kern, dim3(reduce_grid(nvec)), dim3(kEwThreads), 0, static_cast<cudaStream_t>(stream),
+    launch_pdl(kern, dim3(reduce_grid_resident(nvec)), dim3(kEwThreads), 0, static_cast<cudaStream_t>(stream),
                dy1, static_cast<const bf16x8*>(dy2), static_cast<const bf16x8*>(y),
                static_cast<const bf16x8*>(x), save_mean, save_invstd, gamma,
                static_cast<bf16x8*>(g_out), dgamma, dbeta, scratch, counter,
@@ -1030,6 +1353,16 @@ inline int dpt_bn_bwd_apply(const void* g, const void* x, const float* save_mean
     if (!cvec_ok(C)) return DPT_ERR_SHAPE;
     const long long nvec = M * (C / 8);
     ew_pdl_gate();
+    if (bulk_worthwhile(nvec)) {
+        static int attr = bulk_smem_attr(bn_bwd_apply_bulk_kernel, 2);
+        if (attr != 0) return attr;
+        launch_pdl(bn_bwd_apply_bulk_kernel, dim3(bulk_grid(nvec, 3)), dim3(kEwThreads),
+                   static_cast<size_t>(kBulkStages * 2 * kBulkChunk), static_cast<cudaStream_t>(stream),
+                   static_cast<const bf16x8*>(g), static_cast<const bf16x8*>(x), save_mean,
+                   save_invstd, gamma, dgamma, dbeta, static_cast<bf16x8*>(dx), nvec, C / 8,
+                   1.f / static_cast<float>(M), 1.f);
+        DPT_CHECK_LAUNCH();
+    }
     launch_pdl(bn_bwd_apply_kernel, dim3(ew_grid(nvec, C / 8)), dim3(kEwThreads), 0, static_cast<cudaStream_t>(stream), 
         static_cast<const bf16x8*>(g), static_cast<const bf16x8*>(x), save_mean, save_invstd, gamma,
         dgamma, dbeta, static_cast<bf16x8*>(dx), nvec, C / 8, 1.f / static_cast<float>(M), 1.f);

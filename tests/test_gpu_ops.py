@@ -22,7 +22,10 @@ def _close(got, ref, tol, what):
     assert err / den < tol, f"{what}: max abs err {err:.4g} vs ref max {den:.4g}"
 
 
-@pytest.mark.parametrize("shape", [(16, 8, 8, 64), (128, 1, 1, 512), (4, 7, 7, 2048), (3, 5, 5, 32)])
+# the last two shapes are large enough (>= 1.2M 8-channel vectors) for the bulk-copy streaming
+# kernels; the second of them ends in a partial 256-vector chunk
+@pytest.mark.parametrize("shape", [(16, 8, 8, 64), (128, 1, 1, 512), (4, 7, 7, 2048), (3, 5, 5, 32),
+                                   (16, 112, 112, 64), (5, 99, 101, 256)])
 @pytest.mark.parametrize("relu,res", [(False, False), (True, False), (True, True)])
 def test_bn_train_fwd_bwd(shape, relu, res):
     Fn = _F()
