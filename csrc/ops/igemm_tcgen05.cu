@@ -49,7 +49,8 @@ constexpr int OUT_F32_ATOMIC = 2;
 constexpr int kTileM = 128;
 constexpr int kKBlk = 64;
 constexpr int kMaxTaps = 52;
-constexpr int kNumThreads = 192;
+constexpr int kNumThreads = 192;         // TMA warp + MMA warp + 4 epilogue warps
+constexpr int kNumThreadsPersist = 320;  // TMA warp + MMA warp + 8 epilogue warps
 constexpr int kAStageBytes = kTileM * kKBlk * 2;  // 16 KiB in either major-ness
 
 struct IgemmTap {
@@ -83,8 +84,50 @@ struct IgemmParams {
     float* stat_sum;
     float* stat_sq;
     const float* bias;
+    int pgx, pgy, ptiles;           // persistent kernels: logical tile grid (x fastest) and its size
     IgemmTap taps[kMaxTaps];
 };
+
+// What one output tile works on: its position in the row / column space and its k range.
+struct TileCoord {
+    int cls;                 // dgrad parity class
+    int n0, p0, q0;          // row-space origin (fprop / dgrad)
+    int col0;                // first output column
+    int tap_w, row0_w;       // wgrad: filter tap and first output row (cout)
+    int k_begin, k_end;      // k-loop range of this tile (after splitting)
+};
+
+template <int MODE, int BLOCK_N>
+__device__ __forceinline__ TileCoord tile_coord(const IgemmParams& prm, int bx, int by, int bz) {
+    TileCoord tc;
+    tc.cls = 0;
+    tc.n0 = tc.p0 = tc.q0 = 0;
+    tc.tap_w = tc.row0_w = 0;
+    int split = bz;
+    int total;
+    if (MODE != MODE_WGRAD) {
+        tc.cls = bz / prm.splits;
+        split = bz % prm.splits;
+        int t = bx;
+        tc.q0 = (t % prm.tiles_q) * prm.bq;
+        t /= prm.tiles_q;
+        tc.p0 = (t % prm.tiles_p) * prm.bp;
+        t /= prm.tiles_p;
+        tc.n0 = t * prm.bn;
+        tc.col0 = by * BLOCK_N;
+        const int ntap = prm.cls_begin[tc.cls + 1] - prm.cls_begin[tc.cls];
+        total = ntap * prm.chunks;
+    } else {
+        tc.tap_w = bx / prm.ntile_per_tap;
+        tc.col0 = (bx % prm.ntile_per_tap) * BLOCK_N;
+        tc.row0_w = by * kTileM;
+        total = prm.tiles_q * prm.tiles_p * prm.tiles_n;
+    }
+    const int per = (total + prm.splits - 1) / prm.splits;
+    tc.k_begin = split * per;
+    tc.k_end = min(total, tc.k_begin + per);
+    return tc;
+}
 
 template <int W>
 __device__ __forceinline__ void xpose_reduce_step(float (&v)[16], uint32_t lane, uint32_t bit) {
@@ -108,8 +151,18 @@ __device__ __forceinline__ float warp_colsum16(float (&v)[16], uint32_t lane) {
 
 // DT: element type of both operands: 0 = bf16, 1 = fp16 (kind::f16), 2 = fp32 read as TF32
 // (kind::tf32; the reference's FP32 mode also runs its convolutions in TF32 through cuDNN).
-template <int MODE, int BLOCK_N, int NSTAGES, int DT>
-__global__ void __launch_bounds__(kNumThreads, 1)
+// PERSIST: the CTA walks a list of output tiles (tile = blockIdx.x, += gridDim.x) instead of
+// owning one.  The accumulator is double buffered in TMEM (2 x BLOCK_N columns) and handed back
+// and forth through tmem_full / tmem_empty mbarriers, so the epilogue of tile i (TMEM -> registers
+// -> global, BN statistics) overlaps the loads and MMAs of tile i+1, the TMA producer runs up to
+// NSTAGES k-steps ahead across tile boundaries, and barrier initialisation / TMEM allocation /
+// descriptor prefetch are paid once per CTA instead of once per tile.
+// The persistent variant also doubles the epilogue: 8 warps (two per TMEM lane quarter, each
+// taking half of the tile's columns).  With short k loops the kernel is bound by the issue rate
+// of the epilogue warps (ncu on the 1x1 64->256 conv of ResNet-50 layer1: tensor pipe 4 % busy,
+// 12 resident warps, issue slots 42 % busy), so more of them is what buys throughput.
+template <int MODE, int BLOCK_N, int NSTAGES, int DT, bool PERSIST = false>
+__global__ void __launch_bounds__(PERSIST ? kNumThreadsPersist : kNumThreads, 1)
 igemm_kernel(const __grid_constant__ IgemmMaps maps, const __grid_constant__ IgemmParams prm) {
     constexpr bool A_MN = (MODE == MODE_WGRAD);
     constexpr bool B_MN = (MODE != MODE_FPROP);
@@ -121,7 +174,8 @@ igemm_kernel(const __grid_constant__ IgemmMaps maps, const __grid_constant__ Ige
     constexpr int kUmmaK = 32 / ESZ;           // 16 (16-bit) or 8 (tf32)
     constexpr int kBStageBytes = BLOCK_N * 128;
     constexpr int kStageBytes = kAStageBytes + kBStageBytes;
-    constexpr uint32_t kTmemCols = BLOCK_N < 32 ? 32 : BLOCK_N;
+    constexpr uint32_t kAccCols = BLOCK_N < 32 ? 32 : BLOCK_N;
+    constexpr uint32_t kTmemCols = PERSIST ? 2 * kAccCols : kAccCols;
     // operand format field: 1 = BF16, 0 = F16 (bits 7-9 for A, 10-12 for B)
     constexpr uint32_t kIdesc =
         make_idesc(kTileM, BLOCK_N, A_MN ? 1 : 0, B_MN ? 1 : 0, DT == 0 ? 1 : (DT == 1 ? 0 : 2));
@@ -132,47 +186,26 @@ igemm_kernel(const __grid_constant__ IgemmMaps maps, const __grid_constant__ Ige
                                                ~uintptr_t(1023));
     __shared__ __align__(8) uint64_t full_bar[NSTAGES];
     __shared__ __align__(8) uint64_t empty_bar[NSTAGES];
-    __shared__ __align__(8) uint64_t tmem_full_bar;
+    __shared__ __align__(8) uint64_t tmem_full_bar[2];
+    __shared__ __align__(8) uint64_t tmem_empty_bar[2];
     __shared__ uint32_t tmem_base_smem;
     __shared__ __align__(16) float s_stat[2][4][BLOCK_N];  // per-epilogue-warp column partials
 
     const uint32_t warp = threadIdx.x >> 5;
     const uint32_t lane = threadIdx.x & 31;
 
-    // ---------------------------------------------------------------- tile coordinates
-    int cls = 0, split = blockIdx.z;
-    if (MODE != MODE_WGRAD) {
-        cls = blockIdx.z / prm.splits;
-        split = blockIdx.z % prm.splits;
-    }
-    int n0 = 0, p0 = 0, q0 = 0;  // row-space origin of this tile (fprop/dgrad)
-    int col0;                    // first output column of this tile
-    int tap_w = 0;               // wgrad: the tap this CTA owns
-    int row0_w = 0;              // wgrad: first output row (cout)
-    int k_begin, k_end;
-    if (MODE != MODE_WGRAD) {
-        int t = blockIdx.x;
-        q0 = (t % prm.tiles_q) * prm.bq;
-        t /= prm.tiles_q;
-        p0 = (t % prm.tiles_p) * prm.bp;
-        t /= prm.tiles_p;
-        n0 = t * prm.bn;
-        col0 = blockIdx.y * BLOCK_N;
-        const int ntap = prm.cls_begin[cls + 1] - prm.cls_begin[cls];
-        const int total = ntap * prm.chunks;
-        const int per = (total + prm.splits - 1) / prm.splits;
-        k_begin = split * per;
-        k_end = min(total, k_begin + per);
-    } else {
-        tap_w = blockIdx.x / prm.ntile_per_tap;
-        col0 = (blockIdx.x % prm.ntile_per_tap) * BLOCK_N;
-        row0_w = blockIdx.y * kTileM;
-        const int total = prm.tiles_q * prm.tiles_p * prm.tiles_n;
-        const int per = (total + prm.splits - 1) / prm.splits;
-        k_begin = split * per;
-        k_end = min(total, k_begin + per);
-    }
-    const int nk = max(0, k_end - k_begin);
+    // ---------------------------------------------------------------- tile list of this CTA
+    const int tile_first = PERSIST ? static_cast<int>(blockIdx.x) : 0;
+    const int tile_step = PERSIST ? static_cast<int>(gridDim.x) : 1;
+    const int tile_end = PERSIST ? prm.ptiles : 1;
+    auto coord_of = [&](int tile) {
+        if (PERSIST) {
+            const int bx = tile % prm.pgx;
+            const int r = tile / prm.pgx;
+            return tile_coord<MODE, BLOCK_N>(prm, bx, r % prm.pgy, r / prm.pgy);
+        }
+        return tile_coord<MODE, BLOCK_N>(prm, blockIdx.x, blockIdx.y, blockIdx.z);
+    };
 
     // ---------------------------------------------------------------- one-time setup
     if (warp == 0 && lane == 0) {
@@ -182,7 +215,10 @@ igemm_kernel(const __grid_constant__ IgemmMaps maps, const __grid_constant__ Ige
             mbar_init(&full_bar[s], 1);
             mbar_init(&empty_bar[s], 1);
         }
-        mbar_init(&tmem_full_bar, 1);
+        for (int a = 0; a < 2; ++a) {
+            mbar_init(&tmem_full_bar[a], 1);
+            mbar_init(&tmem_empty_bar[a], PERSIST ? 8 : 4);   // one arrival per epilogue warp
+        }
         fence_mbar_init();
     }
     if (warp == 1) {
@@ -203,7 +239,11 @@ igemm_kernel(const __grid_constant__ IgemmMaps maps, const __grid_constant__ Ige
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            for (int k = k_begin; k < k_end; ++k) {
+            for (int tile = tile_first; tile < tile_end; tile += tile_step) {
+            const TileCoord tc = coord_of(tile);
+            const int cls = tc.cls, n0 = tc.n0, p0 = tc.p0, q0 = tc.q0, col0 = tc.col0;
+            const int tap_w = tc.tap_w, row0_w = tc.row0_w;
+            for (int k = tc.k_begin; k < tc.k_end; ++k) {
                 mbar_wait(&empty_bar[stage], phase ^ 1);
                 uint8_t* sa = smem + stage * kStageBytes;
                 uint8_t* sb = sa + kAStageBytes;
@@ -247,12 +287,26 @@ igemm_kernel(const __grid_constant__ IgemmMaps maps, const __grid_constant__ Ige
                     phase ^= 1;
                 }
             }
+            }
         }
     } else if (warp == 1) {
         // ============================================================ MMA issuer
-        if (lane == 0 && nk > 0) {
+        if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
+            uint32_t nacc = 0;   // accumulator tiles produced so far (tiles with an empty k range
+                                 // use no accumulator; the epilogue counts the same way)
+            for (int tile = tile_first; tile < tile_end; tile += tile_step) {
+            const TileCoord tc = coord_of(tile);
+            const int nk = tc.k_end - tc.k_begin;
+            if (nk <= 0) continue;
+            const uint32_t acc = PERSIST ? (nacc & 1u) : 0u;
+            if (PERSIST) {
+                // the epilogue must have drained this accumulator (its previous use)
+                mbar_wait(&tmem_empty_bar[acc], ((nacc >> 1) & 1u) ^ 1u);
+                tc_fence_after();
+            }
+            const uint32_t tmem_acc = tmem_base + acc * kAccCols;
             for (int k = 0; k < nk; ++k) {
                 mbar_wait(&full_bar[stage], phase);
                 tc_fence_after();
@@ -272,9 +326,9 @@ igemm_kernel(const __grid_constant__ IgemmMaps maps, const __grid_constant__ Ige
                         B_MN ? make_smem_desc(sb + kk * (kUmmaK * 128), kMnBlkBytes, kMnSbo, kMnLayout)
                              : make_smem_desc_sw128(sb + kk * 32, 16, 1024);
                     if (DT == 2)
-                        umma_tf32(tmem_base, da, db, kIdesc, (k | kk) != 0 ? 1u : 0u);
+                        umma_tf32(tmem_acc, da, db, kIdesc, (k | kk) != 0 ? 1u : 0u);
                     else
-                        umma_f16(tmem_base, da, db, kIdesc, (k | kk) != 0 ? 1u : 0u);
+                        umma_f16(tmem_acc, da, db, kIdesc, (k | kk) != 0 ? 1u : 0u);
                 }
                 umma_commit(&empty_bar[stage]);  // frees the smem slot when the MMAs retire
                 if (++stage == NSTAGES) {
@@ -282,14 +336,29 @@ igemm_kernel(const __grid_constant__ IgemmMaps maps, const __grid_constant__ Ige
                     phase ^= 1;
                 }
             }
-            umma_commit(&tmem_full_bar);
+            umma_commit(&tmem_full_bar[acc]);
+            ++nacc;
+            }
         }
     } else {
-        // ============================================================ epilogue (4 warps)
+        // ============================================================ epilogue (4 or 8 warps)
         const uint32_t sub = warp & 3;  // TMEM sub-partition this warp may read
         const int r = sub * 32 + lane;  // accumulator row
+        // with 8 epilogue warps, warps 2..5 take the first half of the columns, 6..9 the second
+        constexpr int kColHalves = PERSIST ? 2 : 1;
+        constexpr int kChunksPerWarp = BLOCK_N / 16 / kColHalves;
+        constexpr int kEpiThreads = PERSIST ? 256 : 128;
+        const int half = PERSIST ? static_cast<int>((warp - 2) >> 2) : 0;
+        uint32_t nacc = 0;
+        for (int tile = tile_first; tile < tile_end; tile += tile_step) {
+        const TileCoord tc = coord_of(tile);
+        const int cls = tc.cls, n0 = tc.n0, p0 = tc.p0, q0 = tc.q0, col0 = tc.col0;
+        const int tap_w = tc.tap_w, row0_w = tc.row0_w;
+        const int nk = max(0, tc.k_end - tc.k_begin);
+        const uint32_t acc = PERSIST ? (nacc & 1u) : 0u;
+        const uint32_t tmem_acc = tmem_base + acc * kAccCols;
         if (nk > 0) {
-            mbar_wait(&tmem_full_bar, 0);
+            mbar_wait(&tmem_full_bar[acc], PERSIST ? ((nacc >> 1) & 1u) : 0u);
             tc_fence_after();
         }
         bool row_ok;
@@ -312,12 +381,15 @@ igemm_kernel(const __grid_constant__ IgemmMaps maps, const __grid_constant__ Ige
             koff_out = prm.taps[tap_w].koff;
         }
         const bool vec_ok = (prm.ldo % 8) == 0 && (koff_out % 8) == 0;
+        // 32-byte stores need every 16-column chunk of every row on a 32-byte boundary
+        const bool vec32_ok = (prm.ldo % 16) == 0 && (koff_out % 16) == 0 &&
+                              (reinterpret_cast<uintptr_t>(prm.out) % 32) == 0;
 #pragma unroll 1
-        for (int c = 0; c < BLOCK_N / 16; ++c) {
+        for (int c = half * kChunksPerWarp; c < (half + 1) * kChunksPerWarp; ++c) {
             float f[16];
             if (nk > 0) {
                 uint32_t v[16];
-                tmem_ld16(tmem_base + ((sub * 32u) << 16) + c * 16, v);
+                tmem_ld16(tmem_acc + ((sub * 32u) << 16) + c * 16, v);
                 tmem_ld_wait();
 #pragma unroll
                 for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
@@ -349,9 +421,13 @@ igemm_kernel(const __grid_constant__ IgemmMaps maps, const __grid_constant__ Ige
                                 pk[i] = *reinterpret_cast<uint32_t*>(&h);
                             }
                         }
-                        uint4* o4 = reinterpret_cast<uint4*>(o);
-                        o4[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-                        o4[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                        if (vec32_ok) {
+                            st_global_v8(o, pk);   // one full 32-byte sector
+                        } else {
+                            uint4* o4 = reinterpret_cast<uint4*>(o);
+                            o4[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                            o4[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                        }
                     } else {
 #pragma unroll
                         for (int i = 0; i < 16; ++i)
@@ -368,10 +444,21 @@ igemm_kernel(const __grid_constant__ IgemmMaps maps, const __grid_constant__ Ige
                 } else if (prm.out_mode == OUT_F32) {
                     float* o = reinterpret_cast<float*>(prm.out) + off;
                     if (full && vec_ok) {
-                        float4* o4 = reinterpret_cast<float4*>(o);
+                        if (vec32_ok) {
+                            uint32_t lo[8], hi[8];
 #pragma unroll
-                        for (int i = 0; i < 4; ++i)
-                            o4[i] = make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
+                            for (int i = 0; i < 8; ++i) {
+                                lo[i] = __float_as_uint(f[i]);
+                                hi[i] = __float_as_uint(f[8 + i]);
+                            }
+                            st_global_v8(o, lo);
+                            st_global_v8(o + 8, hi);
+                        } else {
+                            float4* o4 = reinterpret_cast<float4*>(o);
+#pragma unroll
+                            for (int i = 0; i < 4; ++i)
+                                o4[i] = make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
+                        }
                     } else {
 #pragma unroll
                         for (int i = 0; i < 16; ++i)
@@ -411,12 +498,20 @@ igemm_kernel(const __grid_constant__ IgemmMaps maps, const __grid_constant__ Ige
                 }
             }
         }
+        if (PERSIST && nk > 0) {
+            // every tcgen05.ld of this warp has completed (tmem_ld_wait): hand the accumulator
+            // back to the MMA warp so the next-but-one tile can start while we finish up
+            tc_fence_before();
+            if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
+        }
+        if (nk > 0) ++nacc;
         if (MODE == MODE_FPROP && prm.stat_sum != nullptr) {
             // combine the 4 epilogue warps in shared memory, then 16-byte vector RED: the
             // 2*Cout statistics live on a few cache lines and L2 serialises atomics per line
-            asm volatile("bar.sync 1, 128;" ::: "memory");
+            asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");
             if (sub == 0) {
-                for (int j = lane * 4; j < BLOCK_N; j += 128) {
+                constexpr int kColsPerWarp = BLOCK_N / kColHalves;
+                for (int j = half * kColsPerWarp + lane * 4; j < (half + 1) * kColsPerWarp; j += 128) {
                     const int cg = col0 + j;
                     if (cg >= prm.n_total) break;
                     float a[4], b[4];
@@ -438,6 +533,10 @@ igemm_kernel(const __grid_constant__ IgemmMaps maps, const __grid_constant__ Ige
                     }
                 }
             }
+            // the partials are overwritten by the next tile: wait until warp `sub == 0` has
+            // read them
+            if (PERSIST) asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");
+        }
         }
     }
 
@@ -530,13 +629,18 @@ static void pick_box(int rows, int Q, int P, int N, int* bq, int* bp, int* bn) {
     *bn = n;
 }
 
-template <int MODE, int BLOCK_N, int NST>
-static int launch_cfg(const IgemmMaps& maps, const IgemmParams& prm, dim3 grid, cudaStream_t st) {
+// persistent-variant policy knobs (dpt_igemm_set_persist): minimum number of tiles from which the
+// persistent kernels are used, and the CTA count they are launched with
+static long long g_persist_min_tiles = 4 * 148;
+static int g_persist_grid = 2 * 148;
+
+template <int MODE, int BLOCK_N, int NST, bool PERSIST>
+static int launch_cfg(const IgemmMaps& maps, const IgemmParams& prm_in, dim3 grid, cudaStream_t st) {
     constexpr int kBStageBytes = BLOCK_N * 128;
     const int smem = NST * (kAStageBytes + kBStageBytes) + 1024;
-    auto kern = g_lowp_f16 == 2   ? igemm_kernel<MODE, BLOCK_N, NST, 2>
-                : g_lowp_f16 == 1 ? igemm_kernel<MODE, BLOCK_N, NST, 1>
-                                  : igemm_kernel<MODE, BLOCK_N, NST, 0>;
+    auto kern = g_lowp_f16 == 2   ? igemm_kernel<MODE, BLOCK_N, NST, 2, PERSIST>
+                : g_lowp_f16 == 1 ? igemm_kernel<MODE, BLOCK_N, NST, 1, PERSIST>
+                                  : igemm_kernel<MODE, BLOCK_N, NST, 0, PERSIST>;
     static bool attr_done[3] = {false, false, false};
     if (!attr_done[g_lowp_f16]) {
         cudaError_t e =
@@ -552,57 +656,47 @@ static int launch_cfg(const IgemmMaps& maps, const IgemmParams& prm, dim3 grid, 
         }
         if (!igemm_pdl) pdl_skip_flag() = 1;
     }
-    cudaError_t le = launch_pdl(kern, grid, dim3(kNumThreads), static_cast<size_t>(smem), st, maps, prm);
+    IgemmParams prm = prm_in;
+    if (PERSIST) {
+        // logical tile grid in the order the hardware would have scheduled it (x fastest);
+        // two CTAs per SM (2 x 2 x BLOCK_N TMEM columns, 2 x ~97 KB smem)
+        prm.pgx = static_cast<int>(grid.x);
+        prm.pgy = static_cast<int>(grid.y);
+        prm.ptiles = static_cast<int>(grid.x * grid.y * grid.z);
+        const int resident = g_persist_grid;
+        grid = dim3(prm.ptiles < resident ? prm.ptiles : resident, 1, 1);
+    }
+    cudaError_t le = launch_pdl(kern, grid, dim3(PERSIST ? kNumThreadsPersist : kNumThreads),
+                                static_cast<size_t>(smem), st, maps, prm);
     if (le != cudaSuccess) return int(le);
     return int(cudaGetLastError());
 }
 
-// k-loop length of one CTA (the longest over the dgrad parity classes).
-template <int MODE>
-static int ksteps_per_cta(const IgemmParams& prm) {
-    const int splits = prm.splits > 0 ? prm.splits : 1;
-    if (MODE == MODE_WGRAD) {
-        const int total = prm.tiles_q * prm.tiles_p * prm.tiles_n;
-        return (total + splits - 1) / splits;
-    }
-    int worst = 0;
-    const int ncls = prm.nclasses > 0 ? prm.nclasses : 1;
-    for (int c = 0; c < ncls; ++c) {
-        const int total = (prm.cls_begin[c + 1] - prm.cls_begin[c]) * prm.chunks;
-        const int per = (total + splits - 1) / splits;
-        if (per > worst) worst = per;
-    }
-    return worst;
-}
-
-// Pipeline depth / co-residency policy.
-//   * Grids of up to a few waves (every ResNet-18 / CIFAR shape): one CTA per SM with a deep ring
-//     (6 x 32 KB or 8 x 24 KB) — the CTA has to cover the TMA latency on its own.
-//   * Grids of >= 4 waves (ResNet-50 @224: 6272 row tiles in layer1): a 128 x BLOCK_N tile with a
-//     short k loop is latency bound end to end (load -> MMA -> TMEM read -> store, nothing
-//     overlapping inside one CTA), so the smem footprint is cut to 2-4 stages and 2-4 CTAs share
-//     an SM: one CTA's epilogue overlaps its neighbours' loads and MMAs.  TMEM is not the limit
-//     (<= 4 x 128 columns); registers are <= 64 per thread.
-// DPT_IGEMM_CORESIDENT=0 forces the deep single-CTA configuration.
+// Launch policy.
+//   * Grids of up to a few waves (every ResNet-18 / CIFAR shape): one tile per CTA, one CTA per
+//     SM with a deep ring (6 x 32 KB or 8 x 24 KB) — the CTA has to cover the TMA latency on its
+//     own and there is no second tile to overlap with.
+//   * Grids of >= 4 waves (ResNet-50 @224: 6272 row tiles in layer1; large plain GEMMs): a
+//     128 x BLOCK_N tile with a short k loop is latency bound end to end (load -> MMA -> TMEM
+//     read -> store, nothing overlapping inside a one-tile CTA), so the persistent variant runs:
+//     2 CTAs per SM, each looping over tiles with a double-buffered TMEM accumulator.
+// DPT_IGEMM_PERSIST=0 forces the one-tile-per-CTA configuration.
 template <int MODE>
 static int launch(const IgemmMaps& maps, const IgemmParams& prm, dim3 grid, int block_n,
                   cudaStream_t st) {
-    static int coresident = -1;
-    if (coresident < 0) {
-        const char* e = std::getenv("DPT_IGEMM_CORESIDENT");
-        coresident = (e == nullptr || e[0] != '0') ? 1 : 0;
+    static int persist = -1;
+    if (persist < 0) {
+        const char* e = std::getenv("DPT_IGEMM_PERSIST");
+        persist = (e == nullptr || e[0] != '0') ? 1 : 0;
     }
     const long long ctas = static_cast<long long>(grid.x) * grid.y * grid.z;
-    const bool many = coresident && ctas >= 4 * 148;
-    const int nk = ksteps_per_cta<MODE>(prm);
+    const bool many = persist && ctas >= g_persist_min_tiles && ctas < (1LL << 31);
     if (block_n == 128) {
-        if (many && nk <= 4) return launch_cfg<MODE, 128, 2>(maps, prm, grid, st);   // 3 CTAs / SM
-        if (many) return launch_cfg<MODE, 128, 3>(maps, prm, grid, st);              // 2 CTAs / SM
-        return launch_cfg<MODE, 128, 6>(maps, prm, grid, st);
+        if (many) return launch_cfg<MODE, 128, 3, true>(maps, prm, grid, st);
+        return launch_cfg<MODE, 128, 6, false>(maps, prm, grid, st);
     }
-    if (many && nk <= 4) return launch_cfg<MODE, 64, 2>(maps, prm, grid, st);        // 4 CTAs / SM
-    if (many) return launch_cfg<MODE, 64, 4>(maps, prm, grid, st);                   // 2 CTAs / SM
-    return launch_cfg<MODE, 64, 8>(maps, prm, grid, st);
+    if (many) return launch_cfg<MODE, 64, 4, true>(maps, prm, grid, st);
+    return launch_cfg<MODE, 64, 8, false>(maps, prm, grid, st);
 }
 
 // A-side activation maps for a conv whose taps read X[n, p*stride + r - pad, q*stride + s - pad].
@@ -679,6 +773,15 @@ using namespace dpt;
 // called by dpt_set_lowp_dtype (norm_pool_loss.cu) so that every translation unit agrees
 extern "C" int dpt_igemm_set_lowp_dtype(int is_f16) {
     dpt::g_lowp_f16 = (is_f16 >= 0 && is_f16 <= 2) ? is_f16 : 0;
+    return 0;
+}
+
+// Policy of the persistent kernel variant: used from `min_tiles` output tiles upwards (<= 0
+// restores the default of 4 waves) with `grid_ctas` CTAs (<= 0 restores 2 per SM).  Tests use
+// it to push small problems through the multi-tile path.
+extern "C" int dpt_igemm_set_persist(long long min_tiles, int grid_ctas) {
+    dpt::g_persist_min_tiles = min_tiles > 0 ? min_tiles : 4 * 148;
+    dpt::g_persist_grid = grid_ctas > 0 ? grid_ctas : 2 * 148;
     return 0;
 }
 

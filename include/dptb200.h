@@ -31,6 +31,10 @@ int dpt_get_lowp_dtype(void);
 /* ---- tcgen05 / TMA implicit-GEMM convolution (csrc/ops/igemm_tcgen05.cu) ----------------
  * Stand in for the cuDNN convolution forward / backward-data / backward-filter calls that
  * torchvision's resnet18 makes on the reference path (train_ddp.py:153-156, 205-213). */
+/* Persistent-tile variant of the conv / GEMM kernels (CTAs loop over output tiles with a
+ * double-buffered TMEM accumulator): used from `min_tiles` tiles upwards with `grid_ctas` CTAs;
+ * <= 0 restores the defaults (4 waves, 2 CTAs per SM). */
+int dpt_igemm_set_persist(long long min_tiles, int grid_ctas);
 int dpt_conv_fprop(const void* x, const void* w, void* y, int N, int H, int W, int Cin, int Cout,
                    int R, int S, int stride, int pad, float* stat_sum, float* stat_sq,
                    int out_f32_atomic, int splits, void* stream);

@@ -155,3 +155,81 @@ def test_conv_dgrad_splitk(case):
     ref = torch.nn.grad.conv2d_input((N, Cin, H, W), w.float().permute(0, 3, 1, 2),
                                      dy.float().permute(0, 3, 1, 2), stride=s, padding=p)
     _close(dx.permute(0, 3, 1, 2), ref, 2e-3, "dgrad split-k")
+
+
+# ---------------------------------------------------------------------------------------------
+# Persistent variant (CTAs loop over output tiles, double-buffered TMEM accumulator).  Production
+# uses it from 4 waves of tiles upwards; here every case is pushed through it with a grid of only
+# 3 CTAs so each CTA walks several tiles (accumulator hand-over, barrier phases across tiles,
+# producer running ahead over tile boundaries, empty dgrad parity classes).
+@pytest.fixture
+def force_persistent():
+    from dpt_b200.ops import _lib
+    lib = _lib.lib()
+    lib.dpt_igemm_set_persist(1, 3)
+    yield
+    lib.dpt_igemm_set_persist(0, 0)
+
+
+@pytest.mark.parametrize("case", CONV_CASES)
+def test_persistent_conv_all_passes(case, force_persistent):
+    Fn = _F()
+    N, H, W, Cin, Cout, k, s, p = case
+    x = _mk((N, H, W, Cin), 1.0, 31)
+    w = _mk((Cout, k, k, Cin), 0.05, 32)
+    ssum = torch.zeros(Cout, device="cuda")
+    ssq = torch.zeros(Cout, device="cuda")
+    y = Fn.conv_fprop(x, w, s, p, stats=(ssum, ssq))
+    ref = _ref_conv(x, w, s, p)
+    torch.cuda.synchronize()
+    _close(y.permute(0, 3, 1, 2), ref, 1e-2, "persistent fprop")
+    _close(ssum, ref.sum(dim=(0, 2, 3)), 5e-3, "persistent stat sum")
+    _close(ssq, (ref * ref).sum(dim=(0, 2, 3)), 5e-3, "persistent stat sq")
+    y4 = Fn.conv_fprop(x, w, s, p, splits=3)
+    torch.cuda.synchronize()
+    _close(y4.permute(0, 3, 1, 2), ref, 2e-3, "persistent fprop split-k")
+    P, Q = Fn.conv_out_hw(H, W, k, k, s, p)
+    dy = _mk((N, P, Q, Cout), 1.0, 33)
+    dw = Fn.conv_wgrad(dy, x, (Cout, k, k, Cin), s, p)
+    torch.cuda.synchronize()
+    refw = torch.nn.grad.conv2d_weight(x.float().permute(0, 3, 1, 2), (Cout, Cin, k, k),
+                                       dy.float().permute(0, 3, 1, 2), stride=s, padding=p)
+    _close(dw.permute(0, 3, 1, 2), refw, 2e-3, "persistent wgrad")
+    if not (s == 2 and (H % 2 or W % 2)):
+        dx = Fn.conv_dgrad(dy, w, (N, H, W, Cin), s, p)
+        torch.cuda.synchronize()
+        refx = torch.nn.grad.conv2d_input((N, Cin, H, W), w.float().permute(0, 3, 1, 2),
+                                          dy.float().permute(0, 3, 1, 2), stride=s, padding=p)
+        _close(dx.permute(0, 3, 1, 2), refx, 1e-2, "persistent dgrad")
+
+
+def test_persistent_gemm_many_tiles(force_persistent):
+    Fn = _F()
+    M, N, K = 1500, 520, 264
+    A = _mk((M, K), 1.0, 41)
+    B = _mk((N, K), 0.05, 42)
+    C = torch.empty((M, N), device="cuda", dtype=torch.float32)
+    Fn.gemm(0, A, B, C, M, N, K, K, K, N, out_mode=1)      # 12 x 5 tiles on 3 CTAs
+    torch.cuda.synchronize()
+    _close(C, A.float() @ B.float().t(), 2e-3, "persistent gemm NT")
+
+
+def test_persistent_default_policy_large_grid():
+    """Default policy: >= 592 tiles switches to the persistent kernel (2 CTAs per SM)."""
+    Fn = _F()
+    N, H, W, Cin, Cout = 32, 56, 56, 64, 256          # 784 row tiles x 2 column tiles
+    x = _mk((N, H, W, Cin), 1.0, 51)
+    w = _mk((Cout, 1, 1, Cin), 0.05, 52)
+    ssum = torch.zeros(Cout, device="cuda")
+    ssq = torch.zeros(Cout, device="cuda")
+    y = Fn.conv_fprop(x, w, 1, 0, stats=(ssum, ssq))
+    torch.cuda.synchronize()
+    ref = _ref_conv(x, w, 1, 0)
+    _close(y.permute(0, 3, 1, 2), ref, 1e-2, "fprop large")
+    _close(ssum, ref.sum(dim=(0, 2, 3)), 5e-3, "stat sum large")
+    dy = _mk((N, H, W, Cout), 1.0, 53)
+    dx = Fn.conv_dgrad(dy, w, (N, H, W, Cin), 1, 0)
+    torch.cuda.synchronize()
+    refx = torch.nn.grad.conv2d_input((N, Cin, H, W), w.float().permute(0, 3, 1, 2),
+                                      dy.float().permute(0, 3, 1, 2), stride=1, padding=0)
+    _close(dx.permute(0, 3, 1, 2), refx, 1e-2, "dgrad large")
