@@ -467,10 +467,11 @@ bn_bwd_apply_kernel(const bf16x8* __restrict__ g, const bf16x8* __restrict__ x,
 // math overlaps the copies already in flight.  A chunk is 256 consecutive vectors, so the
 // thread <-> channel-group binding (256 % cvec == 0) is the same as in the kernels above.
 constexpr int kBulkStages = 4;
+constexpr int kBulkStagesReduce = 4;   // 4 operands: 64 KB ring + 18 KB reduction scratch -> 2 CTAs / SM
 constexpr int kBulkVec = static_cast<int>(sizeof(bf16x8));   // 16 B (16-bit types) or 32 B (fp32)
 constexpr int kBulkChunk = kEwThreads * kBulkVec;             // bytes per operand per stage
 
-template <int NOPS, typename Body>
+template <int NOPS, int STAGES, typename Body>
 __device__ __forceinline__ void bulk_stream(const bf16x8* const (&src)[NOPS], long long nvec,
                                             uint8_t* ring, uint64_t* full, Body&& body) {
     const long long nchunks = (nvec + kEwThreads - 1) / kEwThreads;
@@ -490,7 +491,7 @@ __device__ __forceinline__ void bulk_stream(const bf16x8* const (&src)[NOPS], lo
                 bulk_load_1d(ring + (stage * NOPS + o) * kBulkChunk, src[o] + v0, bytes, &full[stage]);
     };
     if (threadIdx.x == 0) {
-        for (int s = 0; s < kBulkStages; ++s) {
+        for (int s = 0; s < STAGES; ++s) {
             const long long chunk = first + s * step;
             if (chunk < nchunks) issue(chunk, s);
         }
@@ -511,20 +512,20 @@ __device__ __forceinline__ void bulk_stream(const bf16x8* const (&src)[NOPS], lo
         }
         __syncthreads();   // every thread has copied its vectors out: the slot can be refilled
         if (threadIdx.x == 0) {
-            const long long next = chunk + static_cast<long long>(kBulkStages) * step;
+            const long long next = chunk + static_cast<long long>(STAGES) * step;
             if (next < nchunks) issue(next, stage);
         }
         if (live) body(idx, v);
-        if (++stage == kBulkStages) {
+        if (++stage == STAGES) {
             stage = 0;
             phase ^= 1;
         }
     }
 }
 
-__device__ __forceinline__ void bulk_ring_init(uint64_t* full) {
+__device__ __forceinline__ void bulk_ring_init(uint64_t* full, int stages = kBulkStages) {
     if (threadIdx.x == 0) {
-        for (int s = 0; s < kBulkStages; ++s) mbar_init(&full[s], 1);
+        for (int s = 0; s < stages; ++s) mbar_init(&full[s], 1);
         fence_mbar_init();
     }
     __syncthreads();
@@ -584,7 +585,7 @@ bn_fwd_bulk_kernel(const bf16x8* __restrict__ x, const float* __restrict__ sum,
         *num_batches_tracked += 1;
     const bool has_res = residual != nullptr;
     const bf16x8* const src[2] = {x, residual};
-    bulk_stream<2>(src, nvec, bulk_ring, full, [&](long long idx, const bf16x8 (&v)[2]) {
+    bulk_stream<2, kBulkStages>(src, nvec, bulk_ring, full, [&](long long idx, const bf16x8 (&v)[2]) {
         float f[8];
         unpack8(v[0], f);
 #pragma unroll
@@ -614,7 +615,7 @@ bn_bwd_reduce_bulk_kernel(const bf16x8* __restrict__ dy1, const bf16x8* __restri
     extern __shared__ __align__(128) uint8_t bulk_ring[];
     __shared__ __align__(8) uint64_t full[kBulkStages];
     __shared__ float sh[2][kEwThreads / 32][32][8 + 1];
-    bulk_ring_init(full);
+    bulk_ring_init(full, kBulkStagesReduce);
     pdl_launch_dependents();
     pdl_wait();
     const int cg = static_cast<int>(threadIdx.x % cvec);
@@ -627,7 +628,7 @@ bn_bwd_reduce_bulk_kernel(const bf16x8* __restrict__ dy1, const bf16x8* __restri
     float s1[8] = {0, 0, 0, 0, 0, 0, 0, 0}, s2[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     const bool has_dy2 = dy2 != nullptr, has_y = y != nullptr;
     const bf16x8* const src[4] = {dy1, dy2, y, x};
-    bulk_stream<4>(src, nvec, bulk_ring, full, [&](long long idx, const bf16x8 (&v)[4]) {
+    bulk_stream<4, kBulkStagesReduce>(src, nvec, bulk_ring, full, [&](long long idx, const bf16x8 (&v)[4]) {
         float g[8], xv[8];
         unpack8(v[0], g);
         if (has_dy2) {
@@ -686,7 +687,7 @@ bn_bwd_apply_bulk_kernel(const bf16x8* __restrict__ g, const bf16x8* __restrict_
         c2[k] = dgamma[c] * inv_m * grad_unscale;
     }
     const bf16x8* const src[2] = {g, x};
-    bulk_stream<2>(src, nvec, bulk_ring, full, [&](long long idx, const bf16x8 (&v)[2]) {
+    bulk_stream<2, kBulkStages>(src, nvec, bulk_ring, full, [&](long long idx, const bf16x8 (&v)[2]) {
         float gv[8], xv[8], o[8];
         unpack8(v[0], gv);
         unpack8(v[1], xv);
@@ -700,12 +701,12 @@ bn_bwd_apply_bulk_kernel(const bf16x8* __restrict__ g, const bf16x8* __restrict_
 }
 
 template <typename K>
-static inline int bulk_smem_attr(K kern, int nops) {
-    const int smem = kBulkStages * nops * kBulkChunk;
-    if (smem > 48 * 1024)
-        return static_cast<int>(
-            cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    return 0;
+static inline int bulk_smem_attr(K kern, int nops, int stages = kBulkStages) {
+    // always opt in: static (reduction scratch) + dynamic shared memory may exceed the 48 KB
+    // default even when the dynamic part alone does not
+    const int smem = stages * nops * kBulkChunk;
+    return static_cast<int>(
+        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
 }
 
 // Single-launch BatchNorm backward: pass 1 (masked-gradient sums) and pass 2 (dx) in one kernel
@@ -1310,10 +1311,10 @@ inline int dpt_bn_bwd_reduce_ex(const void* dy1, int dy1_is_f32, const void* dy2
     auto kern = dy1_is_f32 ? bn_bwd_reduce_kernel<true> : bn_bwd_reduce_kernel<false>;
     ew_pdl_gate();
     if (!dy1_is_f32 && bulk_worthwhile(nvec)) {
-        static int attr = bulk_smem_attr(bn_bwd_reduce_bulk_kernel, 4);
+        static int attr = bulk_smem_attr(bn_bwd_reduce_bulk_kernel, 4, kBulkStagesReduce);
         if (attr != 0) return attr;
         launch_pdl(bn_bwd_reduce_bulk_kernel, dim3(bulk_grid(nvec, 2)), dim3(kEwThreads),
-                   static_cast<size_t>(kBulkStages * 4 * kBulkChunk), static_cast<cudaStream_t>(stream),
+                   static_cast<size_t>(kBulkStagesReduce * 4 * kBulkChunk), static_cast<cudaStream_t>(stream),
                    static_cast<const bf16x8*>(dy1), static_cast<const bf16x8*>(dy2),
                    static_cast<const bf16x8*>(y), static_cast<const bf16x8*>(x), save_mean,
                    save_invstd, static_cast<bf16x8*>(g_out), dgamma, dbeta, nvec, C / 8);
