@@ -537,12 +537,17 @@ static inline int bulk_grid(long long nvec, int ctas_per_sm) {
     if (g > chunks) g = chunks;
     return static_cast<int>(g < 1 ? 1 : g);
 }
-// the bulk variants pay off once every CTA streams many chunks
+// The bulk variants pay off once every CTA streams many chunks.  They are OPT-IN
+// (DPT_BULK_EW=1): with them enabled the large-shape BatchNorm test failed intermittently
+// (about one process in three, only relu=True cases of the 5x99x101x256 shape, i.e. only when the
+// apply kernel reads through TMA the masked gradient that the PDL-chained reduce kernel has just
+// written with ordinary stores) and the GPU budget of the round ran out before the cause was
+// pinned down.  Measured with them on: ResNet-50 bs256 30.6 ms/step vs ~34 ms without.
 static inline bool bulk_worthwhile(long long nvec) {
     static int on = -1;
     if (on < 0) {
         const char* e = std::getenv("DPT_BULK_EW");
-        on = (e == nullptr || e[0] != '0') ? 1 : 0;
+        on = (e != nullptr && e[0] == '1') ? 1 : 0;
     }
     return on && nvec >= 148LL * 2 * kEwThreads * 16;
 }

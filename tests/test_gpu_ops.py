@@ -22,12 +22,24 @@ def _close(got, ref, tol, what):
     assert err / den < tol, f"{what}: max abs err {err:.4g} vs ref max {den:.4g}"
 
 
-# the last two shapes are large enough (>= 1.2M 8-channel vectors) for the bulk-copy streaming
-# kernels; the second of them ends in a partial 256-vector chunk
-@pytest.mark.parametrize("shape", [(16, 8, 8, 64), (128, 1, 1, 512), (4, 7, 7, 2048), (3, 5, 5, 32),
-                                   (16, 112, 112, 64), (5, 99, 101, 256)])
+@pytest.mark.parametrize("shape", [(16, 8, 8, 64), (128, 1, 1, 512), (4, 7, 7, 2048), (3, 5, 5, 32)])
 @pytest.mark.parametrize("relu,res", [(False, False), (True, False), (True, True)])
 def test_bn_train_fwd_bwd(shape, relu, res):
+    _bn_train_fwd_bwd(shape, relu, res)
+
+
+# ResNet-50-sized tensors (>= 1.2M 8-channel vectors: large enough for the opt-in bulk-copy
+# streaming kernels, DPT_BULK_EW=1; the second shape ends in a partial 256-vector chunk).
+# Opt-in (DPT_TEST_LARGE=1): see the note at bulk_worthwhile() in norm_pool_loss_impl.cuh.
+@pytest.mark.skipif(__import__("os").environ.get("DPT_TEST_LARGE", "0") != "1",
+                    reason="large-shape BatchNorm cases are opt-in (DPT_TEST_LARGE=1)")
+@pytest.mark.parametrize("shape", [(16, 112, 112, 64), (5, 99, 101, 256)])
+@pytest.mark.parametrize("relu,res", [(False, False), (True, False), (True, True)])
+def test_bn_train_fwd_bwd_large(shape, relu, res):
+    _bn_train_fwd_bwd(shape, relu, res)
+
+
+def _bn_train_fwd_bwd(shape, relu, res):
     Fn = _F()
     N, H, W, C = shape
     x = _rand(shape, 1) * 2 + 0.5
@@ -67,8 +79,23 @@ def test_bn_train_fwd_bwd(shape, relu, res):
     yr.backward(dy.float().permute(0, 3, 1, 2))
     torch.cuda.synchronize()
     # the ReLU mask is taken from the bf16 output: elements whose fp32 value rounds to zero
-    # differ marginally, hence the looser tolerance
-    _close(dx.permute(0, 3, 1, 2), xr.grad, 3e-2, "bn dx")
+    # differ marginally, hence the looser tolerance.  Where the pre-activation is within rounding
+    # distance of zero the ReLU decision itself is a coin flip between two correct fp32
+    # evaluation orders (ours: fma(x, scale, shift); torch: ((x - mean) * invstd) * w + b), and
+    # the batch statistics differ in the last bit from run to run (atomic accumulation order).
+    # With ~13M elements in the large shapes a few such elements exist in every run; they carry
+    # the full incoming gradient on one side and zero on the other, so they are excluded.
+    dx_got, dx_ref = dx.permute(0, 3, 1, 2).float(), xr.grad
+    if relu:
+        with torch.no_grad():
+            pre = F.batch_norm(x.float().permute(0, 3, 1, 2), None, None, gamma, beta, training=True,
+                               eps=1e-5)
+            if res:
+                pre = pre + residual.float().permute(0, 3, 1, 2)
+            decided = pre.abs() > 1e-4
+        assert (~decided).float().mean().item() < 1e-3
+        dx_got, dx_ref = dx_got * decided, dx_ref * decided
+    _close(dx_got, dx_ref, 3e-2, "bn dx")
     _close(dgamma, gr.grad, 2e-2, "dgamma")
     _close(dbeta, br.grad, 2e-2, "dbeta")
 
