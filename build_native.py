@@ -30,6 +30,7 @@ NVCC_FLAGS = [
 
 KERNEL_SOURCES = [
     "csrc/ops/igemm_tcgen05.cu",
+    "csrc/ops/gemm2sm_tcgen05.cu",
     "csrc/ops/norm_pool_loss.cu",
     "csrc/ops/optim.cu",
     "csrc/comm/p2p_collectives.cu",

@@ -31,6 +31,11 @@ int dpt_get_lowp_dtype(void);
 /* ---- tcgen05 / TMA implicit-GEMM convolution (csrc/ops/igemm_tcgen05.cu) ----------------
  * Stand in for the cuDNN convolution forward / backward-data / backward-filter calls that
  * torchvision's resnet18 makes on the reference path (train_ddp.py:153-156, 205-213). */
+/* EXPERIMENTAL two-SM GEMM (thread-block cluster of 2 CTAs, tcgen05.mma.cta_group::2, 256x256
+ * tiles, persistent): C[M,N] = A[M,K] * B[N,K]^T, 16-bit row-major operands (lda/ldb multiples of
+ * 8 elements), C 16-bit or fp32.  Not used by the model paths yet. */
+int dpt_gemm2sm_bf16(const void* A, const void* B, void* C, int M, int N, int K, long long lda,
+                     long long ldb, long long ldc, int out_f32, int f16, void* stream);
 /* Persistent-tile variant of the conv / GEMM kernels (CTAs loop over output tiles with a
  * double-buffered TMEM accumulator): used from `min_tiles` tiles upwards with `grid_ctas` CTAs;
  * <= 0 restores the defaults (4 waves, 2 CTAs per SM). */
