@@ -27,8 +27,7 @@ import torch.distributed as dist
 import torch.nn as nn
 
 from .arena import ParamArena
-from .bucket import (DEFAULT_BUCKET_BYTES_CAP, DEFAULT_FIRST_BUCKET_BYTES, ext, ext_available,
-                     plan_arena_buckets)
+from .bucket import ext, ext_available, plan_arena_buckets
 
 
 class GradBucket:
