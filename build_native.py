@@ -60,24 +60,39 @@ def _stale(src: Path, obj: Path, hdr_m: float) -> bool:
     return (not obj.exists()) or obj.stat().st_mtime < max(src.stat().st_mtime, hdr_m)
 
 
+def _extra_defines() -> list[str]:
+    """Opt-in build variants selected through the environment (each changes the object names, so
+    switching back and forth never links stale objects):
+      DPT_VEC128=1  whole-register (128-bit) activation vectors in the elementwise kernels."""
+    out = []
+    if os.environ.get("DPT_VEC128", "0") == "1":
+        out.append("-DDPT_VEC128=1")
+    return out
+
+
 def build_kernels(verbose: bool = False) -> Path:
     OUT.mkdir(parents=True, exist_ok=True)
     OBJ.mkdir(parents=True, exist_ok=True)
     hdr_m = _headers_mtime()
+    extra = _extra_defines()
+    tag = "".join("." + d[2:].split("=")[0].lower() for d in extra)
+    stamp = OBJ / "variant.txt"
+    relink = (stamp.read_text() if stamp.exists() else "") != tag
     jobs, objs = [], []
     for s in KERNEL_SOURCES:
         src = ROOT / s
-        obj = OBJ / (src.stem + ".o")
+        obj = OBJ / (src.stem + tag + ".o")
         objs.append(obj)
         if _stale(src, obj, hdr_m):
-            jobs.append([NVCC, *NVCC_FLAGS, "-c", str(src), "-o", str(obj)])
+            jobs.append([NVCC, *NVCC_FLAGS, *extra, "-c", str(src), "-o", str(obj)])
     if verbose and jobs:
         print(f"[build] compiling {len(jobs)} CUDA sources for sm_100a")
     with ThreadPoolExecutor(max_workers=min(8, max(1, len(jobs)))) as ex:
         list(ex.map(_run, jobs))
     lib = OUT / "libdptb200.so"
-    if jobs or not lib.exists():
+    if jobs or relink or not lib.exists():
         _run([NVCC, "-shared", "-o", str(lib), *map(str, objs), "-lcudart"])
+        stamp.write_text(tag)
     return lib
 
 

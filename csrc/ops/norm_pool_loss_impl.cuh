@@ -5,6 +5,56 @@ namespace DPT_NS {
 using namespace dpt;
 
 
+#ifdef DPT_VEC128
+// 8 activations as whole 16-byte registers: every global / shared access of a vector is ONE
+// 128-bit instruction (two for fp32 activations).  With the member-wise definition below nvcc
+// emits four 32-bit LDG / STG per vector for the by-reference reads in unpack8() and for most
+// stores (cuobjdump: 32 LDG.E.CONSTANT + 4 STG.E in bn_bwd_reduce_kernel, no .128 anywhere),
+// i.e. 4x the memory instructions and 4-byte partial-sector stores.  Opt-in at build time
+// (DPT_VEC128=1 python build_native.py) until it has been validated on hardware.
+struct alignas(16) bf16x8 {
+    uint4 q[sizeof(lowp2) / 4];   // 1 x 16 B for 16-bit element types, 2 x 16 B for fp32
+};
+
+__device__ __forceinline__ void unpack8(const bf16x8& b, float (&f)[8]) {
+    if constexpr (sizeof(lowp2) == 4) {
+        const uint4 q = b.q[0];   // one 128-bit load
+        const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            lowp2 h;
+            memcpy(&h, &w[i], sizeof(h));
+            float2 t = lp2_to_float2(h);
+            f[2 * i] = t.x;
+            f[2 * i + 1] = t.y;
+        }
+    } else {
+        const uint4 q0 = b.q[0], q1 = b.q[sizeof(lowp2) / 4 - 1];
+        f[0] = __uint_as_float(q0.x); f[1] = __uint_as_float(q0.y);
+        f[2] = __uint_as_float(q0.z); f[3] = __uint_as_float(q0.w);
+        f[4] = __uint_as_float(q1.x); f[5] = __uint_as_float(q1.y);
+        f[6] = __uint_as_float(q1.z); f[7] = __uint_as_float(q1.w);
+    }
+}
+__device__ __forceinline__ bf16x8 pack8(const float (&f)[8]) {
+    bf16x8 b;
+    if constexpr (sizeof(lowp2) == 4) {
+        uint32_t w[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const lowp2 h = floats_to_lp2(f[2 * i], f[2 * i + 1]);
+            memcpy(&w[i], &h, sizeof(h));
+        }
+        b.q[0] = make_uint4(w[0], w[1], w[2], w[3]);
+    } else {
+        b.q[0] = make_uint4(__float_as_uint(f[0]), __float_as_uint(f[1]), __float_as_uint(f[2]),
+                            __float_as_uint(f[3]));
+        b.q[sizeof(lowp2) / 4 - 1] = make_uint4(__float_as_uint(f[4]), __float_as_uint(f[5]),
+                                                __float_as_uint(f[6]), __float_as_uint(f[7]));
+    }
+    return b;
+}
+#else
 struct alignas(16) bf16x8 {
     lowp2 v[4];
 };
@@ -23,6 +73,7 @@ __device__ __forceinline__ bf16x8 pack8(const float (&f)[8]) {
     for (int i = 0; i < 4; ++i) b.v[i] = floats_to_lp2(f[2 * i], f[2 * i + 1]);
     return b;
 }
+#endif
 
 constexpr int kEwThreads = 256;
 
