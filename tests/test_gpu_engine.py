@@ -16,6 +16,19 @@ def _cos(a, b):
 
 @pytest.mark.parametrize("arch,bs,img,ncls", [("resnet18", 32, 32, 10), ("resnet50", 32, 64, 100)])
 def test_engine_matches_torch_fp32(arch, bs, img, ncls):
+    _engine_matches_torch_fp32(arch, bs, img, ncls)
+
+
+@pytest.mark.skipif(__import__("os").environ.get("DPT_TEST_LARGE", "0") != "1",
+                    reason="ImageNet-sized engine parity is opt-in (DPT_TEST_LARGE=1, ~3 GB)")
+def test_engine_matches_torch_fp32_imagenet_size():
+    """ResNet-50 at 224x224, batch 32: layer1 has 784 row tiles, so the convolutions take the
+    persistent kernels and the BatchNorm kernels their long-tensor grids (or, with
+    DPT_BULK_EW=1, the bulk-copy variants)."""
+    _engine_matches_torch_fp32("resnet50", 32, 224, 1000)
+
+
+def _engine_matches_torch_fp32(arch, bs, img, ncls):
     from dpt_b200.models.resnet import build_model
     torch.manual_seed(0)
     dev = torch.device("cuda")
