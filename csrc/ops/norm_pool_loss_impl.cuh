@@ -187,6 +187,11 @@ __global__ void __launch_bounds__(kEwThreads) bn_stats_kernel(const bf16x8* __re
         const int cg = threadIdx.x;
         red_add8(sum + cg * 8, s1);
         red_add8(sq + cg * 8, s2);
+        // The consumer of these sums is launched with the programmatic attribute and reads them
+        // right after griddepcontrol.wait; REDs are fire-and-forget, and with hundreds of CTAs
+        // queueing on a few hot cache lines the last ones can still be in flight when the grid
+        // counts as complete (same effect as measured for split-K accumulators).  Wait for them.
+        __threadfence();
     }
 }
 
@@ -469,6 +474,7 @@ bn_bwd_reduce_kernel(const void* __restrict__ dy1_raw, const bf16x8* __restrict_
     if (threadIdx.x < cvec) {
         red_add8(dbeta + cg * 8, s1);
         red_add8(dgamma + cg * 8, s2);
+        __threadfence();   // see bn_stats_kernel: the PDL-chained apply kernel reads these first
     }
 }
 
@@ -715,6 +721,7 @@ bn_bwd_reduce_bulk_kernel(const bf16x8* __restrict__ dy1, const bf16x8* __restri
     if (threadIdx.x < cvec) {
         red_add8(dbeta + cg * 8, s1);
         red_add8(dgamma + cg * 8, s2);
+        __threadfence();   // see bn_stats_kernel: the PDL-chained apply kernel reads these first
     }
 }
 
