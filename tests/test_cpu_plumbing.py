@@ -247,3 +247,69 @@ def test_c_header_declares_every_bound_symbol():
         lib = _lib.lib()
         for name in _lib._SIGS:
             assert hasattr(lib, name)
+
+
+def _fake_cifar(root, n_per_batch=20):
+    """A tiny directory in the standard cifar-10-batches-py layout (reference train_ddp.py:101-115
+    reads it through torchvision.datasets.CIFAR10)."""
+    import pickle
+
+    import numpy as np
+    base = os.path.join(root, "cifar-10-batches-py")
+    os.makedirs(base, exist_ok=True)
+    rng = np.random.default_rng(0)
+    for name in [f"data_batch_{i}" for i in range(1, 6)] + ["test_batch"]:
+        d = {"data": rng.integers(0, 256, size=(n_per_batch, 3072), dtype=np.uint8),
+             "labels": rng.integers(0, 10, size=n_per_batch).tolist()}
+        with open(os.path.join(base, name), "wb") as f:
+            pickle.dump(d, f)
+    with open(os.path.join(base, "batches.meta"), "wb") as f:
+        pickle.dump({"label_names": [str(i) for i in range(10)]}, f)
+    return base
+
+
+def test_cifar_reader_matches_torchvision_pipeline(tmp_path, monkeypatch):
+    """Our pickle reader + normalisation == torchvision CIFAR10 + ToTensor + Normalize (the
+    reference's eval transform, train_ddp.py:98-100), and the training augmentation produces
+    crops / flips of the padded image."""
+    tv = pytest.importorskip("torchvision")
+    from torchvision import transforms
+
+    from dpt_b200.data import CIFAR_MEAN, CIFAR_STD, CIFAR10Files
+    _fake_cifar(str(tmp_path))
+    monkeypatch.setattr(tv.datasets.cifar, "check_integrity", lambda *a, **k: True)
+    tf = transforms.Compose([transforms.ToTensor(), transforms.Normalize(CIFAR_MEAN, CIFAR_STD)])
+    for train in (True, False):
+        ref = tv.datasets.CIFAR10(root=str(tmp_path), train=train, download=False, transform=tf)
+        ours = CIFAR10Files(str(tmp_path), train=train, augment=False)
+        assert len(ours) == len(ref) == (100 if train else 20)
+        for i in (0, 7, len(ours) - 1):
+            xr, yr = ref[i]
+            xo, yo = ours[i]
+            assert int(yo) == int(yr)
+            assert torch.allclose(xo, xr, atol=1e-6)
+    aug = CIFAR10Files(str(tmp_path), train=True, augment=True)
+    plain = CIFAR10Files(str(tmp_path), train=True, augment=False)
+    torch.manual_seed(0)
+    shifted = 0
+    for i in range(10):
+        xa, _ = aug[i]
+        xp, _ = plain[i]
+        assert xa.shape == (3, 32, 32)
+        # an augmented sample is the plain one shifted by (dy-4, dx-4) and maybe mirrored: its
+        # multiset of interior pixel values is a subset of the plain image's plus padding
+        shifted += int(not torch.equal(xa, xp))
+    assert shifted >= 5
+
+
+def test_entry_point_reads_cifar_files_single_process(tmp_path):
+    """Config without --synthetic: the CIFAR files are picked up (CPU, one process)."""
+    from dpt_b200.train_ddp import main
+    _fake_cifar(str(tmp_path / "data"))
+    out = str(tmp_path / "exp")
+    os.environ.pop("WORLD_SIZE", None)
+    os.environ.pop("RANK", None)
+    main(["--data-dir", str(tmp_path / "data"), "--epochs", "1", "--batch-size", "8", "--workers", "0",
+          "--print-freq", "5", "--output-dir", out, "--steps", "3"])
+    lines = open(os.path.join(out, "metrics_rank0.csv")).read().splitlines()
+    assert len(lines) == 2 and lines[0].startswith("epoch,")
