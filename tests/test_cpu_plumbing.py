@@ -313,3 +313,50 @@ def test_entry_point_reads_cifar_files_single_process(tmp_path):
           "--print-freq", "5", "--output-dir", out, "--steps", "3"])
     lines = open(os.path.join(out, "metrics_rank0.csv")).read().splitlines()
     assert len(lines) == 2 and lines[0].startswith("epoch,")
+
+
+def test_grad_sync_profiler_summary_and_sampling_schedule():
+    """Sampling follows torch DDP's Logger (first 10 iterations, then every 100th,
+    reducer.hpp:33,166-170); the summary is the mean over sampled steps and the headline
+    BASELINE.json metric: exposed sync as a percentage of the step."""
+    from dpt_b200.profiler import GradSyncProfiler
+    prof = GradSyncProfiler(ddp=None)
+    sampled = []
+    for step in range(305):
+        prof._step = step
+        if prof.should_sample():
+            sampled.append(step)
+    assert sampled == list(range(10)) + [100, 200, 300]
+    prof.records = [
+        {"step": 1, "step_ms": 2.0, "backward_ms": 1.0, "comm_busy_ms": 0.6, "comm_exposed_ms": 0.1,
+         "overlap_ms": 0.5},
+        {"step": 2, "step_ms": 4.0, "backward_ms": 3.0, "comm_busy_ms": 0.4, "comm_exposed_ms": 0.2,
+         "overlap_ms": 0.2},
+        {"step": 3, "step_ms": 3.0},                       # a step without bucket timings
+    ]
+    s = prof.summary()
+    assert s["step_ms"] == pytest.approx(3.0) and s["comm_exposed_ms"] == pytest.approx(0.15)
+    assert s["overlap_ms"] == pytest.approx(0.35)
+    assert s["exposed_sync_pct"] == pytest.approx(100.0 * 0.15 / 3.0)
+
+
+def test_metrics_json_sink_and_csv_append_quirk(tmp_path):
+    """JSON sink rewrites the whole list each epoch; the CSV keeps the reference's quirk of
+    appending to an existing file without a second header (train_ddp.py:350-355)."""
+    import json
+
+    from dpt_b200 import metrics as M
+    js = M.MetricsJSON(str(tmp_path / "sub" / "m.json"))
+    js.append({"epoch": 1, "train_loss": 2.0})
+    js.append({"epoch": 2, "train_loss": 1.5, "grad_sync": {"exposed_sync_pct": 4.2}})
+    rows = json.load(open(tmp_path / "sub" / "m.json"))
+    assert [r["epoch"] for r in rows] == [1, 2] and rows[1]["grad_sync"]["exposed_sync_pct"] == 4.2
+    M.MetricsJSON("", enabled=True).append({"ignored": 1})        # no path -> disabled, no error
+    for _ in range(2):                                            # two "runs" into the same directory
+        csv = M.MetricsCSV(str(tmp_path), enabled=True)
+        csv.append(0, 2.3026, 10.0, 2.31, 9.5, 12.3456)
+    lines = open(tmp_path / "metrics_rank0.csv").read().splitlines()
+    assert lines[0] + "\n" == M.CSV_HEADER and len(lines) == 3
+    assert lines[1] == lines[2] == "1,2.3026,10.00,2.3100,9.50,12.3456"
+    M.MetricsCSV(str(tmp_path / "other"), enabled=False).append(0, 1, 1, 1, 1, 1)
+    assert not (tmp_path / "other").exists()
