@@ -39,7 +39,9 @@ def build_parser() -> argparse.ArgumentParser:
                    help="stop every epoch after this many steps (0 = full epoch)")
     p.add_argument("--optimizer", default="sgd", choices=["sgd", "adam", "adamw"])
     p.add_argument("--save-every", default=0, type=int, help="checkpoint every N epochs (0 = off)")
-    p.add_argument("--resume", default="", type=str, help="checkpoint file to resume from")
+    p.add_argument("--resume", default="", type=str,
+                   help="checkpoint file to resume from; 'auto' = <output-dir>/checkpoint.pt if it "
+                        "exists (for torchrun --max-restarts)")
     p.add_argument("--bucket-cap-mb", default=25.0, type=float, help="gradient bucket size cap")
     p.add_argument("--allreduce-algo", default="auto",
                    choices=["auto", "autotune", "oneshot", "twoshot", "nvls"],

@@ -63,6 +63,11 @@ def main(argv=None):
         ddp.enable_fused_sgd(optimizer)
 
     start_epoch = 0
+    if args.resume == "auto":
+        # restart-friendly (torchrun --max-restarts N): continue from this run's own checkpoint
+        # when there is one, start from scratch otherwise
+        auto = Path(args.output_dir) / "checkpoint.pt"
+        args.resume = str(auto) if auto.is_file() else ""
     if args.resume:
         payload = load_checkpoint(args.resume, model, optimizer, scaler)
         start_epoch = int(payload.get("epoch", 0))

@@ -360,3 +360,30 @@ def test_metrics_json_sink_and_csv_append_quirk(tmp_path):
     assert lines[1] == lines[2] == "1,2.3026,10.00,2.3100,9.50,12.3456"
     M.MetricsCSV(str(tmp_path / "other"), enabled=False).append(0, 1, 1, 1, 1, 1)
     assert not (tmp_path / "other").exists()
+
+
+def test_resume_continues_where_the_checkpoint_left_off(tmp_path, capsys):
+    """--save-every + --resume auto: a restarted job (torchrun --max-restarts re-runs the same
+    command line) picks up its own checkpoint, skips the finished epochs and appends to the CSV."""
+    from dpt_b200.train_ddp import main
+    os.environ.pop("WORLD_SIZE", None)
+    os.environ.pop("RANK", None)
+    out = str(tmp_path / "exp")
+    common = ["--synthetic", "--synthetic-size", "24", "--batch-size", "8", "--workers", "0",
+              "--print-freq", "100", "--output-dir", out, "--save-every", "1", "--resume", "auto",
+              "--no-validate"]
+    main(common + ["--epochs", "1"])                       # first attempt: no checkpoint yet
+    first = capsys.readouterr().out
+    assert "Resumed from" not in first and "[Epoch 1/1]" in first
+    ck1 = torch.load(os.path.join(out, "checkpoint.pt"), weights_only=False)
+    assert ck1["epoch"] == 1
+    main(common + ["--epochs", "3"])                       # "restart" with a longer schedule
+    second = capsys.readouterr().out
+    assert "Resumed from" in second and "at epoch 1" in second
+    assert "[Epoch 1/3]" not in second and "[Epoch 2/3]" in second and "[Epoch 3/3]" in second
+    ck3 = torch.load(os.path.join(out, "checkpoint.pt"), weights_only=False)
+    assert ck3["epoch"] == 3
+    # momentum buffers travelled through the checkpoint (optimizer state restored, then advanced)
+    assert len(ck3["optimizer"]["state"]) == 62
+    lines = open(os.path.join(out, "metrics_rank0.csv")).read().splitlines()
+    assert [ln.split(",")[0] for ln in lines] == ["epoch", "1", "2", "3"]
