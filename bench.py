@@ -50,7 +50,7 @@ def parse():
                    help="apply SGD inside the all-reduce kernel (default: on when N > 1)")
     p.add_argument("--no-fused-optimizer", dest="fused_optimizer", action="store_false")
     p.add_argument("--bucket-cap-mb", type=float, default=None)
-    p.add_argument("--allreduce-algo", default="auto", choices=["auto", "twoshot", "nvls"])
+    p.add_argument("--allreduce-algo", default="auto", choices=["auto", "twoshot", "nvls", "twoshot_mc"])
     p.add_argument("--comm-ctas", type=int, default=16,
                    help="CTAs of each bucket all-reduce kernel (fewer = less SM contention with backward)")
     p.add_argument("--eager-buffer-sync", action="store_true",

@@ -119,6 +119,26 @@ __device__ __forceinline__ uint32_t comm_pack_lp2(float a, float b, int f16) {
 }
 
 
+// NVLS: multimem.ld_reduce returns the in-switch sum of every rank's copy, multimem.st writes
+// every copy.  Rank r still owns slice r (so each element is reduced and broadcast exactly
+// once); link traffic per GPU is ~S instead of 2(N-1)/N*S and the reduction costs no SM adds.
+__device__ __forceinline__ float4 multimem_ld_reduce_f32x4(const float4* mc) {
+    float4 r;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+                 : "l"(mc)
+                 : "memory");
+    return r;
+}
+__device__ __forceinline__ void multimem_st_b64(void* mc, unsigned long long v) {
+    asm volatile("multimem.st.relaxed.sys.global.b64 [%0], %1;" ::"l"(mc), "l"(v) : "memory");
+}
+__device__ __forceinline__ void multimem_st_f32x4(float4* mc, float4 v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(v.x),
+                 "f"(v.y), "f"(v.z), "f"(v.w)
+                 : "memory");
+}
+
 // grads: symmetric buffers (float), n4 = number of float4.  In place.
 template <int WORLD>
 __global__ void __launch_bounds__(kCommThreads, 1)
@@ -188,10 +208,21 @@ allreduce_twoshot_kernel(CommCtx c, Peers grads, long long n4, Epilogue ep) {
                 uint2 pk;
                 pk.x = comm_pack_lp2(pa[0], pa[1], ep.shadow_f16);
                 pk.y = comm_pack_lp2(pa[2], pa[3], ep.shadow_f16);
+                if (ep.param_mc != nullptr) {
+                    // NVSwitch multicast push (dpt_allreduce_fused_mcpush): ONE store each for the
+                    // new weights and their 16-bit shadow, replicated to every rank by the switch,
+                    // instead of WORLD peer stores each — 8x fewer store instructions and 8x less
+                    // outbound link traffic for this phase at 8 GPUs
+                    multimem_st_f32x4(reinterpret_cast<float4*>(ep.param_mc) + i, np);
+                    multimem_st_b64(reinterpret_cast<uint2*>(ep.shadow_mc) + i,
+                                    static_cast<unsigned long long>(pk.x) |
+                                        (static_cast<unsigned long long>(pk.y) << 32));
+                } else {
 #pragma unroll
-                for (int p = 0; p < WORLD; ++p) {
-                    st_stream(reinterpret_cast<float4*>(ep.param[p]) + i, np);
-                    reinterpret_cast<uint2*>(ep.shadow[p])[i] = pk;
+                    for (int p = 0; p < WORLD; ++p) {
+                        st_stream(reinterpret_cast<float4*>(ep.param[p]) + i, np);
+                        reinterpret_cast<uint2*>(ep.shadow[p])[i] = pk;
+                    }
                 }
             }
         }
@@ -261,26 +292,6 @@ broadcast_kernel(CommCtx c, Peers bufs, long long n16, int src) {
     }
     xgpu_barrier(c, e0 + 2);
     if (threadIdx.x == 0) c.epoch[blockIdx.x] = e0 + 2;
-}
-
-// NVLS: multimem.ld_reduce returns the in-switch sum of every rank's copy, multimem.st writes
-// every copy.  Rank r still owns slice r (so each element is reduced and broadcast exactly
-// once); link traffic per GPU is ~S instead of 2(N-1)/N*S and the reduction costs no SM adds.
-__device__ __forceinline__ float4 multimem_ld_reduce_f32x4(const float4* mc) {
-    float4 r;
-    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
-                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
-                 : "l"(mc)
-                 : "memory");
-    return r;
-}
-__device__ __forceinline__ void multimem_st_b64(void* mc, unsigned long long v) {
-    asm volatile("multimem.st.relaxed.sys.global.b64 [%0], %1;" ::"l"(mc), "l"(v) : "memory");
-}
-__device__ __forceinline__ void multimem_st_f32x4(float4* mc, float4 v) {
-    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(v.x),
-                 "f"(v.y), "f"(v.z), "f"(v.w)
-                 : "memory");
 }
 
 __global__ void __launch_bounds__(kCommThreads, 1)
@@ -502,11 +513,11 @@ static void launch_oneshot(const dpt_comm* c, const Peers& g, float* out, long l
 //   algo: 0 auto, 1 one-shot (needs `scratch_out`... see dpt_allreduce_oneshot), 2 two-shot
 //   scale: static multiplier (1/world); inv_scale: optional device scalar; found_inf[r]: optional
 //   sgd: optional fused update (param[r], shadow[r] for every rank; local momentum).
-extern "C" int dpt_allreduce_fused(dpt_comm* c, void* const* bufs, long long n, float scale,
-                                   const float* inv_scale, void* const* found_inf,
-                                   void* const* param, void* const* shadow, float* momentum,
-                                   float lr, float mu, float wd, int nesterov, int ctas,
-                                   void* stream) {
+static int allreduce_fused_impl(dpt_comm* c, void* const* bufs, long long n, float scale,
+                                const float* inv_scale, void* const* found_inf,
+                                void* const* param, void* const* shadow, float* momentum,
+                                void* param_mc, void* shadow_mc, float lr, float mu, float wd,
+                                int nesterov, int ctas, void* stream) {
     if (n % 4 != 0) return DPT_ERR_SHAPE;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const int world = c->ctx.world;
@@ -524,6 +535,10 @@ extern "C" int dpt_allreduce_fused(dpt_comm* c, void* const* bufs, long long n, 
         ep.mu = mu;
         ep.wd = wd;
         ep.nesterov = nesterov;
+        if (param_mc != nullptr && shadow_mc != nullptr) {
+            ep.param_mc = static_cast<float*>(param_mc);
+            ep.shadow_mc = static_cast<__nv_bfloat16*>(shadow_mc);
+        }
     }
     if (world == 1) {
         if (ep.fused_sgd) return DPT_ERR_ARG;  // single GPU: use dpt_sgd_flat (same math)
@@ -549,6 +564,30 @@ extern "C" int dpt_allreduce_fused(dpt_comm* c, void* const* bufs, long long n, 
         default: return DPT_ERR_ARG;
     }
     return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int dpt_allreduce_fused(dpt_comm* c, void* const* bufs, long long n, float scale,
+                                   const float* inv_scale, void* const* found_inf,
+                                   void* const* param, void* const* shadow, float* momentum,
+                                   float lr, float mu, float wd, int nesterov, int ctas,
+                                   void* stream) {
+    return allreduce_fused_impl(c, bufs, n, scale, inv_scale, found_inf, param, shadow, momentum,
+                                nullptr, nullptr, lr, mu, wd, nesterov, ctas, stream);
+}
+
+// EXPERIMENTAL (not yet run on hardware): dpt_allreduce_fused with the SGD update fused, where
+// the owner publishes the new weights / 16-bit shadow with one NVSwitch multicast store each
+// (`param_mc` / `shadow_mc` = this rank's multicast mappings of the same arenas at the bucket's
+// offset) instead of one store per peer.  The reduce phase still pulls the peers' gradients P2P.
+extern "C" int dpt_allreduce_fused_mcpush(dpt_comm* c, void* const* bufs, long long n, float scale,
+                                          const float* inv_scale, void* const* found_inf,
+                                          void* const* param, void* const* shadow,
+                                          float* momentum, void* param_mc, void* shadow_mc,
+                                          float lr, float mu, float wd, int nesterov, int ctas,
+                                          void* stream) {
+    if (param == nullptr || param_mc == nullptr || shadow_mc == nullptr) return DPT_ERR_ARG;
+    return allreduce_fused_impl(c, bufs, n, scale, inv_scale, found_inf, param, shadow, momentum,
+                                param_mc, shadow_mc, lr, mu, wd, nesterov, ctas, stream);
 }
 
 // One-shot variant: out (local, n floats) = scale * sum_r in[r].  `in` buffers may be reused by

@@ -86,6 +86,7 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
         .def("set_scale_options", &Reducer::set_scale_options)
         .def("set_enabled", &Reducer::set_enabled)
         .def("set_nvls", &Reducer::set_nvls)
+        .def("set_mc_push", &Reducer::set_mc_push)
         .def("prepare_for_backward", &Reducer::prepare_for_backward)
         .def("mark_ready", &Reducer::mark_ready)
         .def("finalize", &Reducer::finalize)

@@ -165,6 +165,22 @@ void Reducer::launch_bucket(int b, cudaStream_t compute) {
         ++launches_;
         return;
     }
+    if (fuse && mc_push_ && fusion_.param_mc != 0 && fusion_.shadow_mc != 0) {
+        int rc3 = dpt_allreduce_fused_mcpush(
+            comm_, bufs, bk.numel, 1.0f / static_cast<float>(world_),
+            reinterpret_cast<const float*>(inv_scale_),
+            (check_finite_ && !found_inf_ptrs_.empty()) ? finf : nullptr, prm, shd,
+            reinterpret_cast<float*>(fusion_.momentum + bk.offset * 4),
+            reinterpret_cast<void*>(fusion_.param_mc + bk.offset * 4),
+            reinterpret_cast<void*>(fusion_.shadow_mc + bk.offset * 2), fusion_.lr, fusion_.mu,
+            fusion_.wd, fusion_.nesterov, ctas_, comm_stream_);
+        if (rc3 != 0)
+            throw std::runtime_error("dpt_allreduce_fused_mcpush failed with code " +
+                                     std::to_string(rc3));
+        DPTR_CUDA(cudaEventRecord(ev_done_[b], comm_stream_));
+        ++launches_;
+        return;
+    }
     int rc = dpt_allreduce_fused(
         comm_, bufs, bk.numel, 1.0f / static_cast<float>(world_),
         reinterpret_cast<const float*>(inv_scale_),

@@ -76,6 +76,10 @@ class Reducer {
         nvls_with_fusion_ = with_fused_sgd;
     }
 
+    // Fused-SGD two-shot buckets publish through the NVSwitch multicast mappings in the SgdFusion
+    // (param_mc / shadow_mc) instead of per-peer stores.  Experimental.
+    void set_mc_push(bool on) { mc_push_ = on; }
+
     void prepare_for_backward(uintptr_t compute_stream);
     void mark_ready(int param_index, uintptr_t compute_stream);
     // Makes `compute_stream` wait for every launched bucket.  Returns the number launched.
@@ -115,6 +119,7 @@ class Reducer {
     int64_t nvls_min_bytes_ = 0;
     int rank_ = 0;
     bool nvls_with_fusion_ = false;
+    bool mc_push_ = false;
 };
 
 }  // namespace dptr

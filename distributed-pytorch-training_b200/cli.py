@@ -44,7 +44,7 @@ def build_parser() -> argparse.ArgumentParser:
                         "exists (for torchrun --max-restarts)")
     p.add_argument("--bucket-cap-mb", default=25.0, type=float, help="gradient bucket size cap")
     p.add_argument("--allreduce-algo", default="auto",
-                   choices=["auto", "autotune", "oneshot", "twoshot", "nvls"],
+                   choices=["auto", "autotune", "oneshot", "twoshot", "nvls", "twoshot_mc"],
                    help="peer-memory all-reduce algorithm for the native backend")
     p.add_argument("--fused-optimizer", action="store_true",
                    help="apply the SGD update inside the all-reduce kernel (bf16/FP32 only)")

@@ -202,8 +202,12 @@ class DistributedDataParallel(nn.Module):
         self.allreduce_algo = allreduce_algo
         # auto: NVLS only pays off when the in-switch reduction saves link traffic (2(N-1)/N*S vs
         # S per GPU): measured slower than two-shot at N=2, so it is considered from N >= 4
+        # "twoshot_mc" (experimental): two-shot reduce, fused SGD, publish through one multicast
+        # store instead of per-peer stores — needs multicast-bound arenas like NVLS does
+        self._mc_push = allreduce_algo == "twoshot_mc"
         want_nvls = backend == "native" and self.world_size > 1 and (
-            allreduce_algo in ("nvls", "autotune") or (allreduce_algo == "auto" and self.world_size >= 4))
+            allreduce_algo in ("nvls", "autotune", "twoshot_mc")
+            or (allreduce_algo == "auto" and self.world_size >= 4))
         self.arena = ParamArena(params, self.device, comm=self.comm if backend == "native" else None,
                                 multicast=want_nvls)
         self.nvls = want_nvls and hasattr(self.arena.grad_buf, "mc_ptr")
@@ -235,7 +239,7 @@ class DistributedDataParallel(nn.Module):
                 else:
                     nvls_min_bytes = thr
                 self._logging["autotune"] = str(self.autotune_result["table"])
-            if self.nvls:
+            if self.nvls and not self._mc_push:
                 # measured crossover: the multimem kernel wins from ~1 MB up (profiles/README.md)
                 self.reducer.set_nvls(self.arena.grad_buf.mc_ptr,
                                       0 if allreduce_algo == "nvls" else int(nvls_min_bytes),
@@ -335,6 +339,11 @@ class DistributedDataParallel(nn.Module):
             f.param_mc = self.arena.param_buf.mc_ptr
             f.shadow_mc = self.arena.shadow_buf.mc_ptr
         self.reducer.set_fusion(f)
+        if getattr(self, "_mc_push", False):
+            if not f.param_mc or not f.shadow_mc:
+                raise RuntimeError("allreduce_algo='twoshot_mc' needs NVSwitch multicast "
+                                   "(not exposed on this host)")
+            self.reducer.set_mc_push(True)
         optimizer.skip_update = True
         self._fusion_cfg = f
         return True

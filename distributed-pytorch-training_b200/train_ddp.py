@@ -47,7 +47,7 @@ def main(argv=None):
         print("[grad-sync] --cuda-graph: per-bucket timing disabled (run without --cuda-graph "
               "to profile gradient sync)")
     algo = {"auto": "auto", "autotune": "autotune", "oneshot": "twoshot", "twoshot": "twoshot",
-            "nvls": "nvls"}[args.allreduce_algo]
+            "nvls": "nvls", "twoshot_mc": "twoshot_mc"}[args.allreduce_algo]
     model = maybe_wrap_ddp(model, device, local_rank, backend=args.backend,
                            bucket_cap_mb=args.bucket_cap_mb if args.bucket_cap_mb != 25.0 else None,
                            profile=bucket_profile, comm_timeout=args.comm_timeout,

@@ -168,6 +168,12 @@ int dpt_allreduce_fused(dpt_comm* c, void* const* bufs, long long n, float scale
                         const float* inv_scale, void* const* found_inf, void* const* param,
                         void* const* shadow, float* momentum, float lr, float mu, float wd,
                         int nesterov, int ctas, void* stream);
+/* EXPERIMENTAL: fused-SGD two-shot all-reduce whose publish phase is one multicast store
+ * (param_mc / shadow_mc: multicast mappings of the parameter / shadow arenas at this bucket). */
+int dpt_allreduce_fused_mcpush(dpt_comm* c, void* const* bufs, long long n, float scale,
+                               const float* inv_scale, void* const* found_inf, void* const* param,
+                               void* const* shadow, float* momentum, void* param_mc, void* shadow_mc,
+                               float lr, float mu, float wd, int nesterov, int ctas, void* stream);
 int dpt_allreduce_oneshot(dpt_comm* c, void* const* in, float* out, long long n, float scale,
                           const float* inv_scale, void* const* found_inf, int ctas, void* stream);
 /* NVLS (NVSwitch multicast) variant: multimem.ld_reduce + multimem.st through `mc`, this rank's

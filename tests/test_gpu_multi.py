@@ -254,9 +254,13 @@ def _trainstep_worker(rank, world):
     from dpt_b200.parallel.ddp import DistributedDataParallel as OurDDP
     dev = torch.device("cuda", rank)
     shape = (32, 3, 32, 32)
-    for graph, fused, fp16_scaler, algo in ((False, False, False, "twoshot"), (True, False, False, "twoshot"),
-                                            (True, True, False, "twoshot"), (True, False, True, "twoshot"),
-                                            (True, False, False, "nvls"), (True, True, False, "nvls")):
+    configs = [(False, False, False, "twoshot"), (True, False, False, "twoshot"),
+               (True, True, False, "twoshot"), (True, False, True, "twoshot"),
+               (True, False, False, "nvls"), (True, True, False, "nvls")]
+    if os.environ.get("DPT_TEST_MCPUSH", "0") == "1":
+        # experimental: fused-SGD two-shot whose publish phase is one multicast store
+        configs.append((True, True, False, "twoshot_mc"))
+    for graph, fused, fp16_scaler, algo in configs:
         torch.manual_seed(11 + rank)
         model = OurDDP(build_model(dev, "resnet18", 10), device_ids=[rank], backend="native",
                        allreduce_algo=algo)
