@@ -31,17 +31,36 @@ def main():
         peaks = json.load(open(p))
     peak = peaks.get("bf16_tflops", 1590.0)
     out = {"gemm": [], "conv": []}
+    from dpt_b200.ops import _lib
+    lib = _lib.lib()
+    two_sm = "--two-sm" in sys.argv      # also time the experimental cta_group::2 GEMM
     for n in (2048, 4096, 8192):
         A = torch.randn(n, n, device=dev).bfloat16()
         B = torch.randn(n, n, device=dev).bfloat16()
         C = torch.empty(n, n, device=dev, dtype=torch.bfloat16)
         for op, name in ((0, "NT"), (1, "NN")):
-            t = timeit(lambda: Fn.gemm(op, A, B, C, n, n, n, n, n, n, out_mode=0), iters=20)
-            tf = 2 * n ** 3 / t / 1e6
+            row = {"n": n, "op": name}
+            # default policy (persistent variant from 592 tiles) and the one-tile-per-CTA deep ring
+            for label, min_tiles in (("", 0), ("_one_tile", 1 << 40)):
+                lib.dpt_igemm_set_persist(min_tiles, 0)
+                t = timeit(lambda: Fn.gemm(op, A, B, C, n, n, n, n, n, n, out_mode=0), iters=20)
+                row["us" + label] = t
+                row["tflops" + label] = 2 * n ** 3 / t / 1e6
+            lib.dpt_igemm_set_persist(0, 0)
+            t, tf = row["us"], row["tflops"]
+            row["frac_of_measured_peak"] = tf / peak
             ref = timeit(lambda: torch.matmul(A, B.t() if op == 0 else B, out=C), iters=20)
-            out["gemm"].append({"n": n, "op": name, "us": t, "tflops": tf, "frac_of_measured_peak": tf / peak,
-                                "cublas_us": ref})
-            print(f"gemm {name} {n}^3: {t:9.1f} us  {tf:7.1f} TFLOP/s ({100*tf/peak:4.1f}% of measured {peak:.0f})  cuBLAS {ref:9.1f} us", flush=True)
+            row["cublas_us"] = ref
+            if two_sm and op == 0:
+                st = torch.cuda.current_stream().cuda_stream
+                t2 = timeit(lambda: lib.dpt_gemm2sm_bf16(A.data_ptr(), B.data_ptr(), C.data_ptr(), n, n, n,
+                                                         n, n, n, 0, 0, st), iters=20)
+                row["two_sm_us"] = t2
+                row["two_sm_tflops"] = 2 * n ** 3 / t2 / 1e6
+            out["gemm"].append(row)
+            print(f"gemm {name} {n}^3: {t:9.1f} us  {tf:7.1f} TFLOP/s ({100*tf/peak:4.1f}% of measured {peak:.0f})  "
+                  f"one-tile {row['us_one_tile']:9.1f} us  cuBLAS {ref:9.1f} us"
+                  + (f"  two-SM {row['two_sm_us']:9.1f} us" if "two_sm_us" in row else ""), flush=True)
     # (N, H, W, Cin, Cout, k, s, p) ResNet-18 @ 128x3x32x32
     shapes = [(128, 8, 8, 64, 64, 3, 1, 1), (128, 8, 8, 64, 128, 3, 2, 1), (128, 4, 4, 128, 128, 3, 1, 1),
               (128, 4, 4, 128, 256, 3, 2, 1), (128, 2, 2, 256, 256, 3, 1, 1), (128, 2, 2, 256, 512, 3, 2, 1),
