@@ -634,6 +634,27 @@ static void pick_box(int rows, int Q, int P, int N, int* bq, int* bp, int* bn) {
 static long long g_persist_min_tiles = 4 * 148;
 static int g_persist_grid = 2 * 148;
 
+// Opt-in 128 x 256 tiles (DPT_IGEMM_BN256=1 / dpt_igemm_set_bn256): per k-step a CTA stages
+// 16 KB of A and 32 KB of B for twice the math of a 128 x 128 tile, i.e. 25 % less operand traffic
+// per FLOP — the 1-CTA kernel is L2-bandwidth bound on long k loops (profiles/README.md).  Not
+// yet measured on hardware, hence off by default.
+static int g_bn256 = -1;
+static bool bn256_enabled() {
+    if (g_bn256 < 0) {
+        const char* e = std::getenv("DPT_IGEMM_BN256");
+        g_bn256 = (e != nullptr && e[0] == '1') ? 1 : 0;
+    }
+    return g_bn256 != 0;
+}
+// Output-column tile width: 64 below 128 columns, else 128, or 256 when enabled, the column count
+// is a multiple of 256 and `other_tiles` x (cols / 256) still fills two waves of the 148 SMs.
+static int pick_block_n(int cols, long long other_tiles) {
+    if (bn256_enabled() && esz() == 2 && cols % 256 == 0 &&
+        other_tiles * (cols / 256) >= 2 * 148)
+        return 256;
+    return cols >= 128 ? 128 : 64;
+}
+
 template <int MODE, int BLOCK_N, int NST, bool PERSIST>
 static int launch_cfg(const IgemmMaps& maps, const IgemmParams& prm_in, dim3 grid, cudaStream_t st) {
     constexpr int kBStageBytes = BLOCK_N * 128;
@@ -663,7 +684,8 @@ static int launch_cfg(const IgemmMaps& maps, const IgemmParams& prm_in, dim3 gri
         prm.pgx = static_cast<int>(grid.x);
         prm.pgy = static_cast<int>(grid.y);
         prm.ptiles = static_cast<int>(grid.x * grid.y * grid.z);
-        const int resident = g_persist_grid;
+        // 256-wide tiles take all 512 TMEM columns when double buffered: one CTA per SM
+        const int resident = (BLOCK_N == 256 && g_persist_grid > 148) ? 148 : g_persist_grid;
         grid = dim3(prm.ptiles < resident ? prm.ptiles : resident, 1, 1);
     }
     cudaError_t le = launch_pdl(kern, grid, dim3(PERSIST ? kNumThreadsPersist : kNumThreads),
@@ -691,6 +713,10 @@ static int launch(const IgemmMaps& maps, const IgemmParams& prm, dim3 grid, int 
     }
     const long long ctas = static_cast<long long>(grid.x) * grid.y * grid.z;
     const bool many = persist && ctas >= g_persist_min_tiles && ctas < (1LL << 31);
+    if (block_n == 256) {   // 4 x 48 KB stages, one CTA per SM either way
+        if (many) return launch_cfg<MODE, 256, 4, true>(maps, prm, grid, st);
+        return launch_cfg<MODE, 256, 4, false>(maps, prm, grid, st);
+    }
     if (block_n == 128) {
         if (many) return launch_cfg<MODE, 128, 3, true>(maps, prm, grid, st);
         return launch_cfg<MODE, 128, 6, false>(maps, prm, grid, st);
@@ -785,6 +811,13 @@ extern "C" int dpt_igemm_set_persist(long long min_tiles, int grid_ctas) {
     return 0;
 }
 
+// 128 x 256 output tiles where the column count allows it (see pick_block_n); < 0 re-reads the
+// DPT_IGEMM_BN256 environment variable.
+extern "C" int dpt_igemm_set_bn256(int on) {
+    dpt::g_bn256 = on < 0 ? -1 : (on ? 1 : 0);
+    return 0;
+}
+
 extern "C" int dpt_conv_fprop(const void* x, const void* w, void* y, int N, int H, int W, int Cin,
                               int Cout, int R, int S, int stride, int pad, float* stat_sum,
                               float* stat_sq, int out_f32_atomic, int splits, void* stream) {
@@ -796,7 +829,8 @@ extern "C" int dpt_conv_fprop(const void* x, const void* w, void* y, int N, int 
     pick_box(kTileM, Q, P, N, &prm.bq, &prm.bp, &prm.bn);
     int e = build_act_maps(maps.a, x, N, H, W, Cin, stride, kTileM, prm.bq, prm.bp, prm.bn);
     if (e) return e;
-    const int block_n = (Cout >= 128) ? 128 : 64;
+    const int block_n =
+        pick_block_n(Cout, ((long long)N * P * Q + kTileM - 1) / kTileM);
     {
         const long long dims[2] = {(long long)R * S * Cin, Cout};
         const long long str[1] = {(long long)R * S * Cin};
@@ -885,7 +919,7 @@ extern "C" int dpt_conv_dgrad_ex(const void* dy, const void* w, void* dx, int N,
         }
         maps.a[2] = maps.a[3] = maps.a[0];
     }
-    const int block_n = (Cin >= 128) ? 128 : 64;
+    const int block_n = pick_block_n(Cin, ((long long)N * H * W + kTileM - 1) / kTileM);
     {
         const long long dims[2] = {(long long)R * S * Cin, Cout};
         const long long str[1] = {(long long)R * S * Cin};
@@ -980,7 +1014,7 @@ extern "C" int dpt_conv_wgrad(const void* dy, const void* x, float* dw, int N, i
         tb.taps[i].b_map = tb.taps[i].a_map;  // activation parity view lives on the B side here
     }
     memcpy(prm.taps, tb.taps, sizeof(IgemmTap) * tb.ntaps);
-    const int block_n = (Cin >= 128) ? 128 : 64;
+    const int block_n = pick_block_n(Cin, 1 << 20);   // wgrad fills the SMs through its splits
     prm.tiles_q = (Q + prm.bq - 1) / prm.bq;
     prm.tiles_p = (P + prm.bp - 1) / prm.bp;
     prm.tiles_n = (N + prm.bn - 1) / prm.bn;
@@ -1024,7 +1058,7 @@ extern "C" int dpt_gemm_bf16(int op, const void* A, const void* B, void* C, int 
     IgemmParams prm;
     memset(&prm, 0, sizeof(prm));
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    const int block_n = (N >= 128) ? 128 : 64;
+    const int block_n = pick_block_n(N, op == 2 ? (1 << 20) : (M + kTileM - 1) / kTileM);
     prm.nclasses = 1;
     prm.cls_begin[0] = 0;
     for (int c = 1; c < 5; ++c) prm.cls_begin[c] = 1;

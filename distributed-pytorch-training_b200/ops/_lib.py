@@ -51,6 +51,7 @@ _SIGS = {
     "dpt_adam_flat": [vp, vp, vp, vp, vp, i64, f32, f32, f32, f32, f32, i32, vp, vp, vp, vp],
     "dpt_cast_f32_to_bf16": [vp, vp, i64, vp],
     "dpt_igemm_set_persist": [i64, i32],
+    "dpt_igemm_set_bn256": [i32],
     "dpt_gemm2sm_bf16": [vp, vp, vp, i32, i32, i32, i64, i64, i64, i32, i32, vp],
     "dpt_pdl_skip_next": [],
     "dpt_set_lowp_dtype": [i32],

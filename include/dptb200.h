@@ -40,6 +40,9 @@ int dpt_gemm2sm_bf16(const void* A, const void* B, void* C, int M, int N, int K,
  * double-buffered TMEM accumulator): used from `min_tiles` tiles upwards with `grid_ctas` CTAs;
  * <= 0 restores the defaults (4 waves, 2 CTAs per SM). */
 int dpt_igemm_set_persist(long long min_tiles, int grid_ctas);
+/* EXPERIMENTAL 128x256 output tiles (25 % less operand traffic per FLOP) where the column count
+ * is a multiple of 256; also DPT_IGEMM_BN256=1.  Off by default. */
+int dpt_igemm_set_bn256(int on);
 int dpt_conv_fprop(const void* x, const void* w, void* y, int N, int H, int W, int Cin, int Cout,
                    int R, int S, int stride, int pad, float* stat_sum, float* stat_sq,
                    int out_f32_atomic, int splits, void* stream);

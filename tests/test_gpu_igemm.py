@@ -233,3 +233,53 @@ def test_persistent_default_policy_large_grid():
     refx = torch.nn.grad.conv2d_input((N, Cin, H, W), w.float().permute(0, 3, 1, 2),
                                       dy.float().permute(0, 3, 1, 2), stride=1, padding=0)
     _close(dx.permute(0, 3, 1, 2), refx, 1e-2, "dgrad large")
+
+
+# ---------------------------------------------------------------------------------------------
+# Experimental 128 x 256 tiles (DPT_IGEMM_BN256 / dpt_igemm_set_bn256): opt-in until validated.
+@pytest.mark.skipif(__import__("os").environ.get("DPT_TEST_BN256", "0") != "1",
+                    reason="experimental 128x256 tiles: opt in with DPT_TEST_BN256=1")
+@pytest.mark.parametrize("persistent", [False, True])
+def test_block_n_256_all_passes(persistent):
+    from dpt_b200.ops import _lib
+    lib = _lib.lib()
+    Fn = _F()
+    lib.dpt_igemm_set_bn256(1)
+    lib.dpt_igemm_set_persist(1 if persistent else (1 << 40), 7 if persistent else 0)
+    try:
+        N, H, W, Cin, Cout = 64, 28, 28, 256, 512            # 392 row tiles x 2 (or 1) column tiles
+        x = _mk((N, H, W, Cin), 1.0, 61)
+        w = _mk((Cout, 1, 1, Cin), 0.05, 62)
+        ssum = torch.zeros(Cout, device="cuda")
+        ssq = torch.zeros(Cout, device="cuda")
+        y = Fn.conv_fprop(x, w, 1, 0, stats=(ssum, ssq))
+        torch.cuda.synchronize()
+        ref = _ref_conv(x, w, 1, 0)
+        _close(y.permute(0, 3, 1, 2), ref, 1e-2, "fprop bn256")
+        _close(ssum, ref.sum(dim=(0, 2, 3)), 5e-3, "stat sum bn256")
+        _close(ssq, (ref * ref).sum(dim=(0, 2, 3)), 5e-3, "stat sq bn256")
+        dy = _mk((N, H, W, Cout), 1.0, 63)
+        dx = Fn.conv_dgrad(dy, w, (N, H, W, Cin), 1, 0)
+        dw = Fn.conv_wgrad(dy, x, (Cout, 1, 1, Cin), 1, 0)
+        torch.cuda.synchronize()
+        refx = torch.nn.grad.conv2d_input((N, Cin, H, W), w.float().permute(0, 3, 1, 2),
+                                          dy.float().permute(0, 3, 1, 2), stride=1, padding=0)
+        refw = torch.nn.grad.conv2d_weight(x.float().permute(0, 3, 1, 2), (Cout, Cin, 1, 1),
+                                           dy.float().permute(0, 3, 1, 2), stride=1, padding=0)
+        _close(dx.permute(0, 3, 1, 2), refx, 1e-2, "dgrad bn256")
+        _close(dw.permute(0, 3, 1, 2), refw, 2e-3, "wgrad bn256")
+        # 3x3 with padding: the halo taps and the k loop over 9 taps x 4 chunks
+        w3 = _mk((256, 3, 3, Cin), 0.05, 64)
+        y3 = Fn.conv_fprop(x, w3, 1, 1)
+        torch.cuda.synchronize()
+        _close(y3.permute(0, 3, 1, 2), _ref_conv(x, w3, 1, 1), 1e-2, "fprop 3x3 bn256")
+        M, Ng, K = 20000, 512, 264
+        A = _mk((M, K), 1.0, 65)
+        B = _mk((Ng, K), 0.05, 66)
+        C = torch.empty((M, Ng), device="cuda", dtype=torch.float32)
+        Fn.gemm(0, A, B, C, M, Ng, K, K, K, Ng, out_mode=1)
+        torch.cuda.synchronize()
+        _close(C, A.float() @ B.float().t(), 2e-3, "gemm NT bn256")
+    finally:
+        lib.dpt_igemm_set_bn256(0)
+        lib.dpt_igemm_set_persist(0, 0)
