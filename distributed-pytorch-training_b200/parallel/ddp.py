@@ -546,6 +546,22 @@ class DistributedDataParallel(nn.Module):
             "has_sync_bn": 0,
             "iteration": self._iter,
         }
+        # runtime statistics under torch's key names (logger.hpp:90-110), in nanoseconds, from the
+        # device-side events of the last profiled backward (profile=True, eager mode); 0 otherwise
+        stats = {"avg_forward_compute_time": 0, "avg_backward_compute_time": 0,
+                 "avg_backward_comm_time": 0, "avg_backward_compute_comm_overlap_time": 0}
+        try:
+            t = self.sync_timings()
+        except Exception:  # noqa: BLE001 - no device / nothing recorded yet
+            t = {}
+        if t and t.get("buckets"):
+            busy = sum(b["end_ms"] - b["start_ms"] for b in t["buckets"])
+            exposed = max(0.0, max(b["end_ms"] for b in t["buckets"])
+                          - max(b["ready_ms"] for b in t["buckets"]))
+            stats["avg_backward_compute_time"] = int(t["backward_ms"] * 1e6)
+            stats["avg_backward_comm_time"] = int(busy * 1e6)
+            stats["avg_backward_compute_comm_overlap_time"] = int(max(0.0, busy - exposed) * 1e6)
+        data.update(stats)
         data.update(self._logging)
         return data
 

@@ -70,6 +70,9 @@ def _ddp_parity_worker(rank, world, port, q):
         log = ours._get_ddp_logging_data()
         assert log["world_size"] == world and log["num_parameter_tensors"] == 62
         assert log["total_parameter_size_bytes"] == 44726568
+        for k in ("avg_forward_compute_time", "avg_backward_compute_time", "avg_backward_comm_time",
+                  "avg_backward_compute_comm_overlap_time"):
+            assert k in log                               # torch Logger's runtime keys (ns)
         q.put((rank, "ok"))
     except Exception as e:  # noqa: BLE001
         import traceback
