@@ -61,13 +61,9 @@ def _stale(src: Path, obj: Path, hdr_m: float) -> bool:
 
 
 def _extra_defines() -> list[str]:
-    """Opt-in build variants selected through the environment (each changes the object names, so
-    switching back and forth never links stale objects):
-      DPT_VEC128=1  whole-register (128-bit) activation vectors in the elementwise kernels."""
-    out = []
-    if os.environ.get("DPT_VEC128", "0") == "1":
-        out.append("-DDPT_VEC128=1")
-    return out
+    """Build variants selected through the environment (each changes the object names, so switching
+    back and forth never links stale objects).  None at the moment."""
+    return []
 
 
 def build_kernels(verbose: bool = False) -> Path:

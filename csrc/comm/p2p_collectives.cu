@@ -43,6 +43,31 @@ struct CommCtx {
     uint32_t* epoch;             // local: [kMaxCommCtas] barrier counters
     uint32_t* err;               // local (host-mapped) error word, 0 = ok
     unsigned long long timeout_ns;
+    // optional timeline buffer (dpt_comm_set_trace): every collective kernel appends
+    // {kind/bytes, start, after first barrier, end} globaltimer stamps (CTA 0, thread 0)
+    unsigned long long* trace;
+    uint32_t trace_cap;          // records of 4 u64; trace[0] is the atomic cursor
+};
+
+__device__ __forceinline__ unsigned long long globaltimer_ns();
+
+// Timeline record for the step-trace tool (benchmarks/step_trace.py): 4 u64 per record.
+struct TraceRec {
+    unsigned long long* slot;
+    __device__ __forceinline__ void begin(const CommCtx& c, uint32_t kind, long long bytes) {
+        slot = nullptr;
+        if (c.trace == nullptr || blockIdx.x != 0 || threadIdx.x != 0) return;
+        const unsigned long long i = atomicAdd(c.trace, 1ULL);
+        if (i >= c.trace_cap) return;
+        slot = c.trace + 4 + 4 * i;
+        slot[0] = (static_cast<unsigned long long>(kind) << 56) | static_cast<unsigned long long>(bytes);
+        slot[1] = globaltimer_ns();
+        slot[2] = 0;
+        slot[3] = 0;
+    }
+    __device__ __forceinline__ void mark(int k) {
+        if (slot != nullptr) slot[k] = globaltimer_ns();
+    }
 };
 
 struct Peers {
@@ -147,7 +172,10 @@ allreduce_twoshot_kernel(CommCtx c, Peers grads, long long n4, Epilogue ep) {
     if (threadIdx.x == 0) s_epoch = c.epoch[blockIdx.x];
     __syncthreads();
     const uint32_t e0 = s_epoch;
+    TraceRec tr;
+    tr.begin(c, 2u, n4 * 16);
     xgpu_barrier(c, e0 + 1);  // every peer's bucket is complete and its consumers are done
+    tr.mark(2);
     constexpr int kUnroll = WORLD > 4 ? 2 : 4;  // keep WORLD * kUnroll float4 in registers
 
     const long long per = (n4 + WORLD - 1) / WORLD;
@@ -232,6 +260,7 @@ allreduce_twoshot_kernel(CommCtx c, Peers grads, long long n4, Epilogue ep) {
         for (int p = 0; p < WORLD; ++p) *ep.found_inf[p] = 1.f;
     }
     xgpu_barrier(c, e0 + 2);  // all slices have landed everywhere
+    tr.mark(3);
     if (threadIdx.x == 0) c.epoch[blockIdx.x] = e0 + 2;
 }
 
@@ -300,7 +329,10 @@ allreduce_nvls_kernel(CommCtx c, float* __restrict__ mc, long long n4, Epilogue 
     if (threadIdx.x == 0) s_epoch = c.epoch[blockIdx.x];
     __syncthreads();
     const uint32_t e0 = s_epoch;
+    TraceRec tr;
+    tr.begin(c, 3u, n4 * 16);
     xgpu_barrier(c, e0 + 1);
+    tr.mark(2);
     const long long per = (n4 + c.world - 1) / c.world;
     const long long lo = per * c.rank;
     const long long hi = min(n4, lo + per);
@@ -356,7 +388,95 @@ allreduce_nvls_kernel(CommCtx c, float* __restrict__ mc, long long n4, Epilogue 
         for (int p = 0; p < c.world; ++p) *ep.found_inf[p] = 1.f;
     }
     xgpu_barrier(c, e0 + 2);
+    tr.mark(3);
     if (threadIdx.x == 0) c.epoch[blockIdx.x] = e0 + 2;
+}
+
+// One-shot "push" all-reduce for small buckets (the exposed tail of backward): every rank stores
+// its contribution into slot [rank] of a staging area on every peer, ONE cross-GPU barrier, then
+// every rank reduces the WORLD slots it received from its own memory and applies the epilogue to
+// its own copy — no second barrier, no remote loads, (WORLD-1) x S bytes pushed per rank.
+//   * every rank sums in the same fixed order, so results are bitwise identical everywhere;
+//   * with the SGD update fused, each rank updates its own fp32 masters, momentum and 16-bit
+//     shadow for the WHOLE bucket (replicated update: nothing to publish, momentum not sharded);
+//   * the staging area is double buffered on a per-CTA use counter (epoch[kMaxCommCtas + cta]),
+//     so a fast rank pushing for step t+1 can never overwrite slots a slow rank still reduces
+//     for step t (it cannot be two uses ahead: each use ends behind a barrier with that rank).
+// Replaces, for small messages, the NCCL all-reduce torch DDP issues per bucket
+// (train_ddp.py:305-310; LL protocol in NCCL) + unscale + optimizer step.
+template <int WORLD>
+__global__ void __launch_bounds__(kCommThreads, 1)
+allreduce_oneshot_push_kernel(CommCtx c, float* __restrict__ grads, Peers staging, long long cap4,
+                              long long n4, Epilogue ep) {
+    __shared__ uint32_t s_epoch, s_use;
+    if (threadIdx.x == 0) {
+        s_epoch = c.epoch[blockIdx.x];
+        s_use = c.epoch[kMaxCommCtas + blockIdx.x];
+    }
+    __syncthreads();
+    const uint32_t e0 = s_epoch;
+    TraceRec tr;
+    tr.begin(c, 1u, n4 * 16);
+    const long long half = static_cast<long long>(s_use & 1u) * WORLD * cap4;
+    const long long step = static_cast<long long>(gridDim.x) * kCommThreads;
+    const long long first = static_cast<long long>(blockIdx.x) * kCommThreads + threadIdx.x;
+    const float4* g4 = reinterpret_cast<const float4*>(grads);
+    for (long long i = first; i < n4; i += step) {
+        const float4 v = g4[i];
+#pragma unroll
+        for (int p = 0; p < WORLD; ++p)
+            st_stream(reinterpret_cast<float4*>(staging.p[p]) + half + c.rank * cap4 + i, v);
+    }
+    xgpu_barrier(c, e0 + 1);  // CTA b of every peer has pushed exactly the elements CTA b reduces
+    tr.mark(2);
+    const float gs = ep.scale * (ep.inv_scale ? *ep.inv_scale : 1.f);
+    bool bad = false;
+    const float4* mine = reinterpret_cast<const float4*>(staging.p[c.rank]) + half;
+    for (long long i = first; i < n4; i += step) {
+        float4 s = ld_stream(mine + i);
+#pragma unroll
+        for (int p = 1; p < WORLD; ++p) {
+            const float4 v = ld_stream(mine + p * cap4 + i);
+            s.x += v.x;
+            s.y += v.y;
+            s.z += v.z;
+            s.w += v.w;
+        }
+        bad |= !(isfinite(s.x) && isfinite(s.y) && isfinite(s.z) && isfinite(s.w));
+        s.x *= gs;
+        s.y *= gs;
+        s.z *= gs;
+        s.w *= gs;
+        if (!ep.fused_sgd) {
+            reinterpret_cast<float4*>(grads)[i] = s;
+        } else {
+            float4 pv = reinterpret_cast<float4*>(ep.param[c.rank])[i];
+            float4 mv = reinterpret_cast<float4*>(ep.momentum)[i];
+            float pa[4] = {pv.x, pv.y, pv.z, pv.w};
+            float ma[4] = {mv.x, mv.y, mv.z, mv.w};
+            const float ga[4] = {s.x, s.y, s.z, s.w};
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                float d = fmaf(ep.wd, pa[k], ga[k]);
+                ma[k] = fmaf(ep.mu, ma[k], d);
+                d = ep.nesterov ? fmaf(ep.mu, ma[k], d) : ma[k];
+                pa[k] = fmaf(-ep.lr, d, pa[k]);
+            }
+            reinterpret_cast<float4*>(ep.momentum)[i] = make_float4(ma[0], ma[1], ma[2], ma[3]);
+            reinterpret_cast<float4*>(ep.param[c.rank])[i] = make_float4(pa[0], pa[1], pa[2], pa[3]);
+            uint2 pk;
+            pk.x = comm_pack_lp2(pa[0], pa[1], ep.shadow_f16);
+            pk.y = comm_pack_lp2(pa[2], pa[3], ep.shadow_f16);
+            reinterpret_cast<uint2*>(ep.shadow[c.rank])[i] = pk;
+        }
+    }
+    if (ep.found_inf[c.rank] != nullptr && __any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0)
+        *ep.found_inf[c.rank] = 1.f;   // every rank computes the same sums: a local flag suffices
+    tr.mark(3);
+    if (threadIdx.x == 0) {
+        c.epoch[blockIdx.x] = e0 + 1;
+        c.epoch[kMaxCommCtas + blockIdx.x] = s_use + 1;
+    }
 }
 
 __global__ void barrier_kernel(CommCtx c) {
@@ -438,9 +558,10 @@ extern "C" int dpt_comm_create(int rank, int world, void* const* flags, double t
     c->ctx.rank = rank;
     c->ctx.world = world;
     for (int r = 0; r < world; ++r) c->ctx.flags[r] = static_cast<uint32_t*>(flags[r]);
-    cudaError_t e = cudaMalloc(&c->ctx.epoch, sizeof(uint32_t) * kMaxCommCtas);
+    // [0, kMaxCommCtas): barrier epochs; [kMaxCommCtas, 2*kMaxCommCtas): one-shot use counters
+    cudaError_t e = cudaMalloc(&c->ctx.epoch, sizeof(uint32_t) * 2 * kMaxCommCtas);
     if (e != cudaSuccess) return static_cast<int>(e);
-    cudaMemset(c->ctx.epoch, 0, sizeof(uint32_t) * kMaxCommCtas);
+    cudaMemset(c->ctx.epoch, 0, sizeof(uint32_t) * 2 * kMaxCommCtas);
     e = cudaHostAlloc(reinterpret_cast<void**>(&c->err_host), sizeof(uint32_t), cudaHostAllocMapped);
     if (e != cudaSuccess) return static_cast<int>(e);
     *c->err_host = 0;
@@ -616,6 +737,87 @@ extern "C" int dpt_allreduce_oneshot(dpt_comm* c, void* const* in, float* out, l
         case 8: launch_oneshot<8>(c, g, out, n4, ep, ctas, st); break;
         default: return DPT_ERR_ARG;
     }
+    return static_cast<int>(cudaGetLastError());
+}
+
+// One-shot push all-reduce (small buckets).  `grads`: this rank's n floats (in place when the SGD
+// update is not fused); `staging[r]`: rank r's staging area of 2 * world * cap floats (symmetric
+// memory, cap % 4 == 0, n <= cap); `found_inf`, `param`, `shadow` are LOCAL pointers (the update
+// is replicated, nothing is published); param == NULL selects the F1 epilogue.
+extern "C" int dpt_allreduce_oneshot_push(dpt_comm* c, float* grads, void* const* staging,
+                                          long long cap, long long n, float scale,
+                                          const float* inv_scale, float* found_inf, float* param,
+                                          void* shadow, float* momentum, float lr, float mu,
+                                          float wd, int nesterov, int ctas, void* stream) {
+    if (n % 4 != 0 || cap % 4 != 0) return DPT_ERR_SHAPE;
+    if (n > cap) return DPT_ERR_TOO_LARGE;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int world = c->ctx.world;
+    if (world < 2) return DPT_ERR_ARG;
+    const long long n4 = n / 4;
+    Epilogue ep;
+    memset(&ep, 0, sizeof(ep));
+    ep.shadow_f16 = g_comm_shadow_f16;
+    ep.scale = scale;
+    ep.inv_scale = inv_scale;
+    ep.found_inf[c->ctx.rank] = found_inf;
+    if (param != nullptr) {
+        ep.fused_sgd = 1;
+        ep.param[c->ctx.rank] = param;
+        ep.shadow[c->ctx.rank] = static_cast<__nv_bfloat16*>(shadow);
+        ep.momentum = momentum;
+        ep.lr = lr;
+        ep.mu = mu;
+        ep.wd = wd;
+        ep.nesterov = nesterov;
+    }
+    Peers sg;
+    memset(&sg, 0, sizeof(sg));
+    for (int r = 0; r < world; ++r) sg.p[r] = staging[r];
+    if (ctas <= 0) ctas = 8;
+    ctas = clamp_ctas(ctas, n4, 1);
+    float* g = grads;
+    const long long cap4 = cap / 4;
+#define DPT_OS_PUSH(W)                                                                          \
+    case W:                                                                                     \
+        allreduce_oneshot_push_kernel<W><<<ctas, kCommThreads, 0, st>>>(c->ctx, g, sg, cap4, n4, ep); \
+        break;
+    switch (world) {
+        DPT_OS_PUSH(2) DPT_OS_PUSH(3) DPT_OS_PUSH(4) DPT_OS_PUSH(5) DPT_OS_PUSH(6) DPT_OS_PUSH(7)
+        DPT_OS_PUSH(8)
+        default: return DPT_ERR_ARG;
+    }
+#undef DPT_OS_PUSH
+    return static_cast<int>(cudaGetLastError());
+}
+
+// Timeline buffer for the step-trace tool: `buf` = device memory of (1 + records) * 32 bytes that
+// the caller zeroed; every collective kernel launched afterwards appends one record (see
+// TraceRec).  NULL switches tracing off.  Kernels already captured in a CUDA graph keep the
+// setting they were captured with.
+extern "C" int dpt_comm_set_trace(dpt_comm* c, void* buf, int records) {
+    if (c == nullptr) return DPT_ERR_ARG;
+    c->ctx.trace = static_cast<unsigned long long*>(buf);
+    c->ctx.trace_cap = buf != nullptr && records > 0 ? static_cast<uint32_t>(records) : 0u;
+    return 0;
+}
+
+// A single-thread kernel that appends a {kind = 255 | tag, time} record to a trace buffer from
+// any stream: marks phase boundaries of the compute streams on the same clock as the collectives.
+__global__ void trace_stamp_kernel(unsigned long long* trace, uint32_t cap, uint32_t tag) {
+    const unsigned long long i = atomicAdd(trace, 1ULL);
+    if (i >= cap) return;
+    unsigned long long* slot = trace + 4 + 4 * i;
+    slot[0] = (255ULL << 56) | tag;
+    slot[1] = dpt::globaltimer_ns();
+    slot[2] = 0;
+    slot[3] = 0;
+}
+extern "C" int dpt_trace_stamp(void* buf, int records, int tag, void* stream) {
+    if (buf == nullptr || records <= 0) return DPT_ERR_ARG;
+    trace_stamp_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<unsigned long long*>(buf), static_cast<uint32_t>(records),
+        static_cast<uint32_t>(tag));
     return static_cast<int>(cudaGetLastError());
 }
 

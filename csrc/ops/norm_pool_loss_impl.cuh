@@ -5,13 +5,10 @@ namespace DPT_NS {
 using namespace dpt;
 
 
-#ifdef DPT_VEC128
 // 8 activations as whole 16-byte registers: every global / shared access of a vector is ONE
-// 128-bit instruction (two for fp32 activations).  With the member-wise definition below nvcc
-// emits four 32-bit LDG / STG per vector for the by-reference reads in unpack8() and for most
-// stores (cuobjdump: 32 LDG.E.CONSTANT + 4 STG.E in bn_bwd_reduce_kernel, no .128 anywhere),
-// i.e. 4x the memory instructions and 4-byte partial-sector stores.  Opt-in at build time
-// (DPT_VEC128=1 python build_native.py) until it has been validated on hardware.
+// 128-bit instruction (two for fp32 activations).  (A member-wise `lowp2 v[4]` definition made
+// nvcc emit four 32-bit LDG / STG per vector — 4x the memory instructions and 4-byte
+// partial-sector stores; measured on B200: ResNet-18 step 0.734 -> 0.687 ms with this layout.)
 struct alignas(16) bf16x8 {
     uint4 q[sizeof(lowp2) / 4];   // 1 x 16 B for 16-bit element types, 2 x 16 B for fp32
 };
@@ -54,26 +51,6 @@ __device__ __forceinline__ bf16x8 pack8(const float (&f)[8]) {
     }
     return b;
 }
-#else
-struct alignas(16) bf16x8 {
-    lowp2 v[4];
-};
-
-__device__ __forceinline__ void unpack8(const bf16x8& b, float (&f)[8]) {
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        float2 t = lp2_to_float2(b.v[i]);
-        f[2 * i] = t.x;
-        f[2 * i + 1] = t.y;
-    }
-}
-__device__ __forceinline__ bf16x8 pack8(const float (&f)[8]) {
-    bf16x8 b;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) b.v[i] = floats_to_lp2(f[2 * i], f[2 * i + 1]);
-    return b;
-}
-#endif
 
 constexpr int kEwThreads = 256;
 
@@ -570,6 +547,11 @@ __device__ __forceinline__ void bulk_stream(const bf16x8* const (&src)[NOPS], lo
         __syncthreads();   // every thread has copied its vectors out: the slot can be refilled
         if (threadIdx.x == 0) {
             const long long next = chunk + static_cast<long long>(STAGES) * step;
+            // Order the generic-proxy reads of this slot (all threads, before the barrier) ahead
+            // of the async-proxy write that refills it.  Without the fence the refill was
+            // observed to overtake the LDS.128 reads on B200 (wrong dx for the first chunks of a
+            // CTA, reproducible on every run): __syncthreads() orders threads, not proxies.
+            fence_proxy_async();
             if (next < nchunks) issue(next, stage);
         }
         if (live) body(idx, v);
@@ -594,21 +576,19 @@ static inline int bulk_grid(long long nvec, int ctas_per_sm) {
     if (g > chunks) g = chunks;
     return static_cast<int>(g < 1 ? 1 : g);
 }
-// The bulk variants pay off once every CTA streams many chunks.  They are OPT-IN
-// (DPT_BULK_EW=1): with them enabled the large-shape BatchNorm test failed intermittently (about
-// one process in three, only on the 5x99x101x256 shape) and the GPU budget of the round ran out
-// before the failing assertion was captured.  The most likely cause, found by inspection
-// afterwards, is not in these kernels: the per-channel REDs of bn_stats_kernel were not fenced,
-// so the PDL-chained forward kernel could read sums that were still in flight (now fenced, see
-// bn_stats_kernel).  Re-enable by default once the large tests have run clean a few times.
-// Measured with them on: ResNet-50 bs256 30.6 ms/step vs ~34 ms without.
-static inline bool bulk_worthwhile(long long nvec) {
+// The bulk variants pay off once every CTA streams many chunks (ResNet-50 bs256: 30.5 vs 32.1
+// ms/step).  DPT_BULK_EW is a debugging bit mask (1 forward, 2 backward reduce, 4 backward apply;
+// 0 = grid-stride kernels everywhere); default all on.
+// History: without the fence.proxy.async in bulk_stream the backward-apply kernel wrote, for its
+// first chunks, the result of the chunk that REFILLS the slot (C = 256 shapes, every run) — the
+// 128-bit shared loads were overtaken by the TMA write of the refill.
+static inline bool bulk_worthwhile(long long nvec, int which = 7) {
     static int on = -1;
     if (on < 0) {
-        const char* e = std::getenv("DPT_BULK_EW");
-        on = (e != nullptr && e[0] == '1') ? 1 : 0;
+        const char* e = std::getenv("DPT_BULK_EW");   // bit mask: 1 forward, 2 backward reduce, 4 backward apply
+        on = (e != nullptr) ? std::atoi(e) : 7;
     }
-    return on && nvec >= 148LL * 2 * kEwThreads * 16;
+    return (on & which) && nvec >= 148LL * 2 * kEwThreads * 16;
 }
 
 // bn_fwd_kernel for large tensors (same arguments and results).
@@ -1300,7 +1280,7 @@ inline int dpt_bn_fwd_train(const void* x, const float* sum, const float* sq, co
     const long long nvec = M * (C / 8);
     const float unbias = M > 1 ? static_cast<float>(M) / static_cast<float>(M - 1) : 1.f;
     ew_pdl_gate();
-    if (bulk_worthwhile(nvec)) {
+    if (bulk_worthwhile(nvec, 1)) {
         static int attr = bulk_smem_attr(bn_fwd_bulk_kernel, 2);
         if (attr != 0) return attr;
         launch_pdl(bn_fwd_bulk_kernel, dim3(bulk_grid(nvec, 3)), dim3(kEwThreads),
@@ -1375,7 +1355,7 @@ inline int dpt_bn_bwd_reduce_ex(const void* dy1, int dy1_is_f32, const void* dy2
     const long long nvec = M * (C / 8);
     auto kern = dy1_is_f32 ? bn_bwd_reduce_kernel<true> : bn_bwd_reduce_kernel<false>;
     ew_pdl_gate();
-    if (!dy1_is_f32 && bulk_worthwhile(nvec)) {
+    if (!dy1_is_f32 && bulk_worthwhile(nvec, 2)) {
         static int attr = bulk_smem_attr(bn_bwd_reduce_bulk_kernel, 4, kBulkStagesReduce);
         if (attr != 0) return attr;
         launch_pdl(bn_bwd_reduce_bulk_kernel, dim3(bulk_grid(nvec, 2)), dim3(kEwThreads),
@@ -1419,7 +1399,7 @@ inline int dpt_bn_bwd_apply(const void* g, const void* x, const float* save_mean
     if (!cvec_ok(C)) return DPT_ERR_SHAPE;
     const long long nvec = M * (C / 8);
     ew_pdl_gate();
-    if (bulk_worthwhile(nvec)) {
+    if (bulk_worthwhile(nvec, 4)) {
         static int attr = bulk_smem_attr(bn_bwd_apply_bulk_kernel, 2);
         if (attr != 0) return attr;
         launch_pdl(bn_bwd_apply_bulk_kernel, dim3(bulk_grid(nvec, 3)), dim3(kEwThreads),

@@ -85,8 +85,12 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
         .def("set_lr", &Reducer::set_lr)
         .def("set_scale_options", &Reducer::set_scale_options)
         .def("set_enabled", &Reducer::set_enabled)
+        .def("set_rank", &Reducer::set_rank)
         .def("set_nvls", &Reducer::set_nvls)
         .def("set_mc_push", &Reducer::set_mc_push)
+        .def("set_oneshot", &Reducer::set_oneshot)
+        .def("set_local_only", &Reducer::set_local_only)
+        .def("bucket_algos", &Reducer::bucket_algos)
         .def("prepare_for_backward", &Reducer::prepare_for_backward)
         .def("mark_ready", &Reducer::mark_ready)
         .def("finalize", &Reducer::finalize)

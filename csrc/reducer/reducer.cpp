@@ -125,11 +125,72 @@ void Reducer::mark_ready(int p, uintptr_t compute_stream) {
     }
 }
 
+int Reducer::algo_for(const BucketSpec& bk) const {
+    const bool fuse = fusion_.enabled && world_ > 1;
+    if (world_ > 1 && os_cap_ > 0 && bk.numel <= os_cap_ && bk.numel * 4 <= os_max_bytes_) return 1;
+    // measured at 8 GPUs: with the SGD update fused, the two-shot kernel (0.855 ms/step) beats the
+    // NVLS one (0.871); without fusion NVLS wins (0.882 vs 0.926) -> NVLS+fusion only on request
+    const bool nvls_fuse_ok =
+        !fuse || (nvls_with_fusion_ && fusion_.param_mc != 0 && fusion_.shadow_mc != 0);
+    if (nvls_mc_ != 0 && nvls_fuse_ok && world_ > 1 && bk.numel * 4 >= nvls_min_bytes_) return 2;
+    if (fuse && mc_push_ && fusion_.param_mc != 0 && fusion_.shadow_mc != 0) return 3;
+    return 0;
+}
+
+std::vector<int> Reducer::bucket_algos() const {
+    std::vector<int> out;
+    for (const auto& bk : buckets_) out.push_back(algo_for(bk));
+    return out;
+}
+
 void Reducer::launch_bucket(int b, cudaStream_t compute) {
     const BucketSpec& bk = buckets_[b];
     DPTR_CUDA(cudaEventRecord(ev_ready_[b], compute));
     DPTR_CUDA(cudaStreamWaitEvent(comm_stream_, ev_ready_[b], 0));
     if (profile_) DPTR_CUDA(cudaEventRecord(ev_start_[b], comm_stream_));
+    const int algo = algo_for(bk);
+    if (local_only_) {
+        // single-rank stand-in (see set_local_only): same math, no peer traffic
+        const int me0 = rank_;
+        void* one[8] = {reinterpret_cast<void*>(grad_ptrs_[me0] + bk.offset * 4)};
+        int rc0 = 0;
+        if (fusion_.enabled) {
+            rc0 = dpt_sgd_flat(reinterpret_cast<float*>(fusion_.param_ptrs[me0] + bk.offset * 4),
+                               reinterpret_cast<const float*>(grad_ptrs_[me0] + bk.offset * 4),
+                               reinterpret_cast<float*>(fusion_.momentum + bk.offset * 4),
+                               reinterpret_cast<void*>(fusion_.shadow_ptrs[me0] + bk.offset * 2),
+                               bk.numel, fusion_.lr, fusion_.mu, 0.f, fusion_.wd, fusion_.nesterov,
+                               nullptr, nullptr, comm_stream_);
+        } else {
+            (void)one;
+        }
+        if (rc0 != 0) throw std::runtime_error("local-only bucket update failed: " + std::to_string(rc0));
+        DPTR_CUDA(cudaEventRecord(ev_done_[b], comm_stream_));
+        ++launches_;
+        return;
+    }
+    if (algo == 1) {
+        const int me = rank_;
+        void* stg[8] = {nullptr};
+        for (int r = 0; r < world_; ++r) stg[r] = reinterpret_cast<void*>(os_staging_[r]);
+        const bool fuse1 = fusion_.enabled;
+        int rc1 = dpt_allreduce_oneshot_push(
+            comm_, reinterpret_cast<float*>(grad_ptrs_[me] + bk.offset * 4), stg, os_cap_, bk.numel,
+            1.0f / static_cast<float>(world_), reinterpret_cast<const float*>(inv_scale_),
+            (check_finite_ && !found_inf_ptrs_.empty())
+                ? reinterpret_cast<float*>(found_inf_ptrs_[me])
+                : nullptr,
+            fuse1 ? reinterpret_cast<float*>(fusion_.param_ptrs[me] + bk.offset * 4) : nullptr,
+            fuse1 ? reinterpret_cast<void*>(fusion_.shadow_ptrs[me] + bk.offset * 2) : nullptr,
+            fuse1 ? reinterpret_cast<float*>(fusion_.momentum + bk.offset * 4) : nullptr, fusion_.lr,
+            fusion_.mu, fusion_.wd, fusion_.nesterov, os_ctas_, comm_stream_);
+        if (rc1 != 0)
+            throw std::runtime_error("dpt_allreduce_oneshot_push failed with code " +
+                                     std::to_string(rc1));
+        DPTR_CUDA(cudaEventRecord(ev_done_[b], comm_stream_));
+        ++launches_;
+        return;
+    }
     void* bufs[8] = {nullptr};
     void* finf[8] = {nullptr};
     void* prm[8] = {nullptr};
@@ -144,11 +205,7 @@ void Reducer::launch_bucket(int b, cudaStream_t compute) {
         }
     }
     const bool fuse = fusion_.enabled && world_ > 1;
-    // measured at 8 GPUs: with the SGD update fused, the two-shot kernel (0.855 ms/step) beats the
-    // NVLS one (0.871); without fusion NVLS wins (0.882 vs 0.926) -> NVLS+fusion only on request
-    const bool nvls_fuse_ok =
-        !fuse || (nvls_with_fusion_ && fusion_.param_mc != 0 && fusion_.shadow_mc != 0);
-    if (nvls_mc_ != 0 && nvls_fuse_ok && world_ > 1 && bk.numel * 4 >= nvls_min_bytes_) {
+    if (algo == 2) {
         const int me = rank_;
         int rc2 = dpt_allreduce_nvls_sgd(
             comm_, reinterpret_cast<void*>(nvls_mc_ + bk.offset * 4), bk.numel,
@@ -165,7 +222,7 @@ void Reducer::launch_bucket(int b, cudaStream_t compute) {
         ++launches_;
         return;
     }
-    if (fuse && mc_push_ && fusion_.param_mc != 0 && fusion_.shadow_mc != 0) {
+    if (algo == 3) {
         int rc3 = dpt_allreduce_fused_mcpush(
             comm_, bufs, bk.numel, 1.0f / static_cast<float>(world_),
             reinterpret_cast<const float*>(inv_scale_),

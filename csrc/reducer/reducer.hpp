@@ -67,6 +67,7 @@ class Reducer {
         check_finite_ = check_finite;
     }
     void set_enabled(bool on) { enabled_ = on; }  // no_sync()
+    void set_rank(int rank) { rank_ = rank; }
     // NVLS: base of this rank's multicast mapping of the gradient arena; buckets of at least
     // `min_bytes` use the multimem kernel (unless the fused-SGD epilogue is active).
     void set_nvls(uintptr_t mc_grad_base, int64_t min_bytes, int rank, bool with_fused_sgd) {
@@ -79,6 +80,24 @@ class Reducer {
     // Fused-SGD two-shot buckets publish through the NVSwitch multicast mappings in the SgdFusion
     // (param_mc / shadow_mc) instead of per-peer stores.  Experimental.
     void set_mc_push(bool on) { mc_push_ = on; }
+
+    // One-shot push all-reduce (dpt_allreduce_oneshot_push) for buckets of at most `max_bytes`:
+    // `staging_ptrs[r]` = rank r's staging area of 2 * world * cap_elems floats.
+    void set_oneshot(std::vector<uintptr_t> staging_ptrs, int64_t cap_elems, int64_t max_bytes,
+                     int rank, int ctas) {
+        os_staging_ = std::move(staging_ptrs);
+        os_cap_ = cap_elems;
+        os_max_bytes_ = max_bytes;
+        rank_ = rank;
+        os_ctas_ = ctas;
+    }
+    // Measurement aid: launch every bucket as if this were the only rank (same gradient scaling
+    // and, with the fused optimizer, a local SGD update of the whole bucket) — the step without
+    // any cross-GPU traffic or waiting, on the same GPU, under the same graph.  The difference to
+    // the real step is the exposed gradient-sync time.
+    void set_local_only(bool on) { local_only_ = on; }
+    // 0 two-shot, 1 one-shot push, 2 NVLS, 3 two-shot + multicast publish (per bucket, as planned)
+    std::vector<int> bucket_algos() const;
 
     void prepare_for_backward(uintptr_t compute_stream);
     void mark_ready(int param_index, uintptr_t compute_stream);
@@ -120,6 +139,11 @@ class Reducer {
     int rank_ = 0;
     bool nvls_with_fusion_ = false;
     bool mc_push_ = false;
+    std::vector<uintptr_t> os_staging_;
+    int64_t os_cap_ = 0, os_max_bytes_ = 0;
+    int os_ctas_ = 0;
+    bool local_only_ = false;
+    int algo_for(const BucketSpec& bk) const;
 };
 
 }  // namespace dptr

@@ -42,6 +42,10 @@ class GradScaler:
         self._inv_scale = None
         self._found_inf = None
         self._state: dict[int, OptState] = {}
+        # set by DistributedDataParallel.bind_scaler: the all-reduce epilogue multiplies every
+        # gradient by inv_scale and raises found_inf, so unscale_() must not do it a second time
+        # (eager steps after a TrainStep bound the scaler, e.g. the partial batch ending an epoch)
+        self.unscaled_by_reducer = False
 
     # ------------------------------------------------------------------ device state
     def _lazy_init(self, device=None) -> None:
@@ -98,7 +102,7 @@ class GradScaler:
             raise RuntimeError("unscale_() has already been called on this optimizer since the last update().")
         if st is OptState.STEPPED:
             raise RuntimeError("unscale_() is being called after step().")
-        if getattr(optimizer, "grads_already_unscaled", False):
+        if getattr(optimizer, "grads_already_unscaled", False) or self.unscaled_by_reducer:
             pass  # the fused all-reduce epilogue applied inv_scale and the inf check
         elif hasattr(optimizer, "flat_grad") and optimizer.flat_grad is not None and self._native():
             from .ops import functional as Fn

@@ -42,7 +42,11 @@ def add_prefix(sd: dict, prefix: str = "module.") -> dict:
 
 def save_checkpoint(path: str, model, optimizer=None, scaler=None, epoch: int = 0,
                     args=None, rank: int = 0) -> None:
-    """Rank 0 writes; other ranks return immediately (all replicas are identical)."""
+    """Rank 0 writes (all replicas are identical).  EVERY rank must call this: with the SGD
+    update fused into the two-shot all-reduce each rank only holds the momentum of the slices
+    it owns, and the shards are gathered collectively before rank 0 serialises the state."""
+    if optimizer is not None and hasattr(model, "gather_optimizer_state"):
+        model.gather_optimizer_state(optimizer)
     if rank != 0:
         return
     payload = {

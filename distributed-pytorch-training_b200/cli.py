@@ -42,14 +42,26 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--resume", default="", type=str,
                    help="checkpoint file to resume from; 'auto' = <output-dir>/checkpoint.pt if it "
                         "exists (for torchrun --max-restarts)")
-    p.add_argument("--bucket-cap-mb", default=25.0, type=float, help="gradient bucket size cap")
+    p.add_argument("--bucket-cap-mb", default=None, type=float,
+                   help="gradient bucket size cap in MiB (default: 4 for the native backend, whose "
+                        "bucket kernels cost microseconds to launch; torch's 25 for nccl / gloo)")
     p.add_argument("--allreduce-algo", default="auto",
                    choices=["auto", "autotune", "oneshot", "twoshot", "nvls", "twoshot_mc"],
                    help="peer-memory all-reduce algorithm for the native backend")
-    p.add_argument("--fused-optimizer", action="store_true",
-                   help="apply the SGD update inside the all-reduce kernel (bf16/FP32 only)")
-    p.add_argument("--cuda-graph", action="store_true",
-                   help="capture the whole training step in a CUDA graph")
+    p.add_argument("--fused-optimizer", dest="fused_optimizer", action="store_true", default=None,
+                   help="apply the SGD update inside the all-reduce kernel (default: on whenever "
+                        "it applies — native backend, SGD with momentum, no dynamic loss scaling)")
+    p.add_argument("--no-fused-optimizer", dest="fused_optimizer", action="store_false")
+    p.add_argument("--cuda-graph", dest="cuda_graph", action="store_true", default=None,
+                   help="capture the whole training step in a CUDA graph (default: on whenever the "
+                        "native step applies — CUDA device, flat-arena optimizer)")
+    p.add_argument("--no-cuda-graph", dest="cuda_graph", action="store_false")
+    p.add_argument("--eval-amp", action="store_true",
+                   help="run validation in the --amp dtype too (the reference validates in "
+                        "FP32/TF32 even with --amp, train_ddp.py:266-300; that is the default)")
+    p.add_argument("--gpu-augment", action="store_true",
+                   help="CIFAR files: crop / flip / normalise on the GPU (one kernel per batch) "
+                        "instead of per sample in the loader workers")
     p.add_argument("--profile-sync", action="store_true",
                    help="record per-step gradient-sync timing (device events, max over ranks)")
     p.add_argument("--metrics-json", default="", type=str, help="write per-epoch metrics as JSON")

@@ -101,7 +101,10 @@ class SyntheticImages(Dataset):
 class CIFAR10Files(Dataset):
     """CIFAR-10 from the standard ``cifar-10-batches-py`` pickles (no torchvision, no download)."""
 
-    def __init__(self, root: str, train: bool, augment: bool, seed: int = 0) -> None:
+    def __init__(self, root: str, train: bool, augment: bool, seed: int = 0, raw: bool = False) -> None:
+        # raw=True: items are the stored uint8 CHW images; crop / flip / normalise then run on
+        # the GPU once per batch (GpuAugment, --gpu-augment) instead of here once per sample
+        self.raw = raw
         base = os.path.join(root, "cifar-10-batches-py")
         names = [f"data_batch_{i}" for i in range(1, 6)] if train else ["test_batch"]
         data, labels = [], []
@@ -125,6 +128,8 @@ class CIFAR10Files(Dataset):
 
     def __getitem__(self, i: int):
         img = self.data[i]
+        if self.raw:
+            return img, self.labels[i]
         if self.augment:
             # RandomCrop(32, padding=4) + RandomHorizontalFlip (train_ddp.py:91-96)
             padded = torch.zeros(3, 40, 40, dtype=torch.uint8)
@@ -139,16 +144,23 @@ class CIFAR10Files(Dataset):
 
 
 def build_datasets(args):
-    if getattr(args, "synthetic", False) or not CIFAR10Files.available(args.data_dir):
-        if not getattr(args, "synthetic", False):
-            print(f"[data] no CIFAR-10 files under {args.data_dir!r}: using synthetic data")
+    if not getattr(args, "synthetic", False) and not CIFAR10Files.available(args.data_dir):
+        # The reference downloads CIFAR-10 on rank 0 (train_ddp.py:103-112).  Without network a
+        # silent switch to random data would fill metrics_rank0.csv with numbers that look real,
+        # so a missing / mistyped --data-dir is an error; synthetic data has to be asked for.
+        raise FileNotFoundError(
+            f"no CIFAR-10 files under {os.path.join(args.data_dir, 'cifar-10-batches-py')!r} "
+            "(this build does not download); point --data-dir at the extracted "
+            "cifar-10-batches-py directory's parent or pass --synthetic")
+    if getattr(args, "synthetic", False):
         size = getattr(args, "synthetic_size", 50000)
         img = getattr(args, "image_size", 32)
         ncls = getattr(args, "num_classes", 10)
         return (SyntheticImages(size, img, ncls, seed=1234),
                 SyntheticImages(max(size // 5, 1), img, ncls, seed=4321))
-    return (CIFAR10Files(args.data_dir, train=True, augment=True),
-            CIFAR10Files(args.data_dir, train=False, augment=False))
+    raw = bool(getattr(args, "gpu_augment", False)) and torch.cuda.is_available()
+    return (CIFAR10Files(args.data_dir, train=True, augment=True, raw=raw),
+            CIFAR10Files(args.data_dir, train=False, augment=False, raw=raw))
 
 
 def get_dataloaders(args, rank: int, world_size: int):
@@ -163,6 +175,10 @@ def get_dataloaders(args, rank: int, world_size: int):
                               drop_last=False)
     val_loader = DataLoader(test_ds, batch_size=args.batch_size, shuffle=False,
                             num_workers=args.workers, pin_memory=pin, drop_last=False)
+    if getattr(train_ds, "raw", False):
+        # uint8 batches: the loops apply these on the device (trainer.py, _device_batch)
+        train_loader.gpu_transform = GpuAugment(seed=getattr(args, "seed", 0) + rank, train=True)
+        val_loader.gpu_transform = GpuAugment(train=False)
     return train_loader, val_loader, sampler
 
 
@@ -170,13 +186,19 @@ class GpuAugment:
     """RandomCrop(32, padding=4) + RandomHorizontalFlip + Normalize on the device for a uint8
     batch (one kernel per batch instead of PIL per sample)."""
 
-    def __init__(self, pad: int = 4, mean=CIFAR_MEAN, std=CIFAR_STD, seed: int = 0) -> None:
-        self.pad, self.mean, self.std = pad, mean, std
+    def __init__(self, pad: int = 4, mean=CIFAR_MEAN, std=CIFAR_STD, seed: int = 0,
+                 train: bool = True) -> None:
+        self.pad, self.mean, self.std, self.train = pad, mean, std, train
         self.gen = torch.Generator().manual_seed(seed)
 
     def __call__(self, images_u8: torch.Tensor) -> torch.Tensor:
         from .ops import functional as Fn
         n = images_u8.shape[0]
+        if not self.train:
+            # test transform (ToTensor + Normalize, train_ddp.py:98-101): centred crop, no flip
+            p = torch.tensor([[self.pad, self.pad, 0]], dtype=torch.int32).repeat(n, 1)
+            return Fn.augment_crop_flip_norm(images_u8, p.to(images_u8.device, non_blocking=True),
+                                             self.mean, self.std, self.pad)
         p = torch.stack([torch.randint(0, 2 * self.pad + 1, (n,), generator=self.gen),
                          torch.randint(0, 2 * self.pad + 1, (n,), generator=self.gen),
                          torch.randint(0, 2, (n,), generator=self.gen)], dim=1).to(torch.int32)

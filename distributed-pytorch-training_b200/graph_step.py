@@ -106,7 +106,7 @@ class TrainStep:
         g0 = self.optimizer.param_groups[0]
         if g0["momentum"] == 0:
             return
-        plans = plan_arena_buckets(self.arena, 4 << 20, 1 << 20)
+        plans = plan_arena_buckets(self.arena, 4 << 20, 1 << 20, 64 << 10)
         index = {id(p): i for i, p in enumerate(self.arena.order)}
         owner = {}
         for b, pl in enumerate(plans):

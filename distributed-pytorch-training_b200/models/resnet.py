@@ -740,13 +740,16 @@ class ResNetEngine:
             torch.cuda.current_stream().wait_event(self._z32_ev)
             self._lib.pdl_skip_next()
             self._z32_pending = False
-        # input gradient on the critical path, weight/bias gradient on the side stream
+        # input gradient on the critical path first (it READS fc.weight: with the optimizer fused
+        # into the all-reduce, reporting fc ready lets a bucket kernel rewrite the weights, so the
+        # side stream is forked only after this kernel is enqueued — same rule as every conv:
+        # dgrad before wgrad); weight / bias gradient on the side stream
+        Fn.head_bwd(dlogits, m.fc.weight, self.pooled, self.feat_shape, None, None, dx=self.d_feat,
+                    part="dx")
         with self._fork_side():
             Fn.head_bwd(dlogits, m.fc.weight, self.pooled, self.feat_shape, self._gw(m.fc.weight),
                         self._gw(m.fc.bias), part="dw")
             self._ready(m.fc.weight, m.fc.bias)
-        Fn.head_bwd(dlogits, m.fc.weight, self.pooled, self.feat_shape, None, None, dx=self.d_feat,
-                    part="dx")
         dy, dy2 = self.d_feat, None
         for b in reversed(self.blocks):
             dy, dy2 = self._bwd_block(b, dy, dy2)

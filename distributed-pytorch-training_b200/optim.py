@@ -200,6 +200,30 @@ class Adam(_FlatOptimizer):
             arena.refresh_shadow()
         return loss
 
+    def load_state_dict(self, state_dict) -> None:
+        """Flat mode: copy the saved moments INTO the flat arenas the kernel updates (the base
+        class would replace state[p][...] with fresh tensors the flat step never reads, silently
+        restarting from zero moments and step 0)."""
+        if not self._flat:
+            return super().load_state_dict(state_dict)
+        m, v, step = self._flat_state()
+        saved_step = None
+        for idx, st in state_dict.get("state", {}).items():
+            p = self._params[int(idx)]
+            s = self.arena.slot(p)
+            if st.get("exp_avg") is not None:
+                m.as_strided(s.shape, s.stride, s.offset).copy_(st["exp_avg"])
+            if st.get("exp_avg_sq") is not None:
+                v.as_strided(s.shape, s.stride, s.offset).copy_(st["exp_avg_sq"])
+            if st.get("step") is not None:
+                saved_step = int(float(st["step"]))
+        if saved_step is not None:
+            step.fill_(saved_step)
+        for g, sg in zip(self.param_groups, state_dict["param_groups"]):
+            for k, val in sg.items():
+                if k != "params":
+                    g[k] = val
+
 
 class AdamW(Adam):
     def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2) -> None:

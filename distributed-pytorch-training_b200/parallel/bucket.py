@@ -74,14 +74,36 @@ def _py_assignment(nbytes, keys, limits):
     return out
 
 
+def split_tail(idx_buckets, nbytes, tail_bucket_bytes):
+    """Peel the last-ready parameters off the final bucket into a bucket of their own (at most
+    ``tail_bucket_bytes``).  The final bucket closes only after the very last weight gradient of
+    backward (the stem), so everything in it is exposed; a tail of a few tens of KB goes through
+    the low-latency one-shot kernel while the rest of the former last bucket is reduced under the
+    stem's backward kernels."""
+    if tail_bucket_bytes <= 0 or not idx_buckets or len(idx_buckets[-1]) < 2:
+        return idx_buckets
+    last = list(idx_buckets[-1])
+    if sum(nbytes[i] for i in last) <= tail_bucket_bytes:
+        return idx_buckets          # the whole last bucket already is a small tail
+    size, cut = 0, len(last)
+    while cut > 1 and size + nbytes[last[cut - 1]] <= tail_bucket_bytes:
+        size += nbytes[last[cut - 1]]
+        cut -= 1
+    if cut == len(last):
+        return idx_buckets
+    return [list(b) for b in idx_buckets[:-1]] + [last[:cut], last[cut:]]
+
+
 def plan_arena_buckets(arena, bucket_cap_bytes=DEFAULT_BUCKET_BYTES_CAP,
-                       first_bucket_bytes=DEFAULT_FIRST_BUCKET_BYTES):
+                       first_bucket_bytes=DEFAULT_FIRST_BUCKET_BYTES, tail_bucket_bytes=0):
     """Buckets over the arena order (= gradient-ready order).  Each bucket is a contiguous,
     16-byte aligned slice ``[offset, offset + numel)`` of the flat gradient arena.
-    Returns a list of dicts {offset, numel, params (indices into arena.order), bytes}."""
+    Returns a list of dicts {offset, numel, params (indices into arena.order), bytes}.
+    ``tail_bucket_bytes`` > 0 additionally splits a small last bucket off (see split_tail)."""
     params = arena.order
     idx_buckets, _ = compute_bucket_assignment_by_size(
         [p for p in params], [first_bucket_bytes, bucket_cap_bytes])
+    idx_buckets = split_tail(idx_buckets, [p.numel() * 4 for p in params], tail_bucket_bytes)
     plans = []
     for b in idx_buckets:
         first, last = params[b[0]], params[b[-1]]

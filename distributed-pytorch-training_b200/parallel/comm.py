@@ -267,11 +267,15 @@ class Communicator:
         return mine
 
     # ------------------------------------------------------------------ watchdog / heartbeat
-    def start_watchdog(self, interval_s: float = 1.0, abort: bool = False, heartbeat: bool = True):
+    def start_watchdog(self, interval_s: float = 1.0, abort: bool = False, heartbeat: bool = True,
+                       stale_s: float = 15.0):
         """Host thread that (a) polls the device-written error word, so a peer that died or
         stalled is reported with (rank, peer, epoch) instead of hanging the job — the stand-in
-        for ProcessGroupNCCL's watchdog / heartbeat monitor (ProcessGroupNCCL.hpp:610,690) — and
-        (b) publishes a per-rank heartbeat key in the torch store."""
+        for ProcessGroupNCCL's watchdog / heartbeat monitor (ProcessGroupNCCL.hpp:610,690) —
+        (b) publishes a per-rank heartbeat key in the torch store and (c) reports a peer whose
+        heartbeat is older than ``stale_s`` (its process is gone or wedged), usually before the
+        device-side wait times out.  ``abort=True`` ends the process with exit code 70 after the
+        report (what TORCH_NCCL_ASYNC_ERROR_HANDLING=1 does under the reference)."""
         import os
         import sys
         import threading
@@ -286,23 +290,45 @@ class Communicator:
                 store = dist.distributed_c10d._get_default_store()
             except Exception:  # noqa: BLE001
                 store = None
+        self._wd_store = store
+        self._wd_t0 = time.time()
+
+        def report(msg, fault):
+            self.fault = fault
+            sys.stderr.write(f"[dpt_b200 watchdog] rank {self.rank}: {msg}\n")
+            sys.stderr.flush()
+            if abort:
+                os._exit(70)
 
         def run():
+            tick = 0
             while not self._wd_stop.wait(interval_s):
+                tick += 1
                 try:
-                    if store is not None:
-                        store.set(f"dpt_b200/heartbeat/{self.rank}", str(time.time()))
                     code = int(self.lib.dpt_comm_error(self.handle)) if self.handle else 0
                 except Exception:  # noqa: BLE001
                     return
                 if code:
                     peer = (code >> 24) & 0x7F
-                    self.fault = (self.rank, peer, code & 0xFFFFFF)
-                    sys.stderr.write(f"[dpt_b200 watchdog] rank {self.rank}: collective timed out "
-                                     f"waiting for rank {peer} (epoch {code & 0xFFFFFF})\n")
-                    sys.stderr.flush()
-                    if abort:
-                        os._exit(70)
+                    report(f"collective timed out waiting for rank {peer} (epoch {code & 0xFFFFFF})",
+                           (self.rank, peer, code & 0xFFFFFF))
+                    return
+                if store is None:
+                    continue
+                try:
+                    store.set(f"dpt_b200/heartbeat/{self.rank}", str(time.time()))
+                    if tick % 3 == 0:
+                        ages = self.peer_heartbeats()
+                        late = [r for r, a in ages.items() if r != self.rank and a > stale_s]
+                        if late and not self._wd_stop.is_set():
+                            report(f"no heartbeat from rank(s) {late} for more than {stale_s:.0f} s "
+                                   "(process gone or wedged)", (self.rank, late[0], -1))
+                            return
+                except Exception as e:  # noqa: BLE001 - the store lives in rank 0's process
+                    if self._wd_stop.is_set():
+                        return
+                    report(f"rendezvous store unreachable ({type(e).__name__}): rank 0 is gone",
+                           (self.rank, 0, -1))
                     return
 
         self._wd_thread = threading.Thread(target=run, name="dpt-watchdog", daemon=True)
@@ -318,10 +344,12 @@ class Communicator:
             return out
         now = time.time()
         for r in range(self.world):
-            try:
-                out[r] = now - float(store.get(f"dpt_b200/heartbeat/{r}").decode())
-            except Exception:  # noqa: BLE001
-                out[r] = float("inf")
+            key = f"dpt_b200/heartbeat/{r}"
+            if not store.check([key]):      # get() would block on a key that is not there yet
+                out[r] = now - getattr(self, "_wd_t0", now)
+                continue
+            raw = store.get(key).decode()
+            out[r] = 0.0 if raw == "done" else now - float(raw)
         return out
 
     def stop_watchdog(self) -> None:
@@ -329,6 +357,12 @@ class Communicator:
             self._wd_stop.set()
             self._wd_thread.join(timeout=2.0)
             self._wd_thread = None
+            st = getattr(self, "_wd_store", None)
+            if st is not None:
+                try:   # a rank that finished cleanly is not a dead rank
+                    st.set(f"dpt_b200/heartbeat/{self.rank}", "done")
+                except Exception:  # noqa: BLE001
+                    pass
 
     def close(self) -> None:
         self.stop_watchdog()

@@ -151,7 +151,9 @@ class DistributedDataParallel(nn.Module):
                  gradient_as_bucket_view=True, static_graph=True, *, backend: str = "native",
                  comm=None, fused_optimizer=False, profile=False, comm_ctas: int = 0,
                  comm_timeout: float = 30.0, first_bucket_mb: float = 1.0,
-                 allreduce_algo: str = "auto", nvls_min_bytes: int = 1 << 20):
+                 allreduce_algo: str = "auto", nvls_min_bytes: int = 1 << 20,
+                 tail_bucket_kb: float | None = None, oneshot_max_kb: float | None = None,
+                 watchdog: bool = True):
         super().__init__()
         self.module = module
         self.device_ids = device_ids
@@ -187,6 +189,18 @@ class DistributedDataParallel(nn.Module):
         default_cap = 4 if backend == "native" else 25
         self.bucket_bytes_cap = int((bucket_cap_mb if bucket_cap_mb is not None else default_cap) * 1024 * 1024)
         self.first_bucket_bytes = int(first_bucket_mb * 1024 * 1024)
+        # the last-ready gradients (the stem) form a bucket of their own, small enough for the
+        # one-barrier one-shot kernel: only that kernel trails the last backward kernel
+        if tail_bucket_kb is None:
+            tail_bucket_kb = 64.0 if backend == "native" else 0.0
+        self.tail_bucket_bytes = int(tail_bucket_kb * 1024)
+        if oneshot_max_kb is None:
+            oneshot_max_kb = 256.0
+        if allreduce_algo == "oneshot":
+            oneshot_max_kb = 1 << 30       # every bucket that fits the staging area
+        elif allreduce_algo in ("twoshot", "nvls", "twoshot_mc"):
+            oneshot_max_kb = 0.0           # explicit algorithm: no size-based switch
+        self.oneshot_max_bytes = int(oneshot_max_kb * 1024)
         self.profile = profile
         self.fused_optimizer = fused_optimizer
         self._fusion_cfg = None
@@ -215,7 +229,8 @@ class DistributedDataParallel(nn.Module):
         if init_sync:
             self._sync_module_states()
         # ---- reducer --------------------------------------------------------------------
-        self.plans = plan_arena_buckets(self.arena, self.bucket_bytes_cap, self.first_bucket_bytes)
+        self.plans = plan_arena_buckets(self.arena, self.bucket_bytes_cap, self.first_bucket_bytes,
+                                        self.tail_bucket_bytes)
         self._param_index = {id(p): i for i, p in enumerate(self.arena.order)}
         self._cb_queued = False
         if backend == "native":
@@ -229,6 +244,8 @@ class DistributedDataParallel(nn.Module):
             self.reducer = E.Reducer(specs, len(self.arena.order), self.comm.handle.value or 0,
                                      self.world_size, list(self.arena.grad_buf.peer_ptrs), found, 0,
                                      comm_ctas, bool(profile))
+            self.reducer.set_rank(self.rank)
+            self._setup_oneshot(comm_ctas)
             self.autotune_result = None
             if allreduce_algo == "autotune" and self.world_size > 1:
                 # pick the NVLS / two-shot crossover from bus bandwidth measured right now
@@ -251,6 +268,28 @@ class DistributedDataParallel(nn.Module):
                 if self.world_size > 1 else None
         if hasattr(module, "_grad_sink"):
             module._grad_sink = self._sink
+        # live failure detection for the whole job (the role ProcessGroupNCCL's watchdog thread
+        # plays under the reference's DDP, ProcessGroupNCCL.hpp:690): polls the device-written
+        # error word and the peers' heartbeats, reports (rank, peer, epoch) and ends the process
+        if watchdog and backend == "native" and self.world_size > 1 and self.comm is not None:
+            import os
+            self.comm.start_watchdog(abort=os.environ.get("DPT_WATCHDOG_ABORT", "1") != "0")
+
+    def _setup_oneshot(self, comm_ctas: int) -> None:
+        """Staging area + reducer switch for the one-shot push kernel (buckets up to
+        ``oneshot_max_bytes``; the staging area holds 2 x world slots of the largest such bucket)."""
+        self.oneshot_buf = None
+        if self.world_size < 2 or self.oneshot_max_bytes <= 0:
+            return
+        fit = [pl["numel"] for pl in self.plans if pl["numel"] * 4 <= self.oneshot_max_bytes]
+        if not fit:
+            return
+        cap = (max(fit) + 3) // 4 * 4
+        if 2 * self.world_size * cap * 4 > (1 << 30):     # keep the staging area below 1 GiB
+            cap = ((1 << 30) // (8 * self.world_size)) // 4 * 4
+        self.oneshot_buf = self.comm.alloc(2 * self.world_size * cap * 4)
+        self.reducer.set_oneshot(list(self.oneshot_buf.peer_ptrs), cap, self.oneshot_max_bytes,
+                                 self.rank, min(comm_ctas, 8) if comm_ctas > 0 else 8)
 
     # ------------------------------------------------------------------ construction helpers
     def _verify_params_across_processes(self, params) -> None:
@@ -348,6 +387,41 @@ class DistributedDataParallel(nn.Module):
         self._fusion_cfg = f
         return True
 
+    def momentum_shards(self) -> list[tuple[int, int, int]]:
+        """(first element, one-past-last element, owner rank) of every momentum shard: with the
+        fused two-shot / NVLS kernels rank r updates momentum only for slice r of each bucket
+        (csrc/comm/p2p_collectives.cu: per = ceil(n4 / world) float4 per rank); one-shot buckets
+        are updated in full on every rank and do not appear here."""
+        out = []
+        if self._fusion_cfg is None or self.world_size == 1:
+            return out
+        algos = self.reducer.bucket_algos()
+        for pl, algo in zip(self.plans, algos):
+            if algo == 1:
+                continue
+            n4 = pl["numel"] // 4
+            per = (n4 + self.world_size - 1) // self.world_size
+            for r in range(self.world_size):
+                lo, hi = min(n4, per * r), min(n4, per * (r + 1))
+                if hi > lo:
+                    out.append((pl["offset"] + 4 * lo, pl["offset"] + 4 * hi, r))
+        return out
+
+    def gather_optimizer_state(self, optimizer) -> None:
+        """Collective (all ranks): make every rank's flat momentum complete.  Cold path (before a
+        checkpoint): foreign shards are zeroed and one SUM all-reduce over the bootstrap process
+        group fills them with their owners' values (x + 0 + ... + 0 is exact)."""
+        shards = self.momentum_shards()
+        if not shards or not hasattr(optimizer, "_flat_momentum"):
+            return
+        m = optimizer._flat_momentum()
+        torch.cuda.current_stream().synchronize()
+        for lo, hi, owner in shards:
+            if owner != self.rank:
+                m[lo:hi].zero_()
+        dist.all_reduce(m, group=self.process_group)
+        torch.cuda.current_stream().synchronize()
+
     def bind_scaler(self, scaler) -> None:
         """Fuse AMP unscale + non-finite check into the all-reduce epilogue."""
         if scaler is None or not scaler.is_enabled():
@@ -356,6 +430,7 @@ class DistributedDataParallel(nn.Module):
             scaler.bind_found_inf(self.comm.found_inf)
             self.reducer.set_scale_options(scaler.inv_scale.data_ptr(), True)
             self._scaler_fused = True
+            scaler.unscaled_by_reducer = self.world_size > 1
 
     # ------------------------------------------------------------------ gradient path
     def _stream(self) -> int:
@@ -523,6 +598,13 @@ class DistributedDataParallel(nn.Module):
     def bucket_sizes(self):
         return [pl["bytes"] for pl in self.plans]
 
+    def bucket_algorithms(self) -> list[str]:
+        """Kernel chosen for every bucket (in launch order)."""
+        if self.backend != "native" or self.reducer is None:
+            return []
+        names = {0: "twoshot", 1: "oneshot", 2: "nvls", 3: "twoshot_mc"}
+        return [names[a] for a in self.reducer.bucket_algos()]
+
     def _get_ddp_logging_data(self) -> dict:
         """Static + runtime statistics under the key names torch's DDP Logger uses
         (logger.hpp:42-138)."""
@@ -531,8 +613,8 @@ class DistributedDataParallel(nn.Module):
             "world_size": self.world_size,
             "rank": self.rank,
             "backend_name": self.backend,
-            "allreduce_algo": ("nvls+twoshot" if getattr(self, "nvls", False) else "twoshot")
-            if self.backend == "native" else "torch.distributed",
+            "allreduce_algo": self.bucket_algorithms() if self.backend == "native"
+            else "torch.distributed",
             "num_parameter_tensors": len(order),
             "total_parameter_size_bytes": sum(p.numel() * 4 for p in order),
             "bucket_cap_bytes": self.bucket_bytes_cap,

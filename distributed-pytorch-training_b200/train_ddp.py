@@ -40,24 +40,29 @@ def main(argv=None):
     train_loader, val_loader, train_sampler = get_dataloaders(args, rank, world_size)
 
     model = build_model(device, args.arch, args.num_classes)
+    fp16 = args.amp and args.amp_dtype == "fp16"
+    # ---- resolve the "auto" switches: the benchmarked fast path (whole step in one CUDA graph,
+    # SGD update inside the all-reduce kernels) is what runs unless it cannot or is turned off
+    native_ok = device.type == "cuda" and args.backend == "native"
+    if args.cuda_graph is None:
+        args.cuda_graph = native_ok and not args.profile_sync
+    if args.fused_optimizer is None:
+        args.fused_optimizer = native_ok and args.optimizer == "sgd" and not fp16 \
+            and args.momentum != 0
     # per-bucket event timing cannot be recorded inside a captured CUDA graph: with --cuda-graph
     # the profiler only reports the (event-timed) step time
     bucket_profile = args.profile_sync and not args.cuda_graph
     if args.profile_sync and args.cuda_graph and rank == 0:
-        print("[grad-sync] --cuda-graph: per-bucket timing disabled (run without --cuda-graph "
+        print("[grad-sync] --cuda-graph: per-bucket timing disabled (run with --no-cuda-graph "
               "to profile gradient sync)")
-    algo = {"auto": "auto", "autotune": "autotune", "oneshot": "twoshot", "twoshot": "twoshot",
-            "nvls": "nvls", "twoshot_mc": "twoshot_mc"}[args.allreduce_algo]
     model = maybe_wrap_ddp(model, device, local_rank, backend=args.backend,
-                           bucket_cap_mb=args.bucket_cap_mb if args.bucket_cap_mb != 25.0 else None,
-                           profile=bucket_profile, comm_timeout=args.comm_timeout,
-                           allreduce_algo=algo)
+                           bucket_cap_mb=args.bucket_cap_mb, profile=bucket_profile,
+                           comm_timeout=args.comm_timeout, allreduce_algo=args.allreduce_algo)
     ddp = model if isinstance(model, DistributedDataParallel) else None
 
     criterion = CrossEntropyLoss().to(device)
     optimizer = build_optimizer(args.optimizer, model.parameters(), args.lr, args.momentum,
                                 args.weight_decay)
-    fp16 = args.amp and args.amp_dtype == "fp16"
     scaler = GradScaler(device=device, enabled=fp16 and device.type == "cuda")
     if ddp is not None and args.fused_optimizer and not scaler.is_enabled() and args.optimizer == "sgd":
         ddp.enable_fused_sgd(optimizer)
@@ -75,8 +80,7 @@ def main(argv=None):
             print(f"Resumed from {args.resume} at epoch {start_epoch}")
 
     train_step = None
-    native_ok = device.type == "cuda"
-    if args.cuda_graph and native_ok and getattr(optimizer, "_flat", False):
+    if args.cuda_graph and device.type == "cuda" and getattr(optimizer, "_flat", False):
         from .graph_step import TrainStep
         shape = (args.batch_size, 3, args.image_size, args.image_size)
         step_dtype = torch.float32 if not args.amp else (torch.float16 if fp16 else torch.bfloat16)

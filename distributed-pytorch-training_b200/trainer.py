@@ -38,6 +38,15 @@ def _autocast(args, device):
     return contextlib.nullcontext()
 
 
+def _device_batch(loader, images, device):
+    """--gpu-augment: uint8 batches are cropped / flipped / normalised by one kernel on the GPU
+    (reference: torchvision transforms per sample in 4 worker processes, train_ddp.py:91-101)."""
+    tf = getattr(loader, "gpu_transform", None)
+    if tf is None or images.dtype != torch.uint8:
+        return images
+    return tf(images.to(device, non_blocking=True))
+
+
 def _epoch_reduce(loss_sum: float, correct: float, total: float, device, rank: int):
     packed = torch.tensor([loss_sum, correct, total], device=device, dtype=torch.float64)
     reduce_tensor(packed)
@@ -72,6 +81,7 @@ def train_one_epoch(epoch, model, train_loader, optimizer, criterion, device, ar
             break
         batch_start = time.time()
         bsz = images.size(0)
+        images = _device_batch(train_loader, images, device)
         if cuda:
             ev_s = torch.cuda.Event(enable_timing=True)
             ev_e = torch.cuda.Event(enable_timing=True)
@@ -148,12 +158,13 @@ def train_one_epoch(epoch, model, train_loader, optimizer, criterion, device, ar
 
 @torch.no_grad()
 def validate(model, val_loader, criterion, device, rank, world_size, args=None):
-    """Full validation set on every rank (reference train_ddp.py:266-300).  The reference never
-    autocasts here; with ``--amp --amp-dtype bf16`` on CUDA this framework keeps the native bf16
-    inference kernels (BN folded to scale/shift) instead — a documented deviation."""
+    """Full validation set on every rank, never autocast — FP32 storage, TF32 tensor-core
+    convolutions — even under ``--amp``, exactly as the reference (train_ddp.py:266-300; cuDNN's
+    allow_tf32 default).  ``--eval-amp`` opts into the 16-bit inference kernels instead."""
     model.eval()
     acc = torch.zeros(3, device=device, dtype=torch.float64)
-    native_eval = args is not None and getattr(args, "amp", False) and device.type == "cuda"
+    native_eval = args is not None and getattr(args, "amp", False) and device.type == "cuda" \
+        and getattr(args, "eval_amp", False)
     import contextlib
     edt = torch.float16 if (args is not None and getattr(args, "amp_dtype", "bf16") == "fp16") else torch.bfloat16
     ctx = torch.autocast("cuda", dtype=edt) if native_eval else contextlib.nullcontext()
@@ -161,7 +172,7 @@ def validate(model, val_loader, criterion, device, rank, world_size, args=None):
     for i, (images, targets) in enumerate(val_loader):
         if max_steps and i >= max_steps:
             break
-        images = images.to(device, non_blocking=True)
+        images = _device_batch(val_loader, images, device).to(device, non_blocking=True)
         targets = targets.to(device, non_blocking=True)
         with ctx:
             outputs = model(images)

@@ -152,8 +152,9 @@ int dpt_pdl_skip_next(void);
 
 /* ---- NVLink peer-memory collectives (csrc/comm/p2p_collectives.cu) ---------------------------
  * Stand in for ProcessGroupNCCL allreduce / broadcast / barrier as driven by torch DDP on the
- * reference path (train_ddp.py:65, 112, 166, 305-310).  dpt_symm_alloc is the only call in this
- * header that allocates device memory (cudaMalloc + IPC export). */
+ * reference path (train_ddp.py:65, 112, 166, 305-310).  dpt_symm_alloc (cudaMalloc + IPC export)
+ * and dpt_comm_create (512 bytes of device counters + one pinned host word) are the only calls
+ * in this header that allocate memory. */
 typedef struct dpt_comm dpt_comm;
 int dpt_symm_alloc(size_t bytes, void** ptr, void* ipc_handle_64);
 int dpt_symm_open(const void* ipc_handle_64, void** ptr);
@@ -179,6 +180,25 @@ int dpt_allreduce_fused_mcpush(dpt_comm* c, void* const* bufs, long long n, floa
                                float lr, float mu, float wd, int nesterov, int ctas, void* stream);
 int dpt_allreduce_oneshot(dpt_comm* c, void* const* in, float* out, long long n, float scale,
                           const float* inv_scale, void* const* found_inf, int ctas, void* stream);
+/* One-shot "push" all-reduce for small buckets (the exposed tail of backward): every rank stores
+ * its n floats into slot [rank] of every peer's staging area (`staging[r]` = rank r's area of
+ * 2 * world * cap floats in symmetric memory, double buffered), one cross-GPU barrier, then every
+ * rank reduces from its own memory and applies the epilogue to its own copy.  found_inf / param /
+ * shadow are this rank's LOCAL pointers (the SGD update is replicated, so momentum is complete on
+ * every rank); param == NULL leaves the averaged gradient in `grads`.  Returns DPT_ERR_TOO_LARGE
+ * when n > cap.  Stands in for NCCL's low-latency small-message all-reduce under torch DDP
+ * (train_ddp.py:305-310) + GradScaler.unscale_ (:208) + optimizer.step (:214). */
+int dpt_allreduce_oneshot_push(dpt_comm* c, float* grads, void* const* staging, long long cap,
+                               long long n, float scale, const float* inv_scale, float* found_inf,
+                               float* param, void* shadow, float* momentum, float lr, float mu,
+                               float wd, int nesterov, int ctas, void* stream);
+/* Step timeline (benchmarks/step_trace.py; the role DDP's Logger/Timer plays in the reference's
+ * stack, torch reducer_timer.hpp:26-32, but on the device clock and valid under CUDA-graph
+ * replay): `buf` = caller-zeroed device memory of (1 + records) * 32 bytes.  After
+ * dpt_comm_set_trace every collective kernel appends {kind<<56 | bytes, t_start, t_after_first_
+ * barrier, t_end} (globaltimer ns); dpt_trace_stamp appends {255<<56 | tag, t} from any stream. */
+int dpt_comm_set_trace(dpt_comm* c, void* buf, int records);
+int dpt_trace_stamp(void* buf, int records, int tag, void* stream);
 /* NVLS (NVSwitch multicast) variant: multimem.ld_reduce + multimem.st through `mc`, this rank's
  * mapping of the multicast object bound to every rank's buffer (parallel/nvls.py sets it up). */
 int dpt_allreduce_nvls(dpt_comm* c, void* mc, long long n, float scale, const float* inv_scale,

@@ -19,12 +19,9 @@ def test_engine_matches_torch_fp32(arch, bs, img, ncls):
     _engine_matches_torch_fp32(arch, bs, img, ncls)
 
 
-@pytest.mark.skipif(__import__("os").environ.get("DPT_TEST_LARGE", "0") != "1",
-                    reason="ImageNet-sized engine parity is opt-in (DPT_TEST_LARGE=1, ~3 GB)")
 def test_engine_matches_torch_fp32_imagenet_size():
     """ResNet-50 at 224x224, batch 32: layer1 has 784 row tiles, so the convolutions take the
-    persistent kernels and the BatchNorm kernels their long-tensor grids (or, with
-    DPT_BULK_EW=1, the bulk-copy variants)."""
+    persistent kernels and the BatchNorm kernels their bulk-copy variants."""
     _engine_matches_torch_fp32("resnet50", 32, 224, 1000)
 
 

@@ -28,11 +28,9 @@ def test_bn_train_fwd_bwd(shape, relu, res):
     _bn_train_fwd_bwd(shape, relu, res)
 
 
-# ResNet-50-sized tensors (>= 1.2M 8-channel vectors: large enough for the opt-in bulk-copy
-# streaming kernels, DPT_BULK_EW=1; the second shape ends in a partial 256-vector chunk).
-# Opt-in (DPT_TEST_LARGE=1): see the note at bulk_worthwhile() in norm_pool_loss_impl.cuh.
-@pytest.mark.skipif(__import__("os").environ.get("DPT_TEST_LARGE", "0") != "1",
-                    reason="large-shape BatchNorm cases are opt-in (DPT_TEST_LARGE=1)")
+# ResNet-50-sized tensors (>= 1.2M 8-channel vectors: large enough for the bulk-copy streaming
+# kernels; the second shape ends in a partial 256-vector chunk and has C = 256, the case that
+# exposed the missing proxy fence in bulk_stream).
 @pytest.mark.parametrize("shape", [(16, 112, 112, 64), (5, 99, 101, 256)])
 @pytest.mark.parametrize("relu,res", [(False, False), (True, False), (True, True)])
 def test_bn_train_fwd_bwd_large(shape, relu, res):
