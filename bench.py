@@ -50,12 +50,19 @@ def parse():
                    help="apply SGD inside the all-reduce kernel (default: on when N > 1)")
     p.add_argument("--no-fused-optimizer", dest="fused_optimizer", action="store_false")
     p.add_argument("--bucket-cap-mb", type=float, default=None)
-    p.add_argument("--allreduce-algo", default="auto", choices=["auto", "twoshot", "nvls", "twoshot_mc"])
+    p.add_argument("--allreduce-algo", default="auto",
+                   choices=["auto", "oneshot", "twoshot", "nvls", "twoshot_mc", "autotune"])
     p.add_argument("--comm-ctas", type=int, default=16,
                    help="CTAs of each bucket all-reduce kernel (fewer = less SM contention with backward)")
     p.add_argument("--eager-buffer-sync", action="store_true",
                    help="broadcast BN buffers from rank 0 every step (torch DDP behaviour) instead "
                         "of lazily before eval/checkpoint")
+    p.add_argument("--no-extras", action="store_true",
+                   help="skip the cold-path evidence after the timed regions (multi-GPU reduction "
+                        "checks, fp16 + GradScaler arm, loss parity vs torchvision + torch DDP)")
+    p.add_argument("--tail-kb", type=float, default=None, help="tail bucket size (KiB; 0 = off)")
+    p.add_argument("--oneshot-max-kb", type=float, default=None,
+                   help="buckets up to this size use the one-shot push kernel")
     p.add_argument("--profile-sync", action="store_true",
                    help="extra eager pass with per-bucket event timing (reported under grad_sync)")
     return p.parse_args()
@@ -165,7 +172,9 @@ def run_ours(a):
     if world > 1:
         model = ddp = DistributedDataParallel(model, device_ids=[local], backend="native",
                                               bucket_cap_mb=a.bucket_cap_mb, comm_ctas=a.comm_ctas,
-                                              allreduce_algo=a.allreduce_algo)
+                                              allreduce_algo=a.allreduce_algo,
+                                              tail_bucket_kb=a.tail_kb,
+                                              oneshot_max_kb=a.oneshot_max_kb)
     opt = SGD(model.parameters(), lr=0.1, momentum=0.9, weight_decay=5e-4)
     if a.fused_optimizer is None:
         a.fused_optimizer = world > 1 and a.amp_dtype != "fp16"
@@ -258,9 +267,13 @@ def run_ours(a):
                    "l2": "flushed between timed steps (untimed 256 MiB memset)" if flush is not None
                          else "not flushed: one step touches ~207 MB (fp32 params+grads+momentum, bf16 shadow, "
                               "activations) > 126 MB L2",
-                   "grad_allreduce": (f"native NVLink peer-memory two-shot, {a.comm_ctas} CTAs/bucket, fused "
-                                      "1/world" + (" + SGD update" if a.fused_optimizer else "") + " epilogue")
+                   "grad_allreduce": (f"native NVLink peer-memory kernels (per bucket: see bucket_algorithms), "
+                                      f"{a.comm_ctas} CTAs/bucket, fused 1/world"
+                                      + (" + SGD update" if a.fused_optimizer else "") + " epilogue")
                                      if world > 1 else "none (1 GPU)",
+                   "timed_inputs": "device-timed `value`: K graph replays on one resident batch (inputs "
+                                   "already on the device); `e2e`: 8 distinct pinned host batches, H2D + "
+                                   "loss D2H every step",
                    "fused_optimizer": bool(a.fused_optimizer and world > 1),
                    "nvls": bool(getattr(ddp, "nvls", False)) if ddp is not None else False,
                    "grad_buckets_bytes": ddp.bucket_sizes() if ddp is not None else [],
@@ -278,11 +291,174 @@ def run_ours(a):
     }
     if sync:
         res["grad_sync"] = sync
+    # ---- evidence beside the number (all cold path, after the timed regions) ------------------
+    def attempt(name, fn):
+        try:
+            res[name] = fn()
+        except Exception as e:  # noqa: BLE001 - never lose the bench line to an extra
+            res[name] = {"error": f"{type(e).__name__}: {e}"[:300]}
+
+    if ddp is not None:
+        res["config"]["bucket_algorithms"] = ddp.bucket_algorithms()
+        if not a.no_extras:
+            attempt("multi_gpu_checks", lambda: multi_gpu_checks(ddp, device))
+        ddp.shutdown()
+    del step
+    if not a.no_extras and a.amp_dtype == "bf16":
+        attempt("fp16_gradscaler", lambda: fp16_scaler_arm(a, device, rank, world, local))
+    if not a.no_extras and a.arch in ("resnet18", "resnet34", "resnet50"):
+        attempt("loss_parity", lambda: loss_parity(a, device, rank, world, local))
     if rank == 0:
         print(json.dumps(res))
-    if ddp is not None:
-        ddp.shutdown()
     cleanup_distributed()
+
+
+# ------------------------------------------------------------------------ correctness evidence
+def multi_gpu_checks(ddp, device) -> dict:
+    """Cold-path proof, printed with the bench line, that the native gradient path reduces
+    CORRECTLY (the scaling run is the only multi-GPU run the driver does): replicas bit-identical,
+    every rank issued the same collectives, and a real bucket all-reduced by each native kernel
+    equals torch.distributed's NCCL all-reduce of the same data."""
+    import torch
+    import torch.distributed as dist
+    out = {}
+    out["replicas_bit_identical"] = bool(ddp.verify_replicas(raise_on_mismatch=False))
+    try:
+        ep = ddp.comm.validate_epochs()
+        out["collective_epochs_agree"] = True
+        out["collectives_issued_per_cta0"] = int(ep[0])
+    except RuntimeError as e:
+        out["collective_epochs_agree"] = False
+        out["epoch_error"] = str(e)[:200]
+    world = ddp.world_size
+    errs = {}
+    # the largest bucket through the two-shot kernel (and NVLS when bound), the tail bucket
+    # through the one-shot push kernel
+    big = max(ddp.plans, key=lambda pl: pl["numel"])
+    small = ddp.plans[-1]
+    gen = torch.Generator(device=device).manual_seed(4242 + ddp.rank)
+    for name, pl in (("twoshot", big), ("nvls", big), ("oneshot", small)):
+        n = pl["numel"]
+        view = ddp.arena.grad[pl["offset"]: pl["offset"] + n]
+        x = torch.randn(n, device=device, generator=gen)
+        ref = x.clone()
+        dist.all_reduce(ref)
+        ref /= world
+        view.copy_(x)
+        torch.cuda.synchronize()
+        dist.barrier()
+        if name == "twoshot":
+            ddp.comm.allreduce_(ddp.arena.grad_buf, pl["offset"] * 4, n)
+        elif name == "nvls":
+            if not hasattr(ddp.arena.grad_buf, "mc_ptr"):
+                continue
+            ddp.comm.allreduce_nvls_(ddp.arena.grad_buf, pl["offset"] * 4, n)
+        else:
+            if getattr(ddp, "oneshot_buf", None) is None or n * 4 > ddp.oneshot_max_bytes:
+                continue
+            ddp.comm.allreduce_oneshot_push_(view, ddp.oneshot_buf, ddp.oneshot_cap)
+        torch.cuda.synchronize()
+        err = torch.tensor([(view - ref).abs().max().item()], device=device, dtype=torch.float64)
+        dist.all_reduce(err, op=dist.ReduceOp.MAX)
+        errs[name] = {"bytes": n * 4, "max_abs_err_vs_nccl": float(err.item())}
+        view.zero_()
+    out["allreduce_vs_nccl"] = errs
+    ddp.comm.check_health()
+    return out
+
+
+def loss_parity(a, device, rank, world, local, steps=8) -> dict:
+    """N-step loss parity on the SAME weights and the SAME batches: this
+    framework's native model under its native DDP vs torchvision's model with the identical
+    initial state_dict under torch DDP + NCCL, torch.autocast(bf16) and torch.optim.SGD — the
+    stack the reference drives (train_ddp.py:154, 204-214, 305-310), lr 0.01."""
+    import torch
+    import torch.nn.functional as F
+    import torchvision
+    from dpt_b200.graph_step import TrainStep
+    from dpt_b200.models.resnet import build_model
+    from dpt_b200.optim import SGD
+    from dpt_b200.parallel.ddp import DistributedDataParallel
+    torch.manual_seed(777)                      # same init on every rank and for both arms
+    ours = build_model(device, a.arch, a.num_classes)
+    init = {k: v.detach().clone() for k, v in ours.state_dict().items()}
+    ddp = None
+    if world > 1:
+        ours = ddp = DistributedDataParallel(ours, device_ids=[local], backend="native")
+    opt = SGD(ours.parameters(), lr=0.01, momentum=0.9, weight_decay=5e-4)
+    if ddp is not None:
+        ddp.enable_fused_sgd(opt)
+    shape = (a.batch_size, 3, a.image_size, a.image_size)
+    batches = make_host_batches(steps, shape, a.num_classes, seed=99 + rank)
+    step = TrainStep(ours, opt, None, batch_shape=shape, cuda_graph=True)
+    l_ours = []
+    for x, t in batches:
+        step(x, t)
+        l_ours.append(step.read_loss(lag=0))
+    torch.cuda.synchronize()
+    if ddp is not None:
+        ddp.comm.check_health()
+        ddp.shutdown()
+    tv = getattr(torchvision.models, a.arch)(num_classes=a.num_classes).to(device)
+    tv.load_state_dict(init)
+    if world > 1:
+        tv = torch.nn.parallel.DistributedDataParallel(tv, device_ids=[local])
+    topt = torch.optim.SGD(tv.parameters(), lr=0.01, momentum=0.9, weight_decay=5e-4)
+    l_ref = []
+    for x, t in batches:
+        x, t = x.to(device, non_blocking=True), t.to(device, non_blocking=True)
+        topt.zero_grad(set_to_none=True)
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            loss = F.cross_entropy(tv(x), t)
+        loss.backward()
+        topt.step()
+        l_ref.append(float(loss.item()))
+    rel = max(abs(o - r) / max(abs(r), 1e-6) for o, r in zip(l_ours, l_ref))
+    return {"what": "rank-0 training loss per step, same initial weights and batches, lr 0.01, bf16",
+            "loss_ours": [round(v, 4) for v in l_ours],
+            "loss_torch_ddp_nccl": [round(v, 4) for v in l_ref],
+            "max_rel_diff": rel}
+
+
+def fp16_scaler_arm(a, device, rank, world, local) -> dict:
+    """The reference's LITERAL --amp numerics (fp16 autocast + dynamic GradScaler,
+    train_ddp.py:203-209, 346) through the native path: same-precision throughput next to the
+    bf16 headline, device-timed the same way."""
+    import torch
+    from dpt_b200.amp import GradScaler
+    from dpt_b200.graph_step import TrainStep
+    from dpt_b200.models.resnet import build_model
+    from dpt_b200.optim import SGD
+    from dpt_b200.parallel.ddp import DistributedDataParallel
+    model = build_model(device, a.arch, a.num_classes)
+    ddp = None
+    if world > 1:
+        model = ddp = DistributedDataParallel(model, device_ids=[local], backend="native",
+                                              bucket_cap_mb=a.bucket_cap_mb, comm_ctas=a.comm_ctas)
+    opt = SGD(model.parameters(), lr=0.1, momentum=0.9, weight_decay=5e-4)
+    scaler = GradScaler(device=device, enabled=True)
+    shape = (a.batch_size, 3, a.image_size, a.image_size)
+    step = TrainStep(model, opt, scaler, batch_shape=shape, cuda_graph=True, dtype=torch.float16)
+    x, t = make_host_batches(1, shape, a.num_classes, seed=5 + rank)[0]
+    for _ in range(max(a.warmup, 3)):
+        step(x, t)
+    barrier_sync()
+    K = a.steps
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(K):
+        step.graph.replay()
+    e1.record()
+    barrier_sync()
+    ms = max_over_ranks(e0.elapsed_time(e1), device)
+    res = {"value": a.batch_size * world * K / (ms * 1e-3), "unit": "samples/s",
+           "ms_per_step": ms / K, "dtype": "fp16 + dynamic GradScaler (device-side skip/update)",
+           "loss_scale_after": scaler.get_scale(), "launches_per_step": int(step.launches_per_step)}
+    if ddp is not None:
+        ddp.comm.check_health()
+        ddp.shutdown()
+    return res
+
 
 
 def run_profile_sync(a):
@@ -419,7 +595,11 @@ def run_reference(a):
                 "d2h_bytes_per_step": 12,
                 "note": "the reference loop itself copies pinned inputs H2D and reads loss/correct "
                         "with .item() every step, so its device-timed and end-to-end regions coincide"},
-        "gpu_launches": 0,
+        # kernels of THIS repository launched by the reference arm: none by construction (it runs
+        # cuDNN / cuBLAS / ATen / NCCL kernels, which are not counted here)
+        "gpu_launches": None,
+        "gpu_launches_note": "library kernels only (cuDNN/cuBLAS/ATen/NCCL), ~190 per step per "
+                             "SURVEY 3.2; none from this repository",
     }
     if rank == 0:
         print(json.dumps(res))

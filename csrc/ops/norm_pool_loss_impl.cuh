@@ -1507,95 +1507,29 @@ inline int dpt_nchw_f32_to_nhwc_bf16(const float* x, void* y, int N, int C, int 
 }
 
 
-#ifndef DPT_LOWP_IS_F16
-// ------------------------------------------------------------------------------------------------
-// Allocation-free BatchNorm training forward.
-//
-// Who needs this: a BatchNorm forward in training mode needs a little scratch between its two
-// passes (per-channel sum and sum of squares).  The regular entry points (dpt_bn_stats +
-// dpt_bn_fwd_train) leave that scratch to the caller, who normally gets it from cudaMalloc or
-// from a framework allocator.  Some callers must not do either: a host that has handed its whole
-// memory budget to a fixed plan at start-up and forbids later allocations, a latency-critical
-// loop that cannot afford the device-wide synchronisation cudaMalloc/cudaFree imply, or a plugin
-// that is called with nothing but raw pointers and a stream and has no allocator to ask.  For
-// them this entry point carries its own scratch: a file-scope device array, so every GPU that
-// loads this library holds 2 * DPT_BN_NOALLOC_MAX_CHANNELS floats (32 KiB) until the process
-// exits.  It calls no cudaMalloc / cudaFree and no allocating library routine; the caller still
-// passes every input and output.
-//
-// Rules of use:
-//  * C must be <= DPT_BN_NOALLOC_MAX_CHANNELS (4096); larger C is rejected with
-//    DPT_ERR_TOO_LARGE and a message on stderr.
-//  * The first call on each device looks up the device address of the scratch array (once per
-//    device, with that device current) — make that first call before starting any stream
-//    capture on that device.
-//  * All calls on a device share the one array, and it keeps whatever the previous call left;
-//    the entry point clears the part it uses before accumulating.  Two calls that overlap on the
-//    GPU (different streams without ordering between them) race on it: serialise them.
-constexpr int kBnNoAllocMaxChannels = 4096;
-static __device__ __align__(256) float g_bn_noalloc_scratch[2 * kBnNoAllocMaxChannels];
-
-namespace {
-constexpr int kMaxDevices = 64;
-float* g_bn_scratch_dev_ptr[kMaxDevices] = {nullptr};
-std::mutex g_bn_scratch_mutex;
-
-// In host code `g_bn_noalloc_scratch` is only a handle for the symbol, not a device address:
-// resolve it through the runtime for the current device and cache the answer per device.
-int bn_noalloc_scratch(float** out) {
-    int dev = -1;
-    cudaError_t e = cudaGetDevice(&dev);
-    if (e != cudaSuccess) return static_cast<int>(e);
-    if (dev < 0 || dev >= kMaxDevices) return DPT_ERR_ARG;
-    std::lock_guard<std::mutex> lock(g_bn_scratch_mutex);
-    if (g_bn_scratch_dev_ptr[dev] == nullptr) {
-        float* ptr = nullptr;
-        e = cudaGetSymbolAddress((void**)&ptr, g_bn_noalloc_scratch);
-        if (e != cudaSuccess) return static_cast<int>(e);
-        g_bn_scratch_dev_ptr[dev] = ptr;
-    }
-    *out = g_bn_scratch_dev_ptr[dev];
-    return 0;
-}
-}  // namespace
-
-inline int dpt_bn_fwd_train_noalloc(const void* x, const float* gamma, const float* beta,
-                                        const void* residual, void* y, float* save_mean,
-                                        float* save_invstd, float* running_mean,
-                                        float* running_var, long long* num_batches_tracked,
-                                        long long M, int C, float momentum, float eps, int relu,
-                                        void* stream) {
-    if (C > kBnNoAllocMaxChannels) {
-        fprintf(stderr,
-                "[dptb200] dpt_bn_fwd_train_noalloc: C = %d exceeds the built-in scratch "
-                "(max %d channels); use dpt_bn_stats + dpt_bn_fwd_train with your own buffer\n",
-                C, kBnNoAllocMaxChannels);
-        return DPT_ERR_TOO_LARGE;
-    }
-    if (!cvec_ok(C) || M <= 0) return DPT_ERR_SHAPE;
-    float* scratch = nullptr;
-    int rc = bn_noalloc_scratch(&scratch);
-    if (rc != 0) return rc;
+// Statistics + normalisation with caller-provided (already zeroed) scratch of 2*C floats: the
+// per-element-type half of dpt_bn_fwd_train_noalloc (norm_pool_loss.cu).
+inline int bn_fwd_train_with_scratch(float* scratch, const void* x, const float* gamma,
+                                     const float* beta, const void* residual, void* y,
+                                     float* save_mean, float* save_invstd, float* running_mean,
+                                     float* running_var, long long* num_batches_tracked,
+                                     long long M, int C, float momentum, float eps, int relu,
+                                     void* stream) {
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     float* sum = scratch;
     float* sq = scratch + C;
-    // the array still holds the previous call's sums: clear the 2*C floats used here
-    cudaError_t e = cudaMemsetAsync(scratch, 0, sizeof(float) * 2 * C, st);
-    if (e != cudaSuccess) return static_cast<int>(e);
     const long long nvec = M * (C / 8);
     ew_pdl_gate();
-    launch_pdl(bn_stats_kernel, dim3(reduce_grid(nvec)), dim3(kEwThreads), 0, st, static_cast<const bf16x8*>(x), sum,
-                                                                 sq, nvec, C / 8);
+    launch_pdl(bn_stats_kernel, dim3(reduce_grid(nvec)), dim3(kEwThreads), 0, st,
+               static_cast<const bf16x8*>(x), sum, sq, nvec, C / 8);
     const float unbias = M > 1 ? static_cast<float>(M) / static_cast<float>(M - 1) : 1.f;
     ew_pdl_gate();
-    launch_pdl(bn_fwd_kernel, dim3(ew_grid(nvec, C / 8)), dim3(kEwThreads), 0, st, 
+    launch_pdl(bn_fwd_kernel, dim3(ew_grid(nvec, C / 8)), dim3(kEwThreads), 0, st,
         static_cast<const bf16x8*>(x), sum, sq, gamma, beta, static_cast<const bf16x8*>(residual),
         static_cast<bf16x8*>(y), save_mean, save_invstd, running_mean, running_var,
         num_batches_tracked, nvec, C / 8, 1.f / static_cast<float>(M), unbias, momentum, eps, relu);
     DPT_CHECK_LAUNCH();
 }
-
-#endif  // !DPT_LOWP_IS_F16
 
 inline int dpt_augment_crop_flip_norm(const void* in_u8, const int* params, float* out, int N,
                                           int C, int S, int pad, const float* mean3,

@@ -23,8 +23,13 @@ from .parallel.ddp import DistributedDataParallel
 
 class TrainStep:
     def __init__(self, model, optimizer, scaler=None, *, batch_shape, cuda_graph: bool = True,
-                 warmup: int = 2, lazy_buffer_sync: bool = True, dtype=torch.bfloat16) -> None:
+                 warmup: int = 2, lazy_buffer_sync: bool = True, dtype=torch.bfloat16,
+                 trace_records: int = 0) -> None:
         self.lazy_buffer_sync = lazy_buffer_sync
+        # optional device-clock timeline (benchmarks/step_trace.py): phase stamps of this step
+        # and, under DDP, one record per collective kernel — valid under CUDA-graph replay
+        self.trace = None
+        self._trace_records = int(trace_records)
         self.dtype = dtype
         self.ddp = model if isinstance(model, DistributedDataParallel) else None
         self.net = model.module if self.ddp is not None else model
@@ -87,6 +92,11 @@ class TrainStep:
         import os
         self._poison = os.environ.get("DPT_DEBUG_POISON", "0") == "1"
         self._setup_chunked_sgd()
+        if self._trace_records > 0 and dev.type == "cuda":
+            self.trace = torch.zeros((1 + self._trace_records) * 4, dtype=torch.int64, device=dev)
+            if self.ddp is not None and self.ddp.comm is not None:
+                _Fn._lib.lib().dpt_comm_set_trace(self.ddp.comm.handle, self.trace.data_ptr(),
+                                                  self._trace_records)
         if cuda_graph and dev.type == "cuda":
             self._capture(warmup)
 
@@ -137,10 +147,38 @@ class TrainStep:
                                  g0["nesterov"])
 
     # ------------------------------------------------------------------ the step
+    def _stamp(self, tag: int) -> None:
+        if self.trace is not None:
+            from .ops import _lib
+            _lib.lib().dpt_trace_stamp(self.trace.data_ptr(), self._trace_records, tag, _lib.stream())
+
+    def read_trace(self, reset: bool = True) -> list[dict]:
+        """Records appended since the last reset: {"kind": "stamp"|"oneshot"|"twoshot"|"nvls",
+        "tag"/"bytes", "t0", "t_barrier", "t1"} in globaltimer ns (device clock of this GPU)."""
+        torch.cuda.synchronize()
+        raw = self.trace.cpu().tolist()
+        n = min(raw[0], self._trace_records)
+        names = {1: "oneshot", 2: "twoshot", 3: "nvls", 255: "stamp"}
+        out = []
+        for i in range(n):
+            w0, t0, tb, t1 = raw[4 + 4 * i: 8 + 4 * i]
+            kind = (w0 >> 56) & 0xFF
+            val = w0 & ((1 << 56) - 1)
+            rec = {"kind": names.get(kind, str(kind)), "t0": t0}
+            if kind == 255:
+                rec["tag"] = val
+            else:
+                rec.update(bytes=val, t_barrier=tb, t1=t1)
+            out.append(rec)
+        if reset:
+            self.trace.zero_()
+        return out
+
     def _body(self) -> None:
         Fn = self.Fn
         ddp = self.ddp
         Fn.set_lowp_dtype(self.dtype)
+        self._stamp(1)
         if ddp is not None:
             ddp.sync_buffers(lazy=self.lazy_buffer_sync)
             ddp.prepare_for_backward()
@@ -151,9 +189,12 @@ class TrainStep:
         Fn.cross_entropy(logits, self.t, loss=self.loss, dlogits=self.dlogits,
                          loss_scale=self.scaler.scale_tensor if self.scaler is not None else None,
                          metrics=self.metrics)
+        self._stamp(2)
         self.eng.backward(self.dlogits)
+        self._stamp(3)          # every backward kernel (incl. the last weight gradient) is done
         if ddp is not None:
             ddp.finalize_backward()
+        self._stamp(4)          # ... and so is every bucket kernel: 4 - 3 = exposed gradient sync
         from .ops import _lib
         _lib.pdl_skip_next()          # the optimizer kernel follows cross-stream joins
         sc = self.scaler
@@ -168,6 +209,7 @@ class TrainStep:
             sc.update()
         if self._poison:
             self.arena.grad.fill_(float("nan"))
+        self._stamp(5)
 
     def _snapshot(self):
         snap = {"param": self.arena.param.clone(), "metrics": self.metrics.clone()}

@@ -219,6 +219,29 @@ class Communicator:
         _lib.count()
         return out
 
+    def allreduce_oneshot_push_(self, grads: torch.Tensor, staging: SymmBuffer, cap: int, *,
+                                scale: float | None = None, inv_scale: torch.Tensor | None = None,
+                                found_inf: torch.Tensor | None = None, sgd: dict | None = None,
+                                ctas: int = 0, stream: int | None = None) -> None:
+        """One-shot push all-reduce of the local fp32 tensor ``grads`` (numel % 4 == 0, at most
+        ``cap``) through ``staging`` (a SymmBuffer of 2 * world * cap floats).  In place, or with
+        ``sgd = {param, shadow, momentum (local tensors), lr, momentum_coef, weight_decay}`` the
+        replicated fused update."""
+        if scale is None:
+            scale = 1.0 / self.world
+        st = _lib.stream() if stream is None else stream
+        if sgd is not None:
+            args = (_lib.ptr(sgd["param"]), _lib.ptr(sgd["shadow"]), _lib.ptr(sgd["momentum"]),
+                    sgd["lr"], sgd["momentum_coef"], sgd["weight_decay"],
+                    int(sgd.get("nesterov", False)))
+        else:
+            args = (None, None, None, 0.0, 0.0, 0.0, 0)
+        _lib.check(self.lib.dpt_allreduce_oneshot_push(
+            self.handle, grads.data_ptr(), staging.ptrs(0), cap, grads.numel(), scale,
+            _lib.ptr(inv_scale), _lib.ptr(found_inf), *args, ctas, st), "dpt_allreduce_oneshot_push")
+        self.launches += 1
+        _lib.count()
+
     def broadcast_(self, buf: SymmBuffer, byte_offset: int, nbytes: int, src: int = 0,
                    ctas: int = 0, stream: int | None = None) -> None:
         if self.world == 1:

@@ -287,6 +287,7 @@ class DistributedDataParallel(nn.Module):
         cap = (max(fit) + 3) // 4 * 4
         if 2 * self.world_size * cap * 4 > (1 << 30):     # keep the staging area below 1 GiB
             cap = ((1 << 30) // (8 * self.world_size)) // 4 * 4
+        self.oneshot_cap = cap
         self.oneshot_buf = self.comm.alloc(2 * self.world_size * cap * 4)
         self.reducer.set_oneshot(list(self.oneshot_buf.peer_ptrs), cap, self.oneshot_max_bytes,
                                  self.rank, min(comm_ctas, 8) if comm_ctas > 0 else 8)

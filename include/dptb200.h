@@ -99,13 +99,16 @@ int dpt_bn_bwd_apply(const void* g, const void* x, const float* save_mean, const
 /* BatchNorm training forward for callers that may not allocate (fixed start-up memory plans,
  * loops that cannot take cudaMalloc's device-wide sync, plugins handed only pointers + a stream).
  * This entry point has no counterpart in the reference; it exists for those callers only.
- * Same result as dpt_bn_stats followed by dpt_bn_fwd_train, but the sum / sum-of-squares scratch
- * is a 32 KiB device array built into the library (held by every GPU that loads it until exit),
- * so nothing is allocated.  Limits: C <= DPT_BN_NOALLOC_MAX_CHANNELS, otherwise
- * DPT_ERR_TOO_LARGE.  The first call on a device resolves the array's address for that device
- * (make it before any stream capture there).  Calls on one device share the array: it is
- * cleared at the start of each call, and calls that overlap on the GPU race — serialise them. */
-#define DPT_BN_NOALLOC_MAX_CHANNELS 4096
+ * Same result as dpt_bn_stats followed by dpt_bn_fwd_train (and, like them, on activations of
+ * the element type set with dpt_set_lowp_dtype: bf16, fp16 or fp32), but the sum / sum-of-squares
+ * scratch is a 16 KiB device array built into the library (held by every GPU that loads it
+ * until exit), so nothing is allocated.  Limits: C <= DPT_BN_NOALLOC_MAX_CHANNELS, otherwise
+ * DPT_ERR_TOO_LARGE; within the limit C must be 8 * 2^k like for the other BatchNorm entry
+ * points (DPT_ERR_SHAPE otherwise), so the maximum itself is usable.  The first call on a device
+ * resolves the array's address for that device (make it before any stream capture there).
+ * Calls on one device share the array: it is cleared at the start of each call, and calls that
+ * overlap on the GPU race — serialise them. */
+#define DPT_BN_NOALLOC_MAX_CHANNELS 2048
 int dpt_bn_fwd_train_noalloc(const void* x, const float* gamma, const float* beta,
                              const void* residual, void* y, float* save_mean, float* save_invstd,
                              float* running_mean, float* running_var,

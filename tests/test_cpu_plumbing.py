@@ -387,3 +387,43 @@ def test_resume_continues_where_the_checkpoint_left_off(tmp_path, capsys):
     assert len(ck3["optimizer"]["state"]) == 62
     lines = open(os.path.join(out, "metrics_rank0.csv")).read().splitlines()
     assert [ln.split(",")[0] for ln in lines] == ["epoch", "1", "2", "3"]
+
+
+def test_missing_dataset_is_an_error_unless_synthetic(tmp_path):
+    """A mistyped --data-dir must not silently train on random data (the reference would have
+    downloaded CIFAR-10, train_ddp.py:103-112; offline that is an error, not a fallback)."""
+    from dpt_b200.cli import parse_args
+    from dpt_b200.data import build_datasets
+    args = parse_args(["--data-dir", str(tmp_path / "nope")])
+    with pytest.raises(FileNotFoundError, match="--synthetic"):
+        build_datasets(args)
+    train, test = build_datasets(parse_args(["--data-dir", str(tmp_path / "nope"), "--synthetic",
+                                             "--synthetic-size", "10"]))
+    assert len(train) == 10
+
+
+def test_tail_bucket_split_and_cli_auto_switches():
+    """The last-ready gradients (stem conv + bn) get a bucket of their own for the one-shot
+    kernel; every other bucket is unchanged, and an already small last bucket is left alone.
+    The fast-path switches default to 'auto' (None) and --bucket-cap-mb 25 means 25."""
+    from dpt_b200.cli import parse_args
+    from dpt_b200.models.resnet import build_model
+    from dpt_b200.parallel.arena import ParamArena
+    from dpt_b200.parallel.bucket import plan_arena_buckets, split_tail
+    m = build_model(torch.device("cpu"), "resnet18", 10)
+    arena = ParamArena(list(m.named_parameters()), "cpu")
+    base = plan_arena_buckets(arena, 4 << 20, 1 << 20)
+    tail = plan_arena_buckets(arena, 4 << 20, 1 << 20, 64 << 10)
+    assert len(tail) == len(base) + 1
+    assert [p["params"] for p in tail[:-2]] == [p["params"] for p in base[:-1]]
+    names = [arena.slot(arena.order[i]).name for i in tail[-1]["params"]]
+    assert sorted(names) == ["bn1.bias", "bn1.weight", "conv1.weight"] and tail[-1]["bytes"] == 38144
+    assert tail[-2]["offset"] + tail[-2]["numel"] == tail[-1]["offset"]
+    assert tail[-1]["offset"] + tail[-1]["numel"] == base[-1]["offset"] + base[-1]["numel"]
+    assert split_tail([[0, 1], [2, 3]], [100, 100, 10, 10], 64) == [[0, 1], [2, 3]]
+    assert split_tail([[0, 1, 2]], [1000, 10, 10], 64) == [[0], [1, 2]]
+    a = parse_args([])
+    assert a.cuda_graph is None and a.fused_optimizer is None and a.bucket_cap_mb is None
+    assert parse_args(["--bucket-cap-mb", "25"]).bucket_cap_mb == 25.0
+    assert parse_args(["--no-cuda-graph"]).cuda_graph is False
+    assert parse_args(["--fused-optimizer"]).fused_optimizer is True

@@ -143,6 +143,98 @@ def test_peer_memory_collectives():
     _run(_collectives_worker)
 
 
+# --------------------------------------------------------------------------------- one-shot push
+def _oneshot_push_worker(rank, world):
+    """dpt_allreduce_oneshot_push vs the NCCL sum: in place (F1 epilogue incl. inv_scale and the
+    non-finite flag), back-to-back calls with nothing in between (the double-buffered staging
+    area), and the replicated fused SGD update vs all-reduce -> torch.optim.SGD."""
+    import torch.distributed as dist
+    from dpt_b200.parallel.comm import Communicator
+    comm = Communicator(timeout_s=20.0)
+    dev = torch.device("cuda", rank)
+    cap = 65536
+    staging = comm.alloc(2 * world * cap * 4)
+    for n in (4, 1024, 9536, 65536):
+        for rep in range(5):
+            x = torch.randn(n, device=dev,
+                            generator=torch.Generator(device=dev).manual_seed(977 * rank + n + rep))
+            ref = x.clone()
+            dist.all_reduce(ref)
+            g = x.clone()
+            torch.cuda.synchronize()
+            comm.allreduce_oneshot_push_(g, staging, cap)
+            torch.cuda.synchronize()
+            err = (g - ref / world).abs().max().item()
+            assert err <= 1e-5 * max(1.0, ref.abs().max().item()), (n, rep, err)
+            lo, hi = g.clone(), g.clone()
+            dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+            dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+            assert torch.equal(lo, hi), (n, rep)
+    # 50 back-to-back calls, different data every time, no host sync in between
+    n = 9536
+    outs, refs = [], []
+    for it in range(50):
+        x = torch.full((n,), float(rank + 1 + it), device=dev)
+        outs.append(x)
+        refs.append(sum(float(r + 1 + it) for r in range(world)) / world)
+    torch.cuda.synchronize()
+    dist.barrier()
+    for x in outs:
+        comm.allreduce_oneshot_push_(x, staging, cap)
+    torch.cuda.synchronize()
+    for it, (x, r) in enumerate(zip(outs, refs)):
+        assert torch.allclose(x, torch.full_like(x, r)), (it, x[:2].tolist(), r)
+    # n beyond the staging capacity is refused, not truncated
+    big = torch.zeros(cap + 4, device=dev)
+    with pytest.raises(RuntimeError):
+        comm.allreduce_oneshot_push_(big, staging, cap)
+    # inv_scale + non-finite detection (the flag is local: every rank sees the same sums)
+    inv = torch.tensor(0.5, device=dev)
+    finf = torch.zeros(1, device=dev)
+    g = torch.full((1024,), 2.0, device=dev)
+    comm.allreduce_oneshot_push_(g, staging, cap, inv_scale=inv, found_inf=finf)
+    torch.cuda.synchronize()
+    assert torch.allclose(g, torch.full_like(g, 1.0)) and finf.item() == 0.0
+    g = torch.ones(1024, device=dev)
+    if rank == world - 1:
+        g[77] = float("nan")
+    comm.allreduce_oneshot_push_(g, staging, cap, inv_scale=inv, found_inf=finf)
+    torch.cuda.synchronize()
+    assert finf.item() == 1.0
+    # replicated fused SGD
+    n = 9536
+    p = torch.randn(n, device=dev, generator=torch.Generator(device=dev).manual_seed(5))
+    shadow = torch.zeros(n, device=dev, dtype=torch.bfloat16)
+    m = torch.zeros(n, device=dev)
+    ref_p = torch.nn.Parameter(p.clone())
+    opt = torch.optim.SGD([ref_p], lr=0.1, momentum=0.9, weight_decay=5e-4)
+    for it in range(4):
+        gi = torch.randn(n, device=dev, generator=torch.Generator(device=dev).manual_seed(100 * rank + it))
+        gsum = gi.clone()
+        dist.all_reduce(gsum)
+        ref_p.grad = gsum / world
+        opt.step()
+        comm.allreduce_oneshot_push_(gi, staging, cap, sgd={"param": p, "shadow": shadow, "momentum": m,
+                                                            "lr": 0.1, "momentum_coef": 0.9,
+                                                            "weight_decay": 5e-4})
+    torch.cuda.synchronize()
+    assert torch.allclose(p, ref_p.data, atol=1e-5, rtol=1e-5)
+    assert torch.allclose(m, opt.state[ref_p]["momentum_buffer"], atol=1e-5, rtol=1e-5)
+    assert torch.equal(shadow, p.bfloat16())
+    lo, hi = p.clone(), p.clone()
+    dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+    dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+    assert torch.equal(lo, hi)
+    comm.check_health()
+    comm.validate_epochs()
+    comm.close()
+
+
+@needs2
+def test_oneshot_push_allreduce():
+    _run(_oneshot_push_worker)
+
+
 # --------------------------------------------------------------------------------- fused SGD
 def _fused_sgd_worker(rank, world):
     import torch.distributed as dist
@@ -246,6 +338,12 @@ def test_native_ddp_matches_torch_ddp_nccl():
 
 
 def _trainstep_worker(rank, world):
+    """TrainStep under the native DDP wrapper, every (graph, fused update, scaler, algorithm)
+    combination against ONE oracle: the same native model stepped with gradients averaged by
+    torch.distributed (NCCL) and the plain flat SGD kernel.  The parameter UPDATE (p_final -
+    p_init) of every rank-slice of every bucket must match the oracle's — a reduction that is
+    wrong but symmetric (a dropped slice, a wrong 1/world) fails here even though the replicas
+    agree with each other."""
     import torch.distributed as dist
     from dpt_b200.amp import GradScaler
     from dpt_b200.graph_step import TrainStep
@@ -254,50 +352,85 @@ def _trainstep_worker(rank, world):
     from dpt_b200.parallel.ddp import DistributedDataParallel as OurDDP
     dev = torch.device("cuda", rank)
     shape = (32, 3, 32, 32)
-    configs = [(False, False, False, "twoshot"), (True, False, False, "twoshot"),
-               (True, True, False, "twoshot"), (True, False, True, "twoshot"),
-               (True, False, False, "nvls"), (True, True, False, "nvls")]
-    if os.environ.get("DPT_TEST_MCPUSH", "0") == "1":
-        # experimental: fused-SGD two-shot whose publish phase is one multicast store
-        configs.append((True, True, False, "twoshot_mc"))
-    for graph, fused, fp16_scaler, algo in configs:
+    steps = 6
+    g = torch.Generator().manual_seed(3 + rank)
+    x = torch.randn(shape, generator=g).pin_memory()
+    t = torch.randint(0, 10, (32,), generator=g).pin_memory()
+
+    def run(backend, graph, fused, fp16_scaler, algo):
         torch.manual_seed(11 + rank)
-        model = OurDDP(build_model(dev, "resnet18", 10), device_ids=[rank], backend="native",
+        model = OurDDP(build_model(dev, "resnet18", 10), device_ids=[rank], backend=backend,
                        allreduce_algo=algo)
+        if algo == "twoshot_mc" and not getattr(model, "nvls", False):
+            model.shutdown()           # NVSwitch multicast not exposed on this host
+            return None
+        init = model.arena.param.clone()
         opt = SGD(model.parameters(), lr=0.02, momentum=0.9, weight_decay=5e-4)
         if fused:
             assert model.enable_fused_sgd(opt)
         scaler = GradScaler(device=dev, init_scale=256.0, enabled=fp16_scaler)
         step = TrainStep(model, opt, scaler, batch_shape=shape, cuda_graph=graph)
-        g = torch.Generator().manual_seed(3 + rank)
-        x = torch.randn(shape, generator=g).pin_memory()
-        t = torch.randint(0, 10, (32,), generator=g).pin_memory()
         losses = []
-        for _ in range(8):
+        for _ in range(steps):
             step(x, t)
             losses.append(step.read_loss(lag=0))
         torch.cuda.synchronize()
+        return model, opt, scaler, init, losses
+
+    oracle, _, _, init0, losses0 = run("nccl", False, False, False, "auto")
+    delta0 = (oracle.arena.param - init0).clone()
+    assert losses0[-1] < losses0[0], losses0
+    slices = []
+    for pl in oracle.plans:
+        n4 = pl["numel"] // 4
+        per = (n4 + world - 1) // world
+        for r in range(world):
+            lo, hi = min(n4, per * r) * 4, min(n4, per * (r + 1)) * 4
+            if hi - lo >= 256:
+                slices.append((pl["offset"] + lo, pl["offset"] + hi))
+
+    configs = [(False, False, False, "auto"), (True, False, False, "twoshot"),
+               (True, True, False, "twoshot"), (True, True, False, "auto"),
+               (True, True, False, "oneshot"), (True, False, True, "auto"),
+               (True, False, False, "nvls"), (True, True, False, "nvls"),
+               (True, True, False, "twoshot_mc")]
+    for graph, fused, fp16_scaler, algo in configs:
+        res = run("native", graph, fused, fp16_scaler, algo)
+        if res is None:
+            continue
+        model, opt, scaler, init, losses = res
+        tag = f"graph={graph} fused={fused} scaler={fp16_scaler} algo={algo} -> {model.bucket_algorithms()}"
         model.comm.check_health()
-        assert losses[-1] < losses[0], (graph, fused, algo, losses)
+        assert torch.equal(init, init0), "construction broadcast differs between backends"
+        assert losses[-1] < losses[0], (tag, losses)
+        assert abs(losses[-1] - losses0[-1]) < 0.05 * abs(losses0[-1]) + 0.02, (tag, losses, losses0)
         assert model.verify_replicas()                 # bit-exact parameter digest, all ranks
         ep = model.comm.validate_epochs()              # same collectives issued everywhere
         assert max(ep) > 0
-        cs = model.arena.param.double().sum().reshape(1)
-        lo, hi = cs.clone(), cs.clone()
-        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
-        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
-        assert torch.equal(lo, hi), f"replicas diverged (graph={graph}, fused={fused}, algo={algo})"
+        delta = model.arena.param - init
+        worst = 0.0
+        for lo, hi in slices:
+            den = delta0[lo:hi].norm().item()
+            if den < 1e-6:
+                continue
+            rel = (delta[lo:hi] - delta0[lo:hi]).norm().item() / den
+            worst = max(worst, rel)
+            assert rel < 0.08, f"{tag}: update of arena[{lo}:{hi}] differs from the NCCL oracle by {rel:.3f}"
         shc = model.arena.shadow.double().sum().reshape(1)
         lo2, hi2 = shc.clone(), shc.clone()
         dist.all_reduce(lo2, op=dist.ReduceOp.MIN)
         dist.all_reduce(hi2, op=dist.ReduceOp.MAX)
-        assert torch.equal(lo2, hi2), f"bf16 shadows diverged (fused={fused}, algo={algo})"
+        assert torch.equal(lo2, hi2), f"bf16 shadows diverged ({tag})"
         assert torch.equal(model.arena.shadow, model.arena.param.bfloat16()), "shadow != bf16(param)"
-        sh = model.arena.shadow.float().sum().reshape(1)
-        assert torch.isfinite(sh).all()
         if fp16_scaler:
             assert scaler.get_scale() == 256.0
+        if algo == "auto":
+            assert model.bucket_algorithms()[-1] == "oneshot" and model.plans[-1]["bytes"] <= 65536
+        if rank == 0:
+            print(f"[trainstep] {tag}: final loss {losses[-1]:.4f} (oracle {losses0[-1]:.4f}), "
+                  f"worst slice update error {worst:.4f}")
         model.shutdown()
+    oracle.shutdown()
 
 
 @needs2
@@ -442,3 +575,162 @@ def _compat_loop_worker(rank, world):
 @needs2
 def test_reference_style_loop_under_native_ddp():
     _run(_compat_loop_worker, world=2)
+
+
+# --------------------------------------------------------------------------------- checkpoint
+def _fused_checkpoint_worker(rank, world):
+    """With the SGD update fused into the two-shot all-reduce each rank holds momentum only for
+    the slices it owns.  save_checkpoint must gather the shards: the saved momentum_buffers equal
+    those of an unfused run on the same batches, and a resumed (unfused) run continues like it."""
+    import tempfile
+    import torch.distributed as dist
+    from dpt_b200.checkpoint import load_checkpoint, save_checkpoint
+    from dpt_b200.graph_step import TrainStep
+    from dpt_b200.models.resnet import build_model
+    from dpt_b200.optim import SGD
+    from dpt_b200.parallel.ddp import DistributedDataParallel as OurDDP
+    dev = torch.device("cuda", rank)
+    shape = (16, 3, 32, 32)
+    g = torch.Generator().manual_seed(21 + rank)
+    batches = [(torch.randn(shape, generator=g).pin_memory(),
+                torch.randint(0, 10, (16,), generator=g).pin_memory()) for _ in range(5)]
+
+    def build(fused):
+        torch.manual_seed(31 + rank)
+        model = OurDDP(build_model(dev, "resnet18", 10), device_ids=[rank], backend="native",
+                       allreduce_algo="twoshot" if fused else "auto")
+        opt = SGD(model.parameters(), lr=0.01, momentum=0.9, weight_decay=5e-4)
+        if fused:
+            assert model.enable_fused_sgd(opt)
+            assert len(model.momentum_shards()) >= world
+        step = TrainStep(model, opt, None, batch_shape=shape, cuda_graph=True)
+        return model, opt, step
+
+    path = [None]
+    if rank == 0:
+        path[0] = os.path.join(tempfile.mkdtemp(prefix="dpt_ckpt_"), "checkpoint.pt")
+    dist.broadcast_object_list(path, src=0)
+    # fused run: 3 steps, checkpoint (collective: gathers the momentum shards)
+    model, opt, step = build(True)
+    for x, t in batches[:3]:
+        step(x, t)
+    torch.cuda.synchronize()
+    own = opt._flat_momentum().clone()
+    save_checkpoint(path[0], model, opt, None, 1, None, rank)
+    gathered = opt._flat_momentum().clone()
+    lo, hi = gathered.clone(), gathered.clone()
+    dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+    dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+    assert torch.equal(lo, hi), "momentum differs between ranks after the gather"
+    for a, b, owner in model.momentum_shards():
+        if owner == rank:
+            assert torch.equal(gathered[a:b], own[a:b]), "the owner's shard must be untouched"
+    p_fused = model.arena.param.clone()
+    model.shutdown()
+    dist.barrier()
+    # unfused run on the same batches
+    model2, opt2, step2 = build(False)
+    for x, t in batches[:3]:
+        step2(x, t)
+    torch.cuda.synchronize()
+    m_ref = opt2._flat_momentum()
+    rel = (gathered - m_ref).norm().item() / (m_ref.norm().item() + 1e-12)
+    assert rel < 0.02, f"gathered momentum differs from the unfused run ({rel:.4f})"
+    for pl in model2.plans:                       # no slice left stale / zero
+        a, b = pl["offset"], pl["offset"] + pl["numel"]
+        r2 = (gathered[a:b] - m_ref[a:b]).norm().item() / (m_ref[a:b].norm().item() + 1e-12)
+        assert r2 < 0.05, f"bucket at {a}: momentum error {r2:.4f}"
+    relp = (p_fused - model2.arena.param).norm().item() / (model2.arena.param.norm().item())
+    assert relp < 1e-3, relp
+    # resume from the fused checkpoint into an unfused run and compare the continuation
+    for x, t in batches[3:]:
+        step2(x, t)
+    torch.cuda.synchronize()
+    p_cont = model2.arena.param.clone()
+    model2.shutdown()
+    dist.barrier()
+    model3, opt3, step3 = build(False)
+    payload = load_checkpoint(path[0], model3, opt3, None)
+    assert payload["epoch"] == 1
+    m3 = opt3._flat_momentum()
+    assert (m3 - gathered).abs().max().item() == 0.0, "resume must restore the gathered momentum"
+    for x, t in batches[3:]:
+        step3(x, t)
+    torch.cuda.synchronize()
+    rel2 = (model3.arena.param - p_cont).norm().item() / p_cont.norm().item()
+    assert rel2 < 2e-3, f"resumed run diverged from the uninterrupted one ({rel2:.5f})"
+    assert model3.verify_replicas()
+    model3.shutdown()
+
+
+@needs2
+def test_checkpoint_after_fused_sgd_gathers_momentum_shards():
+    _run(_fused_checkpoint_worker, world=2)
+
+
+# --------------------------------------------------------------------------------- killed rank
+def _killed_rank_worker(rank, world, port, q):
+    """Rank 1's process disappears in the middle of training (os._exit inside the step loop).
+    Rank 0 must END with a diagnostic naming the missing rank — through the watchdog DDP starts
+    (exit code 70) or the health check — instead of spinning in a collective forever."""
+    import time
+    _init(rank, world, port)
+    from dpt_b200.graph_step import TrainStep
+    from dpt_b200.models.resnet import build_model
+    from dpt_b200.optim import SGD
+    from dpt_b200.parallel.ddp import DistributedDataParallel as OurDDP
+    dev = torch.device("cuda", rank)
+    shape = (16, 3, 32, 32)
+    model = OurDDP(build_model(dev, "resnet18", 10), device_ids=[rank], backend="native",
+                   comm_timeout=2.0)
+    opt = SGD(model.parameters(), lr=0.01, momentum=0.9)
+    model.enable_fused_sgd(opt)
+    step = TrainStep(model, opt, None, batch_shape=shape, cuda_graph=True)
+    x = torch.randn(shape).pin_memory()
+    t = torch.randint(0, 10, (16,)).pin_memory()
+    q.put((rank, "started"))
+    t0 = time.time()
+    for i in range(100000):
+        if rank == 1 and i == 5:
+            torch.cuda.synchronize()
+            os._exit(0)                       # the rank is gone: no teardown, no goodbye
+        step(x, t)
+        if i % 4 == 3:
+            step.read_loss(lag=0)
+            try:
+                model.comm.check_health()
+            except RuntimeError as e:
+                q.put((rank, "detected: " + str(e)))
+                os._exit(3)
+        if time.time() - t0 > 60:
+            q.put((rank, "no error after 60 s"))
+            os._exit(4)
+
+
+@needs2
+def test_rank_killed_mid_step_ends_the_job_with_a_diagnostic():
+    import time
+    import torch.multiprocessing as mp
+    from dpt_b200.launcher import free_port
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = free_port()
+    procs = [ctx.Process(target=_killed_rank_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    t0 = time.time()
+    procs[0].join(150)
+    took = time.time() - t0
+    alive = procs[0].is_alive()
+    msgs = []
+    while not q.empty():
+        msgs.append(q.get())
+    for p in procs:
+        if p.is_alive():
+            p.kill()
+    assert not alive, f"rank 0 still running {took:.0f} s after its peer vanished: {msgs}"
+    assert procs[1].exitcode == 0
+    detected = [m for r, m in msgs if r == 0 and m.startswith("detected")]
+    assert procs[0].exitcode == 70 or detected, (procs[0].exitcode, msgs)
+    if detected:
+        assert "rank 1" in detected[0], detected

@@ -35,12 +35,12 @@ def _close(got, ref, tol, what):
     assert err / den < tol, f"{what}: max abs err {err:.4g} vs ref max {den:.4g}"
 
 
-def _one_call(lib, shape, seed, relu, with_res):
+def _one_call(lib, shape, seed, relu, with_res, dtype=torch.bfloat16):
     g = torch.Generator(device="cuda").manual_seed(seed)
     N, H, W, Cn = shape
     M = N * H * W
-    x = (torch.randn(shape, device="cuda", generator=g) * 2 + 0.5).to(torch.bfloat16)
-    res = torch.randn(shape, device="cuda", generator=g).to(torch.bfloat16) if with_res else None
+    x = (torch.randn(shape, device="cuda", generator=g) * 2 + 0.5).to(dtype)
+    res = torch.randn(shape, device="cuda", generator=g).to(dtype) if with_res else None
     gamma = torch.rand(Cn, device="cuda", generator=g) + 0.5
     beta = torch.randn(Cn, device="cuda", generator=g)
     st = torch.cuda.current_stream().cuda_stream
@@ -91,9 +91,25 @@ def test_noalloc_bn_matches_regular_entry_point_two_calls_in_a_row():
     _one_call(lib, (8, 8, 8, 64), seed=2, relu=False, with_res=False)
 
 
+def test_noalloc_bn_follows_the_element_type_and_reaches_its_channel_limit():
+    """The entry point honours dpt_set_lowp_dtype like the regular pair (fp16 is the reference's
+    own autocast type, fp32 its non-AMP mode), and its documented maximum, 2048 channels, is a
+    size it really accepts."""
+    from dpt_b200.ops import _lib as L
+    lib = _lib()
+    try:
+        L.set_lowp_dtype(torch.float16)
+        _one_call(lib, (8, 4, 4, 128), seed=3, relu=True, with_res=True, dtype=torch.float16)
+        L.set_lowp_dtype(torch.float32)
+        _one_call(lib, (8, 4, 4, 64), seed=4, relu=True, with_res=False, dtype=torch.float32)
+    finally:
+        L.set_lowp_dtype(torch.bfloat16)
+    _one_call(lib, (4, 2, 2, 2048), seed=5, relu=False, with_res=False)
+
+
 def test_noalloc_bn_rejects_sizes_beyond_the_builtin_scratch():
     lib = _lib()
-    Cn = 8192  # > DPT_BN_NOALLOC_MAX_CHANNELS (4096)
+    Cn = 8192  # > DPT_BN_NOALLOC_MAX_CHANNELS (2048)
     x = torch.zeros((2, 1, 1, Cn), device="cuda", dtype=torch.bfloat16)
     y = torch.empty_like(x)
     v = torch.zeros(Cn, device="cuda")
