@@ -48,6 +48,8 @@ def main():
     ap.add_argument("--tail-kb", type=float, default=None)
     ap.add_argument("--oneshot-max-kb", type=float, default=None)
     ap.add_argument("--no-fused", action="store_true")
+    ap.add_argument("--strict-barriers", action="store_true",
+                    help="closing barrier in every bucket kernel (default: only in the last)")
     ap.add_argument("--tag", default="")
     a = ap.parse_args()
 
@@ -80,6 +82,8 @@ def main():
             ddp.enable_fused_sgd(opt)
         if ddp is not None and local_only:
             ddp.reducer.set_local_only(True)
+        if ddp is not None and a.strict_barriers:
+            ddp.reducer.set_relaxed_barriers(False)
         step = TrainStep(model, opt, None, batch_shape=shape, cuda_graph=True,
                          trace_records=4096 if trace else 0)
         step.x.copy_(x)

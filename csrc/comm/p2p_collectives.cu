@@ -131,9 +131,16 @@ struct Epilogue {
     float* param_mc;
     __nv_bfloat16* shadow_mc;
     int shadow_f16;  // 16-bit shadow format: 0 = bf16, 1 = fp16
+    // 1 = leave without the closing cross-GPU barrier.  Legal for every bucket kernel of a step
+    // but the last: buckets are disjoint, and the opening barrier of the NEXT collective on the
+    // same stream makes this kernel's peer stores visible (a rank only arrives there after this
+    // kernel completed); only the step's final collective has to prove that everything landed
+    // before the step's consumers (next forward, next gradient memset) run.
+    int skip_closing_barrier;
 };
 
 static int g_comm_shadow_f16 = 0;
+static thread_local int g_skip_closing_next = 0;   // consumed by the next fused all-reduce launch
 __device__ __forceinline__ uint32_t comm_pack_lp2(float a, float b, int f16) {
     if (f16) {
         __half2 h = __floats2half2_rn(a, b);
@@ -258,6 +265,11 @@ allreduce_twoshot_kernel(CommCtx c, Peers grads, long long n4, Epilogue ep) {
     if (ep.found_inf[0] != nullptr && __any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) {
 #pragma unroll
         for (int p = 0; p < WORLD; ++p) *ep.found_inf[p] = 1.f;
+    }
+    if (ep.skip_closing_barrier) {
+        tr.mark(3);
+        if (threadIdx.x == 0) c.epoch[blockIdx.x] = e0 + 1;
+        return;
     }
     xgpu_barrier(c, e0 + 2);  // all slices have landed everywhere
     tr.mark(3);
@@ -386,6 +398,11 @@ allreduce_nvls_kernel(CommCtx c, float* __restrict__ mc, long long n4, Epilogue 
     }
     if (ep.found_inf[0] != nullptr && __any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) {
         for (int p = 0; p < c.world; ++p) *ep.found_inf[p] = 1.f;
+    }
+    if (ep.skip_closing_barrier) {
+        tr.mark(3);
+        if (threadIdx.x == 0) c.epoch[blockIdx.x] = e0 + 1;
+        return;
     }
     xgpu_barrier(c, e0 + 2);
     tr.mark(3);
@@ -613,6 +630,8 @@ static void fill_epilogue(Epilogue* ep, int world, float scale, const float* inv
                           void* const* found_inf) {
     memset(ep, 0, sizeof(*ep));
     ep->shadow_f16 = g_comm_shadow_f16;
+    ep->skip_closing_barrier = g_skip_closing_next;
+    g_skip_closing_next = 0;
     ep->scale = scale;
     ep->inv_scale = inv_scale;
     if (found_inf != nullptr)
@@ -789,6 +808,15 @@ extern "C" int dpt_allreduce_oneshot_push(dpt_comm* c, float* grads, void* const
     }
 #undef DPT_OS_PUSH
     return static_cast<int>(cudaGetLastError());
+}
+
+// The next dpt_allreduce_fused* / dpt_allreduce_nvls* launch from this thread leaves without its
+// closing barrier (see Epilogue::skip_closing_barrier).  Only for a collective that is followed,
+// on the same stream and on every rank, by another collective of this communicator before
+// anything consumes its result; the gradient reducer uses it for all buckets but the last.
+extern "C" int dpt_comm_skip_closing_barrier_next(void) {
+    g_skip_closing_next = 1;
+    return 0;
 }
 
 // Timeline buffer for the step-trace tool: `buf` = device memory of (1 + records) * 32 bytes that

@@ -90,6 +90,7 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
         .def("set_mc_push", &Reducer::set_mc_push)
         .def("set_oneshot", &Reducer::set_oneshot)
         .def("set_local_only", &Reducer::set_local_only)
+        .def("set_relaxed_barriers", &Reducer::set_relaxed_barriers)
         .def("bucket_algos", &Reducer::bucket_algos)
         .def("prepare_for_backward", &Reducer::prepare_for_backward)
         .def("mark_ready", &Reducer::mark_ready)

@@ -205,6 +205,10 @@ void Reducer::launch_bucket(int b, cudaStream_t compute) {
         }
     }
     const bool fuse = fusion_.enabled && world_ > 1;
+    // every bucket kernel but the step's last leaves without its closing barrier: the next
+    // bucket's opening barrier covers its peer stores (dptb200.h)
+    if (relaxed_barriers_ && world_ > 1 && b + 1 < static_cast<int>(buckets_.size()))
+        dpt_comm_skip_closing_barrier_next();
     if (algo == 2) {
         const int me = rank_;
         int rc2 = dpt_allreduce_nvls_sgd(

@@ -96,6 +96,8 @@ class Reducer {
     // any cross-GPU traffic or waiting, on the same GPU, under the same graph.  The difference to
     // the real step is the exposed gradient-sync time.
     void set_local_only(bool on) { local_only_ = on; }
+    // closing barrier only in the last bucket kernel of a step (default on)
+    void set_relaxed_barriers(bool on) { relaxed_barriers_ = on; }
     // 0 two-shot, 1 one-shot push, 2 NVLS, 3 two-shot + multicast publish (per bucket, as planned)
     std::vector<int> bucket_algos() const;
 
@@ -143,6 +145,7 @@ class Reducer {
     int64_t os_cap_ = 0, os_max_bytes_ = 0;
     int os_ctas_ = 0;
     bool local_only_ = false;
+    bool relaxed_barriers_ = true;
     int algo_for(const BucketSpec& bk) const;
 };
 

@@ -71,6 +71,7 @@ _SIGS = {
     "dpt_allreduce_oneshot_push": [vp, vp, C.POINTER(vp), i64, i64, f32, vp, vp, vp, vp, vp, f32, f32,
                                    f32, i32, i32, vp],
     "dpt_comm_set_trace": [vp, vp, i32],
+    "dpt_comm_skip_closing_barrier_next": [],
     "dpt_trace_stamp": [vp, i32, i32, vp],
     "dpt_allreduce_nvls": [vp, vp, i64, f32, vp, C.POINTER(vp), i32, vp],
     "dpt_allreduce_nvls_sgd": [vp, vp, i64, f32, vp, C.POINTER(vp), vp, vp, vp, vp, f32, f32, f32, i32,

@@ -183,6 +183,13 @@ int dpt_allreduce_fused_mcpush(dpt_comm* c, void* const* bufs, long long n, floa
                                float lr, float mu, float wd, int nesterov, int ctas, void* stream);
 int dpt_allreduce_oneshot(dpt_comm* c, void* const* in, float* out, long long n, float scale,
                           const float* inv_scale, void* const* found_inf, int ctas, void* stream);
+/* The next dpt_allreduce_fused* / dpt_allreduce_nvls* launch made by this thread returns without
+ * its closing cross-GPU barrier.  Legal only when another collective of the same communicator
+ * follows on the same stream on every rank before the result is consumed (its opening barrier
+ * then covers this kernel's peer stores); the reducer uses it for every bucket but the last.
+ * (NCCL pipelines successive all-reduces of a stream the same way under torch DDP,
+ * train_ddp.py:305-310.) */
+int dpt_comm_skip_closing_barrier_next(void);
 /* One-shot "push" all-reduce for small buckets (the exposed tail of backward): every rank stores
  * its n floats into slot [rank] of every peer's staging area (`staging[r]` = rank r's area of
  * 2 * world * cap floats in symmetric memory, double buffered), one cross-GPU barrier, then every

@@ -287,11 +287,13 @@ def _ddp_worker(rank, world):
     from dpt_b200.parallel.ddp import DistributedDataParallel as OurDDP
     dev = torch.device("cuda", rank)
     torch.manual_seed(100 + rank)
-    # IEEE fp32 convolutions: with TF32 a 1e-7 weight difference (cuDNN picks differently
-    # rounded kernels for differently aligned weights) can flip a TF32 rounding and the
-    # random-init net amplifies that to O(0.1) gradient differences within two steps
+    # IEEE fp32 + deterministic cuDNN algorithms on both sides: the two runs then differ only in
+    # the gradient reduction order (none at world 2: a + b is commutative and 1/2 is exact) and in
+    # the optimizer's rounding (fused multiply-add vs torch's separate foreach ops)
     torch.backends.cudnn.allow_tf32 = False
     torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.deterministic = True
+    torch.backends.cudnn.benchmark = False
     base = resnet18(10).to(dev)
     base.native = "never"        # same ATen model math on both sides: isolates the gradient path
     ours = OurDDP(copy.deepcopy(base), device_ids=[rank], backend="native", profile=True)
@@ -304,6 +306,7 @@ def _ddp_worker(rank, world):
     opt_o = SGD(ours.parameters(), lr=0.002, momentum=0.9, weight_decay=5e-4)
     opt_r = torch.optim.SGD(ref.parameters(), lr=0.002, momentum=0.9, weight_decay=5e-4)
     g = torch.Generator(device=dev).manual_seed(7 + rank)
+    init = {n: p.detach().clone() for n, p in ref.module.named_parameters()}   # rank 0's weights
     for it in range(4):
         x = torch.randn(16, 3, 32, 32, device=dev, generator=g)
         t = torch.randint(0, 10, (16,), device=dev, generator=g)
@@ -311,21 +314,29 @@ def _ddp_worker(rank, world):
             opt.zero_grad(set_to_none=True)
             F.cross_entropy(model(x), t).backward()
             if it == 0 and model is ref:
-                # averaged gradients of the first step: only the reduction order differs
+                # averaged gradients of the first step (identical weights): only the reduction
+                # order differs — exact at world 2, a few ulp beyond
                 torch.cuda.synchronize()
+                tol0 = 1e-6 if world == 2 else 2e-5
                 for (n, a), b in zip(ours.module.named_parameters(), ref.module.parameters()):
                     err = (a.grad - b.grad).abs().max().item()
                     den = b.grad.abs().max().item() + 1e-12
-                    assert err / den < 2e-3, f"{n}: averaged grad differs from torch DDP + NCCL ({err/den:.3g})"
+                    assert err / den <= tol0, f"{n}: averaged grad differs from torch DDP + NCCL ({err/den:.3g})"
             opt.step()
     torch.cuda.synchronize()
     ours.comm.check_health()
+    worst = 0.0
     for (n, a), b in zip(ours.module.named_parameters(), ref.module.parameters()):
-        # TF32 cuDNN kernels are not run-to-run deterministic; trajectories stay parallel
-        c = torch.nn.functional.cosine_similarity(a.flatten(), b.flatten(), dim=0).item()
-        assert c > 0.999, f"{n} diverged from torch DDP + NCCL (cos {c:.6f})"
+        # absolute agreement after 4 optimizer steps, measured against the size of the UPDATE
+        # (so zero-initialised biases are judged as strictly as the weights)
+        upd = (b - init[n]).norm().item()
+        rel = (a - b).norm().item() / (upd + 1e-12)
+        worst = max(worst, rel)
+        assert rel < 2e-2, f"{n}: update differs from torch DDP + NCCL after 4 steps (rel {rel:.3g})"
+    if rank == 0:
+        print(f"[ddp parity] worst per-tensor error relative to the 4-step update: {worst:.3g}")
     for (n, a), b in zip(ours.module.named_buffers(), ref.module.buffers()):
-        assert torch.allclose(a.float(), b.float(), atol=5e-3, rtol=5e-2), f"buffer {n}"
+        assert torch.allclose(a.float(), b.float(), atol=1e-4, rtol=1e-3), f"buffer {n}"
     t = ours.sync_timings()
     assert len(t["buckets"]) == len(ours.plans) and all(b["end_ms"] >= b["start_ms"] for b in t["buckets"])
     assert ours.reducer.launches() == 4 * len(ours.plans)
@@ -371,13 +382,17 @@ def _trainstep_worker(rank, world):
         scaler = GradScaler(device=dev, init_scale=256.0, enabled=fp16_scaler)
         step = TrainStep(model, opt, scaler, batch_shape=shape, cuda_graph=graph)
         losses = []
-        for _ in range(steps):
+        first = None
+        for i in range(steps):
             step(x, t)
             losses.append(step.read_loss(lag=0))
+            if i == 0:
+                torch.cuda.synchronize()
+                first = (model.arena.param - init).clone()   # the update of step 1
         torch.cuda.synchronize()
-        return model, opt, scaler, init, losses
+        return model, opt, scaler, init, losses, first
 
-    oracle, _, _, init0, losses0 = run("nccl", False, False, False, "auto")
+    oracle, _, _, init0, losses0, first0 = run("nccl", False, False, False, "auto")
     delta0 = (oracle.arena.param - init0).clone()
     assert losses0[-1] < losses0[0], losses0
     slices = []
@@ -389,6 +404,27 @@ def _trainstep_worker(rank, world):
             if hi - lo >= 256:
                 slices.append((pl["offset"] + lo, pl["offset"] + hi))
 
+    def slice_err(a, b):
+        worst = 0.0
+        for lo, hi in slices:
+            den = b[lo:hi].norm().item()
+            if den > 1e-7:
+                worst = max(worst, (a[lo:hi] - b[lo:hi]).norm().item() / den)
+        return worst
+
+    # noise floor: the oracle against itself (atomics order in the native model kernels)
+    oracle2, _, _, _, _, first0b = run("nccl", False, False, False, "auto")
+    floor1 = slice_err(first0b, first0)
+    floor6 = slice_err(oracle2.arena.param - init0, delta0)
+    oracle2.shutdown()
+    # (random-init bf16 ResNet on noise: the model's own gradient varies by tens of percent from
+    # run to run in the worst slice, so this check only catches O(1) errors such as a dropped
+    # slice; test_reducer_paths_are_exact below pins the gradient path to 1e-6)
+    tol1 = max(0.05, 4.0 * floor1)
+    if rank == 0:
+        print(f"[trainstep] run-to-run noise of the NCCL oracle: step-1 update {floor1:.4f}, "
+              f"{steps}-step update {floor6:.4f} (worst slice, relative)")
+
     configs = [(False, False, False, "auto"), (True, False, False, "twoshot"),
                (True, True, False, "twoshot"), (True, True, False, "auto"),
                (True, True, False, "oneshot"), (True, False, True, "auto"),
@@ -398,7 +434,7 @@ def _trainstep_worker(rank, world):
         res = run("native", graph, fused, fp16_scaler, algo)
         if res is None:
             continue
-        model, opt, scaler, init, losses = res
+        model, opt, scaler, init, losses, first = res
         tag = f"graph={graph} fused={fused} scaler={fp16_scaler} algo={algo} -> {model.bucket_algorithms()}"
         model.comm.check_health()
         assert torch.equal(init, init0), "construction broadcast differs between backends"
@@ -407,15 +443,17 @@ def _trainstep_worker(rank, world):
         assert model.verify_replicas()                 # bit-exact parameter digest, all ranks
         ep = model.comm.validate_epochs()              # same collectives issued everywhere
         assert max(ep) > 0
-        delta = model.arena.param - init
-        worst = 0.0
+        # step 1 (same weights, same batch on both sides): every rank-slice of every bucket must
+        # carry the oracle's update — a dropped slice or a wrong scale is an O(1) error here
         for lo, hi in slices:
-            den = delta0[lo:hi].norm().item()
-            if den < 1e-6:
+            den = first0[lo:hi].norm().item()
+            if den < 1e-7:
                 continue
-            rel = (delta[lo:hi] - delta0[lo:hi]).norm().item() / den
-            worst = max(worst, rel)
-            assert rel < 0.08, f"{tag}: update of arena[{lo}:{hi}] differs from the NCCL oracle by {rel:.3f}"
+            rel = (first[lo:hi] - first0[lo:hi]).norm().item() / den
+            assert rel < tol1, f"{tag}: step-1 update of arena[{lo}:{hi}] differs from the NCCL oracle by {rel:.4f}"
+        worst = slice_err(first, first0)
+        worst6 = slice_err(model.arena.param - init, delta0)
+        cos = torch.nn.functional.cosine_similarity(model.arena.param - init, delta0, dim=0).item()
         shc = model.arena.shadow.double().sum().reshape(1)
         lo2, hi2 = shc.clone(), shc.clone()
         dist.all_reduce(lo2, op=dist.ReduceOp.MIN)
@@ -427,8 +465,8 @@ def _trainstep_worker(rank, world):
         if algo == "auto":
             assert model.bucket_algorithms()[-1] == "oneshot" and model.plans[-1]["bytes"] <= 65536
         if rank == 0:
-            print(f"[trainstep] {tag}: final loss {losses[-1]:.4f} (oracle {losses0[-1]:.4f}), "
-                  f"worst slice update error {worst:.4f}")
+            print(f"[trainstep] {tag}: final loss {losses[-1]:.4f} (oracle {losses0[-1]:.4f}), worst slice "
+                  f"error step 1 {worst:.4f} / step {steps} {worst6:.4f}, cos {cos:.5f}")
         model.shutdown()
     oracle.shutdown()
 
@@ -436,6 +474,86 @@ def _trainstep_worker(rank, world):
 @needs2
 def test_trainstep_under_native_ddp_graph_and_fused_optimizer():
     _run(_trainstep_worker)
+
+
+# --------------------------------------------------------------------------------- exact reducer
+def _reducer_exact_worker(rank, world):
+    """The whole native gradient path with KNOWN gradients: the arena is filled with per-rank
+    random values, every parameter is reported ready in arena order (what the engine does), and
+    the result is compared element by element with NCCL all-reduce / world (+ torch.optim.SGD for
+    the fused update).  Covers every bucket algorithm, the tail bucket, the relaxed closing
+    barriers and the momentum shards; tolerance 1e-6 relative."""
+    import torch.distributed as dist
+    from dpt_b200.models.resnet import build_model
+    from dpt_b200.optim import SGD
+    from dpt_b200.parallel.ddp import DistributedDataParallel as OurDDP
+    dev = torch.device("cuda", rank)
+    configs = [("auto", False), ("auto", True), ("twoshot", False), ("twoshot", True),
+               ("oneshot", True), ("nvls", False), ("nvls", True), ("twoshot_mc", True)]
+    for algo, fused in configs:
+        torch.manual_seed(50 + rank)
+        model = OurDDP(build_model(dev, "resnet18", 10), device_ids=[rank], backend="native",
+                       allreduce_algo=algo, bucket_cap_mb=2)
+        if algo in ("nvls", "twoshot_mc") and not getattr(model, "nvls", False):
+            model.shutdown()
+            continue
+        arena = model.arena
+        opt = SGD(model.parameters(), lr=0.05, momentum=0.9, weight_decay=1e-3)
+        if fused:
+            assert model.enable_fused_sgd(opt)
+        ref_p = torch.nn.Parameter(arena.param.clone())
+        ref_opt = torch.optim.SGD([ref_p], lr=0.05, momentum=0.9, weight_decay=1e-3)
+        order = list(arena.order)
+        tag = f"algo={algo} fused={fused} -> {model.bucket_algorithms()}"
+        for it in range(3):
+            g = torch.randn(arena.numel, device=dev,
+                            generator=torch.Generator(device=dev).manual_seed(1000 * it + rank))
+            ref = g.clone()
+            dist.all_reduce(ref)
+            ref /= world
+            arena.grad.copy_(g)
+            torch.cuda.synchronize()
+            dist.barrier()
+            model.prepare_for_backward()
+            for p in order:
+                model._sink([p])
+            assert model.finalize_backward() == len(model.plans)
+            if not fused:
+                torch.cuda.synchronize()
+                # padding between parameters is not reduced: compare parameter slots only
+                for pl in model.plans:
+                    a, b = pl["offset"], pl["offset"] + pl["numel"]
+                    err = (arena.grad[a:b] - ref[a:b]).abs().max().item()
+                    assert err <= 1e-6 * max(1.0, ref[a:b].abs().max().item()), (tag, it, a, err)
+                opt.step()
+            ref_p.grad = ref
+            ref_opt.step()
+            torch.cuda.synchronize()
+            for pl in model.plans:
+                a, b = pl["offset"], pl["offset"] + pl["numel"]
+                err = (arena.param[a:b] - ref_p.data[a:b]).abs().max().item()
+                assert err <= 2e-6 * max(1.0, ref_p.data[a:b].abs().max().item()), \
+                    f"{tag}: step {it}: parameters of bucket at {a} differ from all-reduce + SGD by {err:.3g}"
+            assert torch.equal(arena.shadow, arena.param.bfloat16()), (tag, "shadow != bf16(param)")
+            assert model.verify_replicas()
+        # momentum: complete after the shard gather, equal to torch's buffer
+        model.gather_optimizer_state(opt)
+        m = opt._flat_momentum()
+        mref = ref_opt.state[ref_p]["momentum_buffer"]
+        for pl in model.plans:
+            a, b = pl["offset"], pl["offset"] + pl["numel"]
+            err = (m[a:b] - mref[a:b]).abs().max().item()
+            assert err <= 2e-6 * max(1.0, mref[a:b].abs().max().item()), (tag, "momentum", a, err)
+        model.comm.check_health()
+        model.comm.validate_epochs()
+        if rank == 0:
+            print(f"[reducer exact] {tag}: ok")
+        model.shutdown()
+
+
+@needs2
+def test_reducer_paths_are_exact():
+    _run(_reducer_exact_worker)
 
 
 # --------------------------------------------------------------------------------- fault path
