@@ -301,7 +301,7 @@ def run_ours(a):
     if ddp is not None:
         res["config"]["bucket_algorithms"] = ddp.bucket_algorithms()
         if not a.no_extras:
-            attempt("multi_gpu_checks", lambda: multi_gpu_checks(ddp, device))
+            attempt("multi_gpu_checks", lambda: multi_gpu_checks(ddp, device, opt))
         ddp.shutdown()
     del step
     if not a.no_extras and a.amp_dtype == "bf16":
@@ -314,7 +314,7 @@ def run_ours(a):
 
 
 # ------------------------------------------------------------------------ correctness evidence
-def multi_gpu_checks(ddp, device) -> dict:
+def multi_gpu_checks(ddp, device, optimizer=None) -> dict:
     """Cold-path proof, printed with the bench line, that the native gradient path reduces
     CORRECTLY (the scaling run is the only multi-GPU run the driver does): replicas bit-identical,
     every rank issued the same collectives, and a real bucket all-reduced by each native kernel
@@ -363,6 +363,45 @@ def multi_gpu_checks(ddp, device) -> dict:
         errs[name] = {"bytes": n * 4, "max_abs_err_vs_nccl": float(err.item())}
         view.zero_()
     out["allreduce_vs_nccl"] = errs
+    # the REAL step-time gradient path (reducer -> per-bucket kernels with the fused SGD update,
+    # whatever algorithm each bucket uses by default) on known gradients, against NCCL all-reduce
+    # + the SGD formula; parameters / momentum / shadow are restored afterwards
+    if optimizer is not None and getattr(ddp, "_fusion_cfg", None) is not None:
+        g0 = optimizer.param_groups[0]
+        arena = ddp.arena
+        m = optimizer._flat_momentum()
+        snap_p, snap_m = arena.param.clone(), m.clone()
+        m.zero_()
+        x = torch.randn(arena.numel, device=device, generator=gen)
+        ref = x.clone()
+        dist.all_reduce(ref)
+        ref /= world
+        arena.grad.copy_(x)
+        torch.cuda.synchronize()
+        dist.barrier()
+        ddp.prepare_for_backward()
+        for p in list(arena.order):
+            ddp._sink([p])
+        ddp.finalize_backward()
+        torch.cuda.synchronize()
+        expect = snap_p - g0["lr"] * (ref + g0["weight_decay"] * snap_p)   # first step: m = d
+        worst = 0.0
+        for pl in ddp.plans:
+            a, b = pl["offset"], pl["offset"] + pl["numel"]
+            worst = max(worst, (arena.param[a:b] - expect[a:b]).abs().max().item())
+        shadow_ok = bool(torch.equal(arena.shadow, arena.param.to(arena.shadow.dtype)))
+        t = torch.tensor([worst, 0.0 if shadow_ok else 1.0], device=device, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        out["fused_update_path"] = {"bucket_algorithms": ddp.bucket_algorithms(),
+                                    "param_max_abs_err_vs_nccl_plus_sgd": float(t[0].item()),
+                                    "shadow_equals_cast_of_param": bool(t[1].item() == 0.0),
+                                    "replicas_bit_identical_after": bool(ddp.verify_replicas(False))}
+        arena.param.copy_(snap_p)
+        m.copy_(snap_m)
+        arena.grad.zero_()
+        arena.refresh_shadow()
+        torch.cuda.synchronize()
+        dist.barrier()
     ddp.comm.check_health()
     return out
 

@@ -23,8 +23,11 @@ def _init(rank, world, port):
                        "WORLD_SIZE": str(world), "LOCAL_RANK": str(rank)})
     sys.path.insert(0, ROOT)
     torch.cuda.set_device(rank)
+    import datetime
+    # a rank that fails an assertion leaves the others inside a collective: keep that wait short
     dist.init_process_group("nccl", rank=rank, world_size=world,
-                            device_id=torch.device("cuda", rank))
+                            device_id=torch.device("cuda", rank),
+                            timeout=datetime.timedelta(seconds=120))
 
 
 def _run(worker, world=None):
@@ -37,13 +40,52 @@ def _run(worker, world=None):
     procs = [ctx.Process(target=_guard, args=(worker, r, world, port, q)) for r in range(world)]
     for p in procs:
         p.start()
+    import queue as _queue
+    import time
     results = []
-    for _ in procs:
-        results.append(q.get(timeout=900))
+    deadline = time.time() + 600          # whole test
+    failed_at = None
+    while len(results) < world and time.time() < deadline:
+        try:
+            results.append(q.get(timeout=2.0))
+        except _queue.Empty:
+            if all(not p.is_alive() for p in procs) and q.empty():
+                break
+            # once one rank has failed the others are usually stuck in a collective with it:
+            # give them 30 s, then stop the test instead of sitting out a communicator timeout
+            if failed_at is not None and time.time() - failed_at > 30:
+                break
+            continue
+        if results[-1][1] != "ok" and failed_at is None:
+            failed_at = time.time()
     for p in procs:
-        p.join(120)
-    for rank, msg in results:
-        assert msg == "ok", f"rank {rank}:\n{msg}"
+        p.join(5 if failed_at is not None else 60)
+    for p in procs:
+        if p.is_alive():
+            p.kill()
+    bad = [(r, m) for r, m in results if m != "ok"]
+    assert not bad, "\n".join(f"rank {r}:\n{m}" for r, m in bad[:2])
+    assert len(results) == world, f"only {len(results)} of {world} ranks reported (hung or died)"
+
+
+def _rank_mean(values):
+    """Element-wise mean over ranks of a list of floats (collective)."""
+    import torch.distributed as dist
+    t = torch.tensor(values, device="cuda", dtype=torch.float64)
+    dist.all_reduce(t)
+    return (t / dist.get_world_size()).tolist()
+
+
+def _agree(ok: bool, msg: str = "") -> None:
+    """Collective assertion: every rank calls it with its local verdict; if ANY rank failed, all
+    ranks raise.  Conditions on rank-local data (each rank trains on its own batch) must go
+    through this — a plain assert that fails on one rank only leaves the others waiting for it
+    in the next collective."""
+    import torch.distributed as dist
+    flag = torch.tensor([0 if ok else 1], device="cuda", dtype=torch.int32)
+    dist.all_reduce(flag, op=dist.ReduceOp.MAX)
+    if int(flag.item()) != 0:
+        raise AssertionError(msg if not ok else "another rank failed: " + msg.split(":")[0])
 
 
 def _guard(worker, rank, world, port, q):
@@ -390,7 +432,9 @@ def _trainstep_worker(rank, world):
                 torch.cuda.synchronize()
                 first = (model.arena.param - init).clone()   # the update of step 1
         torch.cuda.synchronize()
-        return model, opt, scaler, init, losses, first
+        # every rank trains on its own batch: judge the loss curve averaged over ranks, so all
+        # ranks reach the same verdict
+        return model, opt, scaler, init, _rank_mean(losses), first
 
     oracle, _, _, init0, losses0, first0 = run("nccl", False, False, False, "auto")
     delta0 = (oracle.arena.param - init0).clone()
@@ -679,6 +723,7 @@ def _compat_loop_worker(rank, world):
         losses.append(loss.item())
     torch.cuda.synchronize()
     model.comm.check_health()
+    losses = _rank_mean(losses)           # same verdict on every rank
     assert losses[-1] < losses[0], losses
     cs = model.arena.param.double().sum().reshape(1)
     lo, hi = cs.clone(), cs.clone()
