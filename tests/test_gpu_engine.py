@@ -77,10 +77,25 @@ def _engine_matches_torch_fp32(arch, bs, img, ncls):
         # bf16 activations put both implementations ~0.9-0.99 from the fp32 gradient on this
         # tiny-batch net; ours must be as close to fp32 as torch's bf16 path is
         assert c > min(0.95, c_torch_bf16 - 0.04), f"{n}: grad cosine {c:.4f} (torch bf16 {c_torch_bf16:.4f})"
+        # cosine is blind to a whole-tensor scale error (a wrong 1/M, a missing loss-scale
+        # factor): the gradient NORM must match fp32 too, as well as torch's own bf16 path does
+        ratio = p.grad.float().norm().item() / (q.grad.float().norm().item() + 1e-20)
+        ratio_torch = r.grad.float().norm().item() / (q.grad.float().norm().item() + 1e-20)
+        slack = 0.10 + 2.0 * abs(ratio_torch - 1.0)
+        assert abs(ratio - 1.0) < slack, \
+            f"{n}: |grad| / |fp32 grad| = {ratio:.4f} (torch bf16: {ratio_torch:.4f})"
+    g_all = torch.cat([p.grad.float().flatten() for p in model.parameters()])
+    q_all = torch.cat([q.grad.float().flatten() for q in ref.parameters()])
+    c_all = torch.cat([r.grad.float().flatten() for r in cal.parameters()])
+    tot, tot_torch = (g_all.norm() / q_all.norm()).item(), (c_all.norm() / q_all.norm()).item()
+    assert abs(tot - 1.0) < 0.05 + 2.0 * abs(tot_torch - 1.0), (tot, tot_torch)
     # running statistics follow the same momentum update
     for (n, b), br in zip(model.named_buffers(), ref.named_buffers()):
         if "running" in n:
             assert _cos(b, br[1]) > 0.99, n
+            if "running_var" in n:      # a scale error (wrong 1/M, missing unbias) shows here
+                rr = b.float().norm().item() / br[1].float().norm().item()
+                assert abs(rr - 1.0) < 0.02, f"{n}: norm ratio {rr:.4f}"
         elif "num_batches" in n:
             assert int(b) == int(br[1]) == 1
 

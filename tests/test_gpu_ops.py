@@ -37,6 +37,33 @@ def test_bn_train_fwd_bwd_large(shape, relu, res):
     _bn_train_fwd_bwd(shape, relu, res)
 
 
+def test_bn_statistics_with_mean_much_larger_than_std():
+    """Batch statistics are accumulated as sum / sum of squares in fp32 (not Welford like
+    torch): check the cancellation in E[x^2] - E[x]^2 where it matters for this framework's
+    inputs — bf16 activations with |mean| = 10 std (at |mean| = 100 std bf16 itself cannot
+    represent the data: its spacing there is half a standard deviation)."""
+    Fn = _F()
+    shape = (64, 8, 8, 64)
+    C = shape[-1]
+    g = torch.Generator(device="cuda").manual_seed(9)
+    x = (torch.randn(shape, device="cuda", generator=g) + 10.0).to(torch.bfloat16)
+    ssum = torch.zeros(C, device="cuda")
+    ssq = torch.zeros(C, device="cuda")
+    Fn.bn_stats(x, ssum, ssq)
+    gamma = torch.ones(C, device="cuda")
+    beta = torch.zeros(C, device="cuda")
+    rm, rv = torch.zeros(C, device="cuda"), torch.ones(C, device="cuda")
+    y, mean, invstd = Fn.bn_fwd_train(x, ssum, ssq, gamma, beta, running_mean=rm, running_var=rv)
+    xf = x.float().view(-1, C)
+    torch.cuda.synchronize()
+    assert torch.allclose(mean, xf.mean(0), rtol=1e-5, atol=1e-4)
+    var_ref = xf.var(0, unbiased=False)
+    var = 1.0 / invstd.square() - 1e-5
+    assert torch.allclose(var, var_ref, rtol=2e-3), ((var - var_ref).abs().max().item())
+    ref = (xf - xf.mean(0)) * (var_ref + 1e-5).rsqrt()
+    _close(y.view(-1, C), ref, 1.5e-2, "normalised output at mean = 10 std")
+
+
 def _bn_train_fwd_bwd(shape, relu, res):
     Fn = _F()
     N, H, W, C = shape
