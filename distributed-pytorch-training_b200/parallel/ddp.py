@@ -416,16 +416,25 @@ class DistributedDataParallel(nn.Module):
 
     def gather_optimizer_state(self, optimizer) -> None:
         """Collective (all ranks): make every rank's flat momentum complete.  Cold path (before a
-        checkpoint): foreign shards are zeroed and one SUM all-reduce over the bootstrap process
-        group fills them with their owners' values (x + 0 + ... + 0 is exact)."""
+        checkpoint): every element keeps exactly one contributor — its shard's owner, or rank 0
+        for replicated regions — and one SUM all-reduce over the bootstrap process group puts the
+        owners' values everywhere (x + 0 + ... + 0 is exact)."""
         shards = self.momentum_shards()
         if not shards or not hasattr(optimizer, "_flat_momentum"):
             return
         m = optimizer._flat_momentum()
         torch.cuda.current_stream().synchronize()
-        for lo, hi, owner in shards:
-            if owner != self.rank:
-                m[lo:hi].zero_()
+        if self.rank == 0:
+            # rank 0 contributes its own shards and everything that is replicated (one-shot
+            # buckets are updated in full on every rank; padding)
+            for lo, hi, owner in shards:
+                if owner != 0:
+                    m[lo:hi].zero_()
+        else:
+            keep = [(lo, hi, m[lo:hi].clone()) for lo, hi, owner in shards if owner == self.rank]
+            m.zero_()
+            for lo, hi, t in keep:
+                m[lo:hi].copy_(t)
         dist.all_reduce(m, group=self.process_group)
         torch.cuda.current_stream().synchronize()
 
