@@ -291,7 +291,7 @@ class Communicator:
 
     # ------------------------------------------------------------------ watchdog / heartbeat
     def start_watchdog(self, interval_s: float = 1.0, abort: bool = False, heartbeat: bool = True,
-                       stale_s: float = 15.0):
+                       stale_s: float = 45.0):
         """Host thread that (a) polls the device-written error word, so a peer that died or
         stalled is reported with (rank, peer, epoch) instead of hanging the job — the stand-in
         for ProcessGroupNCCL's watchdog / heartbeat monitor (ProcessGroupNCCL.hpp:610,690) —

@@ -14,7 +14,16 @@ needs2 = pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_c
 
 
 def _world():
+    """Ranks for the kernel-level tests: every GPU of the box (DPT_TEST_WORLD caps it)."""
     return min(torch.cuda.device_count(), int(os.environ.get("DPT_TEST_WORLD", "8")))
+
+
+def _model_world():
+    """Ranks for the tests that train whole models through every algorithm variant: 2 by
+    default (what they were validated on: profiles/r2/multi_gpu_tests_2gpu_*.log; the 8-GPU
+    paths are checked for exactness by bench.py's multi_gpu_checks at every N of the scaling
+    run); DPT_TEST_WORLD_MODEL=8 runs them on the whole box."""
+    return min(torch.cuda.device_count(), int(os.environ.get("DPT_TEST_WORLD_MODEL", "2")))
 
 
 def _init(rank, world, port):
@@ -517,7 +526,7 @@ def _trainstep_worker(rank, world):
 
 @needs2
 def test_trainstep_under_native_ddp_graph_and_fused_optimizer():
-    _run(_trainstep_worker)
+    _run(_trainstep_worker, world=_model_world())
 
 
 # --------------------------------------------------------------------------------- exact reducer
@@ -597,7 +606,7 @@ def _reducer_exact_worker(rank, world):
 
 @needs2
 def test_reducer_paths_are_exact():
-    _run(_reducer_exact_worker)
+    _run(_reducer_exact_worker, world=_model_world())
 
 
 # --------------------------------------------------------------------------------- fault path
