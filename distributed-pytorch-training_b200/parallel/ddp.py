@@ -27,6 +27,7 @@ import torch.distributed as dist
 import torch.nn as nn
 
 from .arena import ParamArena
+from . import tuning
 from .bucket import ext, ext_available, plan_arena_buckets
 
 
@@ -151,7 +152,7 @@ class DistributedDataParallel(nn.Module):
                  gradient_as_bucket_view=True, static_graph=True, *, backend: str = "native",
                  comm=None, fused_optimizer=False, profile=False, comm_ctas: int = 0,
                  comm_timeout: float = 30.0, first_bucket_mb: float = 1.0,
-                 allreduce_algo: str = "auto", nvls_min_bytes: int = 1 << 20,
+                 allreduce_algo: str = "auto", nvls_min_bytes: int = tuning.NVLS_MIN_BYTES,
                  tail_bucket_kb: float | None = None, oneshot_max_kb: float | None = None,
                  watchdog: bool = True):
         super().__init__()
@@ -186,16 +187,16 @@ class DistributedDataParallel(nn.Module):
         # kernel costs ~15 us to launch and NVSwitch bandwidth does not depend on message count, so
         # the native backend defaults to 4 MiB: the last bucket (the exposed tail of backward) is
         # then ~1-2 MB instead of ~9 MB for ResNet-18.
-        default_cap = 4 if backend == "native" else 25
+        default_cap = tuning.NATIVE_BUCKET_CAP_MB if backend == "native" else tuning.TORCH_BUCKET_CAP_MB
         self.bucket_bytes_cap = int((bucket_cap_mb if bucket_cap_mb is not None else default_cap) * 1024 * 1024)
         self.first_bucket_bytes = int(first_bucket_mb * 1024 * 1024)
         # the last-ready gradients (the stem) form a bucket of their own, small enough for the
         # one-barrier one-shot kernel: only that kernel trails the last backward kernel
         if tail_bucket_kb is None:
-            tail_bucket_kb = 64.0 if backend == "native" else 0.0
+            tail_bucket_kb = tuning.TAIL_BUCKET_BYTES / 1024 if backend == "native" else 0.0
         self.tail_bucket_bytes = int(tail_bucket_kb * 1024)
         if oneshot_max_kb is None:
-            oneshot_max_kb = 256.0
+            oneshot_max_kb = tuning.ONESHOT_MAX_BYTES / 1024      # measured crossovers: tuning.py
         if allreduce_algo == "oneshot":
             oneshot_max_kb = 1 << 30       # every bucket that fits the staging area
         elif allreduce_algo in ("twoshot", "nvls", "twoshot_mc"):
@@ -222,10 +223,10 @@ class DistributedDataParallel(nn.Module):
         # auto: with the SGD update fused, N >= 4 and multicast-bound arenas the owner publishes new
         # weights / shadow with ONE multimem.st instead of N peer stores (measured at 8 GPUs under
         # the graph: 0.712 vs 0.728 ms/step, backward 392 vs 401 us next to the bucket kernels)
-        self._mc_push_auto = allreduce_algo == "auto" and self.world_size >= 4
+        self._mc_push_auto = allreduce_algo == "auto" and self.world_size >= tuning.MC_PUBLISH_MIN_WORLD
         want_nvls = backend == "native" and self.world_size > 1 and (
             allreduce_algo in ("nvls", "autotune", "twoshot_mc")
-            or (allreduce_algo == "auto" and self.world_size >= 4))
+            or (allreduce_algo == "auto" and self.world_size >= tuning.NVLS_MIN_WORLD))
         self.arena = ParamArena(params, self.device, comm=self.comm if backend == "native" else None,
                                 multicast=want_nvls)
         self.nvls = want_nvls and hasattr(self.arena.grad_buf, "mc_ptr")

@@ -427,3 +427,24 @@ def test_tail_bucket_split_and_cli_auto_switches():
     assert parse_args(["--bucket-cap-mb", "25"]).bucket_cap_mb == 25.0
     assert parse_args(["--no-cuda-graph"]).cuda_graph is False
     assert parse_args(["--fused-optimizer"]).fused_optimizer is True
+
+
+def test_algorithm_table_for_the_default_bucket_plans():
+    """parallel/tuning.py: the per-bucket kernel choice of allreduce_algo='auto' for the two
+    reference-sized models at 2 and 8 GPUs (tail bucket one-shot, fused buckets two-shot with the
+    multicast publish from 4 GPUs, NVLS only without the fused update and from 1 MB)."""
+    from dpt_b200.models.resnet import build_model
+    from dpt_b200.parallel import tuning
+    from dpt_b200.parallel.arena import ParamArena
+    from dpt_b200.parallel.bucket import plan_arena_buckets
+    m = build_model(torch.device("cpu"), "resnet18", 10)
+    plans = plan_arena_buckets(ParamArena(list(m.named_parameters()), "cpu"), 4 << 20, 1 << 20,
+                               tuning.TAIL_BUCKET_BYTES)
+    sizes = [pl["numel"] * 4 for pl in plans]
+    pick = lambda world, fused, mc: [tuning.choose_algorithm(b, world, fused, mc) for b in sizes]  # noqa: E731
+    assert pick(2, True, True) == ["twoshot"] * 7 + ["oneshot"]
+    assert pick(8, True, True) == ["twoshot_mc"] * 7 + ["oneshot"]
+    assert pick(8, True, False) == ["twoshot"] * 7 + ["oneshot"]       # multicast not exposed
+    assert pick(8, False, True) == ["nvls"] * 7 + ["oneshot"]
+    assert pick(1, True, True) == ["none"] * 8
+    assert tuning.choose_algorithm(512 * 1024, 8, False, True) == "twoshot"   # between the thresholds

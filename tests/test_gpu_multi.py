@@ -558,6 +558,12 @@ def _reducer_exact_worker(rank, world):
         ref_opt = torch.optim.SGD([ref_p], lr=0.05, momentum=0.9, weight_decay=1e-3)
         order = list(arena.order)
         tag = f"algo={algo} fused={fused} -> {model.bucket_algorithms()}"
+        if algo == "auto":
+            # the documented decision table (parallel/tuning.py) is what the C++ reducer does
+            from dpt_b200.parallel import tuning
+            mc = bool(getattr(model, "nvls", False))
+            want = [tuning.choose_algorithm(pl["numel"] * 4, world, fused, mc) for pl in model.plans]
+            assert want == model.bucket_algorithms(), (want, model.bucket_algorithms())
         for it in range(3):
             g = torch.randn(arena.numel, device=dev,
                             generator=torch.Generator(device=dev).manual_seed(1000 * it + rank))
