@@ -503,6 +503,8 @@ class DistributedDataParallel(nn.Module):
         grad_mode = torch.is_grad_enabled() and self.module.training
         if grad_mode:
             self._iter += 1
+            if getattr(self, "_join_active", False):
+                self._join_count(1)          # see join(): shadowing ranks answer with 0
             if self.require_forward_param_sync:
                 self.sync_buffers()
             self.prepare_for_backward()
@@ -559,10 +561,62 @@ class DistributedDataParallel(nn.Module):
             self.require_backward_grad_sync = old
 
     @contextlib.contextmanager
-    def join(self, *args, **kwargs):
-        """Uneven-input join is not needed with DistributedSampler's padding; accepted for API
-        compatibility and behaves as a plain context."""
-        yield
+    def join(self, divide_by_initial_world_size: bool = True, enable: bool = True,
+             throw_on_early_termination: bool = False):
+        """Training with uneven inputs across ranks (torch distributed.py:1798, the Join
+        algorithm): every rank wraps its loop in ``with model.join():``; a rank that runs out of
+        batches keeps "shadowing" the collectives of the ranks that still train — the per-step
+        count of active ranks, the buffer broadcast and one all-reduce of zeros per bucket — so
+        nobody hangs, and gradients stay divided by the initial world size (torch's default).
+
+        Implemented for the torch.distributed reducer (``backend="gloo"|"nccl"``).  The native
+        backend plans one static step for all ranks and the DistributedSampler pads every rank to
+        the same number of batches (reference train_ddp.py:121-127), so there the context only
+        has to be accepted.  Custom communication hooks are not shadowed."""
+        if not divide_by_initial_world_size:
+            raise NotImplementedError("join(divide_by_initial_world_size=False)")
+        shadowing = enable and self.world_size > 1 and isinstance(self.reducer, _TorchReducer) \
+            and self.reducer.comm_hook is None
+        if not shadowing:
+            yield
+            return
+        self._join_active = True
+        first_iter = self._iter
+        try:
+            yield
+        finally:
+            self._join_active = False
+        my_iters = self._iter - first_iter
+        # this rank is out of inputs: shadow until every rank is
+        while True:
+            if self._join_count(0) == 0:
+                break
+            if throw_on_early_termination:
+                raise RuntimeError(f"Rank {self.rank} exhausted all inputs.")
+            if self.broadcast_buffers and self._mod_buffers:
+                dist.broadcast(self._buffer_flat, src=self._global_src(), group=self.process_group)
+            for pl in self.plans:
+                zeros = torch.zeros(pl["numel"], dtype=torch.float32, device=self.device)
+                dist.all_reduce(zeros, group=self.process_group)
+        # torch's post-hook (_sync_final_model): every rank leaves with the model of the rank that
+        # trained longest (highest rank among those), so the replicas agree again
+        counts = torch.zeros(self.world_size, dtype=torch.int64, device=self.device)
+        counts[self.rank] = my_iters
+        dist.all_reduce(counts, group=self.process_group)
+        best = int(counts.max().item())
+        src = max(r for r in range(self.world_size) if int(counts[r].item()) == best)
+        gsrc = dist.get_global_rank(self.process_group, src) if self.process_group is not None else src
+        dist.broadcast(self.arena.param, src=gsrc, group=self.process_group)
+        if self._mod_buffers:
+            dist.broadcast(self._buffer_flat, src=gsrc, group=self.process_group)
+        self.arena.refresh_shadow()
+
+    def _join_count(self, mine: int) -> int:
+        """Number of ranks still training (each contributes 1 at the top of a training forward,
+        a shadowing rank contributes 0)."""
+        t = torch.tensor([mine], dtype=torch.int64, device=self.device)
+        dist.all_reduce(t, group=self.process_group)
+        return int(t.item())
 
     def register_comm_hook(self, state, hook) -> None:
         """Escape hatch with torch's GradBucket surface.  Custom hooks run on the

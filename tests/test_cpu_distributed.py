@@ -117,6 +117,50 @@ def _comm_hook_worker(rank, world, port, q):
             dist.destroy_process_group()
 
 
+def _join_worker(rank, world, port, q):
+    """Uneven inputs: rank 0 has 3 batches, rank 1 has 5.  Under ``with model.join():`` nobody
+    hangs and the parameters follow torch DDP's Join algorithm step by step."""
+    try:
+        _init(rank, world, port)
+        import copy
+        from dpt_b200.optim import SGD
+        from dpt_b200.parallel.ddp import DistributedDataParallel as OurDDP
+        from torch.nn.parallel import DistributedDataParallel as TorchDDP
+        torch.manual_seed(3)
+        base = torch.nn.Sequential(torch.nn.Conv2d(3, 8, 3, padding=1), torch.nn.BatchNorm2d(8),
+                                   torch.nn.ReLU(), torch.nn.Flatten(), torch.nn.Linear(8 * 8 * 8, 10))
+        ours = OurDDP(copy.deepcopy(base), backend="gloo", bucket_cap_mb=0.01, first_bucket_mb=0.001)
+        ref = TorchDDP(copy.deepcopy(base))
+        assert len(ours.plans) >= 2
+        opt_o = SGD(ours.parameters(), lr=0.05, momentum=0.9)
+        opt_r = torch.optim.SGD(ref.parameters(), lr=0.05, momentum=0.9)
+        n_batches = 3 if rank == 0 else 5
+        g = torch.Generator().manual_seed(20 + rank)
+        data = [(torch.randn(4, 3, 8, 8, generator=g), torch.randint(0, 10, (4,), generator=g))
+                for _ in range(n_batches)]
+        for model, opt in ((ours, opt_o), (ref, opt_r)):
+            with model.join():
+                for x, t in data:
+                    opt.zero_grad(set_to_none=True)
+                    torch.nn.functional.cross_entropy(model(x), t).backward()
+                    opt.step()
+        for (n, a), b in zip(ours.module.named_parameters(), ref.module.parameters()):
+            assert torch.allclose(a, b, atol=1e-5, rtol=1e-4), f"{n} differs from torch DDP under join()"
+        # both implementations finish by handing every rank the longest-trained rank's model
+        cs = torch.stack([p.detach().double().sum() for p in ours.parameters()])
+        lo, hi = cs.clone(), cs.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        assert torch.equal(lo, hi), "replicas differ after join()"
+        q.put((rank, "ok"))
+    except Exception:  # noqa: BLE001
+        import traceback
+        q.put((rank, traceback.format_exc()))
+    finally:
+        if dist.is_initialized():
+            dist.destroy_process_group()
+
+
 def _run(worker, world=2):
     from dpt_b200.launcher import free_port
     ctx = mp.get_context("spawn")
@@ -251,3 +295,7 @@ def test_entry_point_two_process_gloo(tmp_path):
     assert lines[0].startswith("epoch,train_loss") and len(lines) == 2
     ck = torch.load(os.path.join(out, "checkpoint.pt"), weights_only=False)
     assert all(k.startswith("module.") for k in ck["model"]) and ck["epoch"] == 1
+
+
+def test_join_with_uneven_inputs_matches_torch_ddp_gloo():
+    _run(_join_worker)
