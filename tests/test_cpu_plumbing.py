@@ -448,3 +448,88 @@ def test_algorithm_table_for_the_default_bucket_plans():
     assert pick(8, False, True) == ["nvls"] * 7 + ["oneshot"]
     assert pick(1, True, True) == ["none"] * 8
     assert tuning.choose_algorithm(512 * 1024, 8, False, True) == "twoshot"   # between the thresholds
+
+
+def test_watchdog_reports_stale_heartbeat_and_device_error_word(monkeypatch):
+    """Communicator.start_watchdog without a GPU: a stub library and an in-memory store.
+    (1) a peer whose heartbeat stops is reported after `stale_s`; (2) a device-side timeout
+    (error word written by a kernel) is decoded into (rank, peer, epoch); (3) a rank that
+    finished cleanly ("done") is not a dead rank."""
+    import time
+    import torch.distributed as dist
+    from dpt_b200.parallel import comm as C
+
+    class Store:
+        def __init__(self):
+            self.d = {}
+
+        def set(self, k, v):
+            self.d[k] = v.encode() if isinstance(v, str) else v
+
+        def get(self, k):
+            return self.d[k]
+
+        def check(self, keys):
+            return all(k in self.d for k in keys)
+
+    class Lib:
+        code = 0
+
+        def dpt_comm_error(self, handle):
+            return Lib.code
+
+    store = Store()
+    monkeypatch.setattr(dist, "is_initialized", lambda: True)
+    monkeypatch.setattr(dist.distributed_c10d, "_get_default_store", lambda: store)
+
+    def make():
+        c = object.__new__(C.Communicator)
+        c.rank, c.world, c.lib, c.handle = 0, 2, Lib(), 1
+        return c
+
+    # (1) rank 1 beat once, long ago
+    store.set("dpt_b200/heartbeat/1", str(time.time() - 100.0))
+    c = make()
+    c.start_watchdog(interval_s=0.02, abort=False, stale_s=5.0)
+    deadline = time.time() + 5
+    while c.fault is None and time.time() < deadline:
+        time.sleep(0.02)
+    c.stop_watchdog()
+    assert c.fault == (0, 1, -1), c.fault
+    assert store.get("dpt_b200/heartbeat/0") == b"done"
+    # (3) the same peer marked done: no fault
+    store.set("dpt_b200/heartbeat/1", "done")
+    c = make()
+    c.start_watchdog(interval_s=0.02, abort=False, stale_s=5.0)
+    time.sleep(0.3)
+    assert c.fault is None and c.peer_heartbeats()[1] == 0.0
+    # (2) device error word: bit 31 | peer << 24 | epoch
+    Lib.code = 0x80000000 | (1 << 24) | 77
+    deadline = time.time() + 5
+    while c.fault is None and time.time() < deadline:
+        time.sleep(0.02)
+    c.stop_watchdog()
+    Lib.code = 0
+    assert c.fault == (0, 1, 77), c.fault
+
+
+def test_momentum_shards_follow_the_kernels_slice_formula():
+    """DistributedDataParallel.momentum_shards must name exactly the slices the fused two-shot /
+    NVLS kernels update on each rank (p2p_collectives.cu: per = ceil(n4 / world) float4, rank r
+    owns [r*per, min(n4, (r+1)*per))), skip one-shot buckets, and tile every sharded bucket."""
+    from dpt_b200.parallel.ddp import DistributedDataParallel as D
+
+    class R:
+        def bucket_algos(self):
+            return [0, 2, 1, 3]
+
+    d = object.__new__(D)
+    d._fusion_cfg, d.world_size, d.reducer = object(), 3, R()
+    d.plans = [{"offset": 0, "numel": 40}, {"offset": 40, "numel": 16}, {"offset": 56, "numel": 8},
+               {"offset": 64, "numel": 4}]
+    shards = D.momentum_shards(d)
+    assert shards == [(0, 16, 0), (16, 32, 1), (32, 40, 2),            # n4 = 10, per = 4
+                      (40, 48, 0), (48, 56, 1),                        # n4 = 4, per = 2: rank 2 owns nothing
+                      (64, 68, 0)]                                     # n4 = 1: only rank 0
+    d._fusion_cfg = None
+    assert D.momentum_shards(d) == []
