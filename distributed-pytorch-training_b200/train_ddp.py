@@ -25,6 +25,22 @@ from .trainer import train_one_epoch, validate
 from .utils import nvtx
 
 
+def _maybe_inject_fault(epoch: int, rank: int, output_dir: str) -> None:
+    """Fault injection for the restart tests: ``DPT_FAULT_EXIT="<rank>:<epoch>"`` makes
+    that rank die (exit code 1, no teardown) at the start of that epoch — once per output
+    directory, so the restarted job runs through."""
+    import os
+    spec = os.environ.get("DPT_FAULT_EXIT", "")
+    if not spec:
+        return
+    frank, fepoch = (int(v) for v in spec.split(":"))
+    marker = Path(output_dir) / ".fault_injected"
+    if rank == frank and epoch == fepoch and not marker.exists():
+        marker.write_text(f"rank {rank} killed at epoch {epoch}\n")
+        print(f"[fault injection] rank {rank} exits at the start of epoch {epoch}", flush=True)
+        os._exit(1)
+
+
 def main(argv=None):
     args = parse_args(argv)
     Path(args.output_dir).mkdir(parents=True, exist_ok=True)
@@ -92,6 +108,7 @@ def main(argv=None):
     js = M.MetricsJSON(args.metrics_json, enabled=(rank == 0))
 
     for epoch in range(start_epoch, args.epochs):
+        _maybe_inject_fault(epoch, rank, args.output_dir)
         train_loss, train_acc, epoch_time = train_one_epoch(
             epoch, model, train_loader, optimizer, criterion, device, args, rank, world_size,
             scaler=scaler, train_sampler=train_sampler, train_step=train_step, profiler=profiler)
