@@ -270,6 +270,8 @@ class TrainStep:
         self.graph = g
         self._restore(snap)
         torch.cuda.synchronize()
+        if self.trace is not None:
+            self.trace.zero_()              # drop the warm-up steps' records
         if self.ddp is not None and self.ddp.comm is not None:
             self.ddp.comm.check_health()
 

@@ -13,7 +13,9 @@ stream (csrc/reducer/reducer.cpp), giving per step:
   per bucket           bytes, ready/start/end offsets, bus GB/s (S/t * 2(N-1)/N)
 
 Aggregation across ranks is max (BASELINE.json metric convention).  Event timing is not
-available inside a captured CUDA graph, so profile in eager mode.
+available inside a captured CUDA graph; the graph-replayed step is profiled from the device-clock
+trace instead (``summarize_trace`` below: phase stamps + one record per bucket kernel written by
+the kernels themselves, ``TrainStep(trace_records=...)``).
 """
 from __future__ import annotations
 
@@ -83,3 +85,47 @@ class GradSyncProfiler:
         if "step_ms" in out and "comm_exposed_ms" in out and out["step_ms"] > 0:
             out["exposed_sync_pct"] = 100.0 * out["comm_exposed_ms"] / out["step_ms"]
         return out
+
+
+def summarize_trace(records: list[dict], world: int = 1, reduce_max: bool = True) -> dict:
+    """Per-step gradient-sync metrics of the CUDA-graph step from ``TrainStep.read_trace()``
+    records (globaltimer ns): stamps 1 step start, 2 forward done, 3 every backward kernel done,
+    4 every bucket kernel done, 5 step end; bucket records carry start / first-barrier / end.
+    Same keys as ``GradSyncProfiler.summary`` (ms), mean over complete steps, max over ranks."""
+    steps, cur = [], None
+    for r in sorted(records, key=lambda r: r["t0"]):
+        if r["kind"] == "stamp" and r.get("tag") == 1:
+            cur = {"t": {}, "buckets": []}
+            steps.append(cur)
+        if cur is None:
+            continue
+        if r["kind"] == "stamp":
+            cur["t"][r["tag"]] = r["t0"]
+        else:
+            cur["buckets"].append(r)
+    full = [s for s in steps if all(k in s["t"] for k in (1, 2, 3, 4, 5))]
+    if not full:
+        return {}
+    for s in full:      # bucket kernels of eager (unstamped) steps that follow do not belong here
+        s["buckets"] = [b for b in s["buckets"] if s["t"][1] <= b["t0"] <= s["t"][5]]
+
+    def mean(f):
+        return sum(f(s) for s in full) / len(full) / 1e6      # ns -> ms
+
+    out = {
+        "step_ms": mean(lambda s: s["t"][5] - s["t"][1]),
+        "backward_ms": mean(lambda s: s["t"][3] - s["t"][2]),
+        "comm_busy_ms": mean(lambda s: sum(b["t1"] - b["t0"] for b in s["buckets"])),
+        "comm_exposed_ms": mean(lambda s: max(0, s["t"][4] - s["t"][3])),
+    }
+    out["overlap_ms"] = max(0.0, out["comm_busy_ms"] - out["comm_exposed_ms"])
+    out["barrier_wait_ms"] = mean(lambda s: sum(max(0, b["t_barrier"] - b["t0"]) for b in s["buckets"]))
+    keys = list(out)
+    if reduce_max and world > 1 and dist.is_available() and dist.is_initialized() and torch.cuda.is_available():
+        t = torch.tensor([out[k] for k in keys], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        out = {k: float(v) for k, v in zip(keys, t.tolist())}
+    if out["step_ms"] > 0:
+        out["exposed_sync_pct"] = 100.0 * out["comm_exposed_ms"] / out["step_ms"]
+    out["steps"] = len(full)
+    return out

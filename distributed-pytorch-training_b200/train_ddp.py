@@ -61,16 +61,15 @@ def main(argv=None):
     # SGD update inside the all-reduce kernels) is what runs unless it cannot or is turned off
     native_ok = device.type == "cuda" and args.backend == "native"
     if args.cuda_graph is None:
-        args.cuda_graph = native_ok and not args.profile_sync
+        args.cuda_graph = native_ok
     if args.fused_optimizer is None:
         args.fused_optimizer = native_ok and args.optimizer == "sgd" and not fp16 \
             and args.momentum != 0
     # per-bucket event timing cannot be recorded inside a captured CUDA graph: with --cuda-graph
     # the profiler only reports the (event-timed) step time
     bucket_profile = args.profile_sync and not args.cuda_graph
-    if args.profile_sync and args.cuda_graph and rank == 0:
-        print("[grad-sync] --cuda-graph: per-bucket timing disabled (run with --no-cuda-graph "
-              "to profile gradient sync)")
+    # (under the graph the profile comes from the device-clock trace the kernels write themselves)
+    trace_profile = bool(args.profile_sync and args.cuda_graph)
     model = maybe_wrap_ddp(model, device, local_rank, backend=args.backend,
                            bucket_cap_mb=args.bucket_cap_mb, profile=bucket_profile,
                            comm_timeout=args.comm_timeout, allreduce_algo=args.allreduce_algo)
@@ -101,8 +100,8 @@ def main(argv=None):
         shape = (args.batch_size, 3, args.image_size, args.image_size)
         step_dtype = torch.float32 if not args.amp else (torch.float16 if fp16 else torch.bfloat16)
         train_step = TrainStep(model, optimizer, scaler, batch_shape=shape, cuda_graph=True,
-                               dtype=step_dtype)
-    profiler = GradSyncProfiler(ddp) if args.profile_sync else None
+                               dtype=step_dtype, trace_records=16384 if trace_profile else 0)
+    profiler = GradSyncProfiler(ddp) if (args.profile_sync and not trace_profile) else None
 
     csv = M.MetricsCSV(args.output_dir, enabled=(rank == 0))
     js = M.MetricsJSON(args.metrics_json, enabled=(rank == 0))
@@ -117,6 +116,9 @@ def main(argv=None):
         else:
             val_loss, val_acc = validate(model, val_loader, criterion, device, rank, world_size, args)
         sync = profiler.summary() if profiler is not None else {}
+        if trace_profile and train_step is not None and train_step.trace is not None:
+            from .profiler import summarize_trace
+            sync = summarize_trace(train_step.read_trace(reset=True), world_size)
         if rank == 0:
             print(M.epoch_line(epoch, args.epochs, train_loss, train_acc, val_loss, val_acc,
                                epoch_time))

@@ -533,3 +533,28 @@ def test_momentum_shards_follow_the_kernels_slice_formula():
                       (64, 68, 0)]                                     # n4 = 1: only rank 0
     d._fusion_cfg = None
     assert D.momentum_shards(d) == []
+
+
+def test_trace_summary_of_the_graph_step():
+    """profiler.summarize_trace on hand-made records: two complete steps and a truncated third;
+    exposed sync = (all bucket kernels done) - (all backward kernels done), never negative."""
+    from dpt_b200.profiler import summarize_trace
+    us = 1000
+    recs = []
+    for k, t0 in enumerate((0, 1_000_000)):
+        recs += [{"kind": "stamp", "tag": 1, "t0": t0}, {"kind": "stamp", "tag": 2, "t0": t0 + 300 * us},
+                 {"kind": "stamp", "tag": 3, "t0": t0 + 700 * us},
+                 {"kind": "stamp", "tag": 4, "t0": t0 + (720 if k == 0 else 700) * us},
+                 {"kind": "stamp", "tag": 5, "t0": t0 + 722 * us},
+                 {"kind": "twoshot", "bytes": 1 << 20, "t0": t0 + 320 * us, "t_barrier": t0 + 330 * us,
+                  "t1": t0 + 380 * us},
+                 {"kind": "oneshot", "bytes": 38144, "t0": t0 + 702 * us, "t_barrier": t0 + 710 * us,
+                  "t1": t0 + 718 * us}]
+    recs += [{"kind": "stamp", "tag": 1, "t0": 2_000_000}, {"kind": "stamp", "tag": 2, "t0": 2_300_000}]
+    s = summarize_trace(recs, world=1)
+    assert s["steps"] == 2
+    assert abs(s["step_ms"] - 0.722) < 1e-9 and abs(s["backward_ms"] - 0.400) < 1e-9
+    assert abs(s["comm_busy_ms"] - 0.076) < 1e-9 and abs(s["comm_exposed_ms"] - 0.010) < 1e-9
+    assert abs(s["barrier_wait_ms"] - 0.018) < 1e-9
+    assert abs(s["exposed_sync_pct"] - 100 * 0.010 / 0.722) < 1e-9
+    assert summarize_trace([{"kind": "stamp", "tag": 2, "t0": 5}]) == {}
