@@ -170,11 +170,16 @@ def get_dataloaders(args, rank: int, world_size: int):
     sampler = DistributedSampler(train_ds, num_replicas=world_size, rank=rank,
                                  shuffle=True) if distributed else None
     pin = torch.cuda.is_available()
+    # the reference's loaders respawn their 4 worker processes at every epoch, twice (train and
+    # validation; persistent_workers defaults to False, torch dataloader.py:264-265): same batches
+    # here, but the workers stay alive between epochs
+    keep = args.workers > 0
     train_loader = DataLoader(train_ds, batch_size=args.batch_size, shuffle=(sampler is None),
                               sampler=sampler, num_workers=args.workers, pin_memory=pin,
-                              drop_last=False)
+                              drop_last=False, persistent_workers=keep)
     val_loader = DataLoader(test_ds, batch_size=args.batch_size, shuffle=False,
-                            num_workers=args.workers, pin_memory=pin, drop_last=False)
+                            num_workers=args.workers, pin_memory=pin, drop_last=False,
+                            persistent_workers=keep)
     if getattr(train_ds, "raw", False):
         # uint8 batches: the loops apply these on the device (trainer.py, _device_batch)
         train_loader.gpu_transform = GpuAugment(seed=getattr(args, "seed", 0) + rank, train=True)
