@@ -60,6 +60,8 @@ def parse():
     p.add_argument("--no-extras", action="store_true",
                    help="skip the cold-path evidence after the timed regions (multi-GPU reduction "
                         "checks, fp16 + GradScaler arm, loss parity vs torchvision + torch DDP)")
+    p.add_argument("--extras-timeout", type=float, default=150.0,
+                   help="seconds the cold-path extras may take before the bench line is printed without them")
     p.add_argument("--tail-kb", type=float, default=None, help="tail bucket size (KiB; 0 = off)")
     p.add_argument("--oneshot-max-kb", type=float, default=None,
                    help="buckets up to this size use the one-shot push kernel")
@@ -292,6 +294,33 @@ def run_ours(a):
     if sync:
         res["grad_sync"] = sync
     # ---- evidence beside the number (all cold path, after the timed regions) ------------------
+    # The bench line must never be lost to an extra: if the extras have not finished after
+    # `--extras-timeout` seconds (a rank stuck in a collective, say), every rank stops and rank 0
+    # prints the line with what it has.
+    printed = threading.Lock()
+
+    def emit(note=None):
+        if not printed.acquire(blocking=False):
+            return
+        if rank == 0:
+            for _ in range(3):          # the main thread may be adding a key at this very moment
+                try:
+                    line = dict(res)
+                    if note:
+                        line["extras_note"] = note
+                    print(json.dumps(line), flush=True)
+                    break
+                except RuntimeError:
+                    time.sleep(0.05)
+
+    def bail():
+        emit(f"extras did not finish within {a.extras_timeout:.0f} s and were abandoned")
+        os._exit(0)
+
+    timer = threading.Timer(a.extras_timeout, bail)
+    timer.daemon = True
+    timer.start()
+
     def attempt(name, fn):
         try:
             res[name] = fn()
@@ -308,8 +337,8 @@ def run_ours(a):
         attempt("fp16_gradscaler", lambda: fp16_scaler_arm(a, device, rank, world, local))
     if not a.no_extras and a.arch in ("resnet18", "resnet34", "resnet50"):
         attempt("loss_parity", lambda: loss_parity(a, device, rank, world, local))
-    if rank == 0:
-        print(json.dumps(res))
+    timer.cancel()
+    emit()
     cleanup_distributed()
 
 
