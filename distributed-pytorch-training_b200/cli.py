@@ -31,7 +31,7 @@ def build_parser() -> argparse.ArgumentParser:
                    help="synthetic CIFAR-shaped data (no dataset files / network needed)")
     p.add_argument("--synthetic-size", default=50000, type=int,
                    help="number of synthetic training samples")
-    p.add_argument("--arch", default="resnet18", choices=["resnet18", "resnet34", "resnet50"],
+    p.add_argument("--arch", default="resnet18", choices=["resnet18", "resnet34", "resnet50", "resnet101", "resnet152"],
                    help="model architecture")
     p.add_argument("--num-classes", default=10, type=int)
     p.add_argument("--image-size", default=32, type=int)

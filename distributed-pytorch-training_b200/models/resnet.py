@@ -226,10 +226,23 @@ def resnet50(num_classes: int = 1000) -> ResNet:
     return ResNet(Bottleneck, [3, 4, 6, 3], num_classes)
 
 
+def resnet101(num_classes: int = 1000) -> ResNet:
+    return ResNet(Bottleneck, [3, 4, 23, 3], num_classes)
+
+
+def resnet152(num_classes: int = 1000) -> ResNet:
+    return ResNet(Bottleneck, [3, 8, 36, 3], num_classes)
+
+
+ARCHS = {"resnet18": resnet18, "resnet34": resnet34, "resnet50": resnet50, "resnet101": resnet101,
+         "resnet152": resnet152}
+
+
 def build_model(device, arch: str = "resnet18", num_classes: int = 10) -> ResNet:
-    """Reference train_ddp.py:153-156 (``resnet18(num_classes=10).to(device)``)."""
-    model = {"resnet18": resnet18, "resnet34": resnet34, "resnet50": resnet50}[arch](num_classes)
-    return model.to(device)
+    """Reference train_ddp.py:153-156 (``resnet18(num_classes=10).to(device)``).  The other
+    torchvision depths share the block types and therefore the kernels; 18 and 50 are the
+    benchmarked ones (BASELINE.json configs 2 and 4)."""
+    return ARCHS[arch](num_classes).to(device)
 
 
 # ===================================================================================== engine

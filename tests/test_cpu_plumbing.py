@@ -166,7 +166,7 @@ def test_sgd_and_adam_match_torch_on_cpu():
         assert torch.allclose(so["state"][k]["momentum_buffer"], sr["state"][k]["momentum_buffer"])
 
 
-@pytest.mark.parametrize("arch", ["resnet18", "resnet34", "resnet50"])
+@pytest.mark.parametrize("arch", ["resnet18", "resnet34", "resnet50", "resnet101", "resnet152"])
 def test_state_dict_keys_match_torchvision(arch):
     import torchvision
     from dpt_b200.models import resnet as R
@@ -181,7 +181,7 @@ def test_state_dict_keys_match_torchvision(arch):
     ours.load_state_dict(sr)     # torchvision -> ours
     x = torch.randn(2, 3, 32, 32)
     ours.eval(); ref.eval()
-    assert torch.allclose(ours(x), ref(x), atol=1e-4)
+    assert torch.allclose(ours(x), ref(x), atol=1e-4, rtol=1e-5)   # deep nets: outputs of O(100)
 
 
 def test_resnet18_workload_constants():
