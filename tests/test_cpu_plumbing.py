@@ -181,7 +181,8 @@ def test_state_dict_keys_match_torchvision(arch):
     ours.load_state_dict(sr)     # torchvision -> ours
     x = torch.randn(2, 3, 32, 32)
     ours.eval(); ref.eval()
-    assert torch.allclose(ours(x), ref(x), atol=1e-4, rtol=1e-5)   # deep nets: outputs of O(100)
+    a, b = ours(x), ref(x)
+    assert (a - b).abs().max().item() <= 1e-5 * max(1.0, b.abs().max().item())   # deep nets: outputs of O(100)
 
 
 def test_resnet18_workload_constants():
