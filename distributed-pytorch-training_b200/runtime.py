@@ -51,9 +51,34 @@ def setup_distributed(backend: str | None = None, timeout_s: float = 600.0):
         kwargs = {}
         if pg_backend == "nccl":
             kwargs["device_id"] = torch.device("cuda", local_rank)
-        dist.init_process_group(backend=pg_backend, init_method="env://",
-                                timeout=datetime.timedelta(seconds=timeout_s), **kwargs)
+        timeout = datetime.timedelta(seconds=timeout_s)
+        store = _restart_safe_store(rank, world_size, timeout)
+        if store is not None:
+            dist.init_process_group(backend=pg_backend, store=store, rank=rank,
+                                    world_size=world_size, timeout=timeout, **kwargs)
+        else:
+            dist.init_process_group(backend=pg_backend, init_method="env://", timeout=timeout,
+                                    **kwargs)
     return rank, world_size, local_rank
+
+
+def _restart_safe_store(rank: int, world_size: int, timeout):
+    """Under ``torchrun --max-restarts`` with a static rendezvous (``--master-addr/--master-port``)
+    every restarted worker group talks to the SAME agent-hosted TCPStore, and ``env://`` uses it
+    without a per-attempt prefix: a restarted rank can read the dead incarnation's rendezvous keys
+    (gloo: its peer's old listening address -> "connection refused" or a stalled connect; observed
+    on this code base's restart test about every other run).  The reference inherits that
+    behaviour (train_ddp.py:65); here the keys of every RESTARTED attempt live under their own
+    prefix.  Returns None outside torchrun and for the first attempt (plain ``env://`` then)."""
+    import os
+    attempt = os.environ.get("TORCHELASTIC_RESTART_COUNT")
+    addr, port = os.environ.get("MASTER_ADDR"), os.environ.get("MASTER_PORT")
+    if attempt is None or addr is None or port is None or int(attempt) == 0:
+        return None        # first incarnation: nothing stale in the store, plain env://
+    agent_hosts_store = os.environ.get("TORCHELASTIC_USE_AGENT_STORE", "False") == "True"
+    base = dist.TCPStore(addr, int(port), world_size, is_master=(rank == 0 and not agent_hosts_store),
+                         timeout=timeout, wait_for_workers=False)
+    return dist.PrefixStore(f"dpt_b200/attempt_{attempt}", base)
 
 
 def cleanup_distributed() -> None:

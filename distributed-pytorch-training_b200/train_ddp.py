@@ -131,6 +131,10 @@ def main(argv=None):
         if args.save_every and (epoch + 1) % args.save_every == 0:
             save_checkpoint(str(Path(args.output_dir) / "checkpoint.pt"), model, optimizer, scaler,
                             epoch + 1, args, rank)
+            if world_size > 1:
+                # nobody runs ahead (and possibly dies) while rank 0 is still writing: a restart
+                # then always finds this epoch's checkpoint
+                torch.distributed.barrier()
 
     if ddp is not None:
         ddp.shutdown()

@@ -303,27 +303,44 @@ def test_join_with_uneven_inputs_matches_torch_ddp_gloo():
 
 def test_torchrun_restart_resumes_from_the_checkpoint(tmp_path):
     """Elastic recovery as far as the reference's stack offers it: a rank dies at
-    the start of the second epoch, torchrun (--max-restarts 1) tears the group down and starts it
+    the start of the second epoch, torchrun (--max-restarts) tears the group down and starts it
     again with the same command line, ``--resume auto`` picks up the checkpoint written after the
-    first epoch, and the job finishes all epochs — the first epoch is not trained twice."""
+    first epoch, and the job finishes all epochs — the first epoch is not trained twice.
+
+    (With plain ``env://`` the restarted ranks read the dead incarnation's rendezvous keys from
+    the agent's store about every other run — "connection refused" or a stalled connect;
+    ``runtime._restart_safe_store`` gives every attempt its own key prefix.  One retry is kept
+    for a loaded machine; a second rendezvous failure fails the test.)"""
     import subprocess
     from dpt_b200.launcher import free_port
-    out = tmp_path / "exp"
-    env = dict(os.environ, DPT_FAULT_EXIT="1:1", OMP_NUM_THREADS="2")
-    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT"):
-        env.pop(k, None)
-    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
-           "--max-restarts=1", "--monitor-interval=1", "--master-addr", "127.0.0.1",
-           "--master-port", str(free_port()), os.path.join(ROOT, "train_ddp.py"),
-           "--synthetic", "--synthetic-size", "32", "--epochs", "3", "--batch-size", "4", "--workers", "0",
-           "--backend", "gloo", "--print-freq", "100", "--output-dir", str(out), "--save-every", "1",
-           "--resume", "auto", "--steps", "2"]
-    r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600, cwd=ROOT)
-    log = r.stdout + r.stderr
-    assert r.returncode == 0, log[-3000:]
-    assert "[fault injection] rank 1 exits at the start of epoch 1" in log
-    assert "Resumed from" in log and "at epoch 1" in log, log[-3000:]
-    lines = open(out / "metrics_rank0.csv").read().splitlines()
-    assert [ln.split(",")[0] for ln in lines] == ["epoch", "1", "2", "3"], lines
-    ck = torch.load(out / "checkpoint.pt", weights_only=False)
-    assert ck["epoch"] == 3
+    last = ""
+    for attempt in range(2):
+        out = tmp_path / f"exp{attempt}"
+        env = dict(os.environ, DPT_FAULT_EXIT="1:1", OMP_NUM_THREADS="2")
+        for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT"):
+            env.pop(k, None)
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+               "--max-restarts=1", "--monitor-interval=1", "--master-addr", "127.0.0.1",
+               "--master-port", str(free_port()), os.path.join(ROOT, "train_ddp.py"),
+               "--synthetic", "--synthetic-size", "32", "--epochs", "3", "--batch-size", "4", "--workers", "0",
+               "--backend", "gloo", "--print-freq", "100", "--output-dir", str(out), "--save-every", "1",
+               "--resume", "auto", "--steps", "2"]
+        try:
+            r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=150, cwd=ROOT)
+        except subprocess.TimeoutExpired as e:
+            last = "timed out: " + str(e.stdout)[-500:] + str(e.stderr)[-1500:]
+            continue
+        log = r.stdout + r.stderr
+        if r.returncode != 0:
+            last = log[-3000:]
+            if "connectFullMesh" in log or "Connection refused" in log or "timed out" in log:
+                continue                                  # rendezvous trouble, not a resume bug
+            raise AssertionError(last)
+        assert "[fault injection] rank 1 exits at the start of epoch 1" in log
+        assert "Resumed from" in log and "at epoch 1" in log, log[-3000:]
+        lines = open(out / "metrics_rank0.csv").read().splitlines()
+        assert [ln.split(",")[0] for ln in lines] == ["epoch", "1", "2", "3"], lines
+        ck = torch.load(out / "checkpoint.pt", weights_only=False)
+        assert ck["epoch"] == 3
+        return
+    raise AssertionError("torchrun restart did not complete (twice): " + last[-2000:])
